@@ -1,0 +1,395 @@
+#!/usr/bin/env python
+"""Benchmark of the synchronous data-parallel ResNet training step (BASELINE.json metric:
+ResNet-50 train images/sec at 1/2/4/8 B200; conv tensor-pipe utilisation).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload imagenet50|cifar50]
+
+N > 1 is launched by the driver under torchrun (one rank per GPU, NCCL).  One "step" is one
+full training step (forward, backward, gradient all-reduce, fused update) on synthetic data.
+Rank 0 prints ONE JSON line.  See DESIGN.md "Measurement" for how every field is produced.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # name: (dataset, image size, classes, per-GPU batch for weak scaling, weight decay)
+    "imagenet50": dict(dataset="imagenet", size=224, classes=1000, batch=128, wd=1e-4,
+                       desc="ResNet-50 v2 bottleneck [3,4,6,3], ImageNet-shape 224x224, 128 images/GPU (C3)"),
+    "cifar50": dict(dataset="cifar10", size=32, classes=10, batch=128, wd=2e-4,
+                    desc="cifar10_resnet_v2_generator(50) basic blocks, 32x32, 128 images/GPU (C2 net)"),
+}
+# derived images/s from the reference README: ImageNet ResNet-50, 128/worker
+PUBLISHED = {("imagenet50", 1): 123.0, ("imagenet50", 8): 952.0, ("cifar50", 1): 1784.0}
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return dict(hbm=d["hbm_gbs"], tf_burst=d["bf16_tflops"], tf_sust=d.get("bf16_tflops_sustained", d["bf16_tflops"]),
+                    src="measured")
+    return dict(hbm=6650.0, tf_burst=1590.0, tf_sust=1400.0, src="fallback")
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index = index
+        self.samples = []
+        self._stop = threading.Event()
+
+    def run(self):
+        while not self._stop.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+                f = [x.strip() for x in out.strip().split(",")]
+                if len(f) >= 7:
+                    self.samples.append(f)
+            except Exception:
+                pass
+            self._stop.wait(0.2)
+
+    def stop(self):
+        self._stop.set()
+        self.join(timeout=6)
+        sm = sorted(float(s[0]) for s in self.samples if s[0].replace(".", "").isdigit())
+        mx = [float(s[1]) for s in self.samples if s[1].replace(".", "").isdigit()]
+        reasons = []
+        for i, name in enumerate(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")):
+            if any(s[3 + i].lower().startswith("active") for s in self.samples):
+                reasons.append(name)
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(self.samples)}
+
+
+def conv_flops(graph):
+    """Algorithmic FLOPs: 2*N*Ho*Wo*Cout*k^2*Cin per GEMM; dgrad skipped where the
+    input needs no gradient (the stem)."""
+    out = {}
+    for n in graph.nodes:
+        if n.op == "conv2d":
+            x, y = n.inputs[0], n.outputs[0]
+            f = 2.0 * y.numel * n.attrs["k"] ** 2 * x.shape[3]
+            out[y.name] = (f, x.requires_grad)
+    return out
+
+
+def family(name):
+    return name.split(":")[0]
+
+
+def hbm_bytes(name, ex, graph):
+    """Algorithmic HBM bytes of one launch of the HBM-bound families."""
+    fam, _, key = name.partition(":")
+    s = 2 if ex.bf16 else 4
+    if fam in ("bn_stats", "bn_apply", "bn_infer", "bn_bwd_reduce", "bn_bwd_apply"):
+        node = [n for n in graph.nodes if n.op == "bn_act" and n.attrs["scope"] == key][0]
+        E = node.inputs[0].numel
+        fused = ex._fused_add_for(node) is not None
+        if fam == "bn_stats":
+            return E * s * (3 if fused else 1)
+        if fam in ("bn_apply", "bn_infer", "bn_bwd_reduce"):
+            return 2 * E * s
+        slot = node.inputs[0].gradslot
+        return (4 if len(slot.members) > 1 else 3) * E * s
+    if fam == "sgd_momentum_fused":
+        return ex.n_flat * (20 + (2 if ex.bf16 else 0))
+    return None
+
+
+def profile_step(ex, graph, iters=3):
+    """Per-launch CUDA-event timing of the un-captured launch list (same stream the kernels run on)."""
+    import torch
+    lists = [("fwd", ex.fwd), ("bwd", ex.bwd), ("upd", ex.update)]
+    st = torch.cuda.current_stream()
+    acc = {}
+    for it in range(iters + 1):
+        evs = []
+        for _, lst in lists:
+            for name, fn in lst:
+                a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                a.record(st)
+                fn(st.cuda_stream)
+                b.record(st)
+                evs.append((name, a, b))
+        torch.cuda.synchronize()
+        if it == 0:
+            continue        # warm-up
+        for name, a, b in evs:
+            acc.setdefault(name, []).append(a.elapsed_time(b))
+    return {k: sum(v) / len(v) for k, v in acc.items()}
+
+
+def roofline_report(ex, graph, per_launch_ms, pk):
+    cf = conv_flops(graph)
+    fams = {}
+    for name, ms in per_launch_ms.items():
+        fam, _, key = name.partition(":")
+        d = fams.setdefault(fam, dict(ms=0.0, flops=0.0, bytes=0.0, launches=0))
+        d["ms"] += ms
+        d["launches"] += 1
+        base = fam.replace("_tc", "")
+        if base in ("conv_fprop", "conv_dgrad", "conv_wgrad") and key in cf:
+            d["flops"] += cf[key][0]
+        else:
+            b = hbm_bytes(name, ex, graph)
+            if b:
+                d["bytes"] += b
+    total = sum(d["ms"] for d in fams.values())
+    table = []
+    for fam, d in sorted(fams.items(), key=lambda kv: -kv[1]["ms"]):
+        row = dict(kernel=fam, launches=d["launches"], ms=round(d["ms"], 4), share=round(d["ms"] / total, 4))
+        if d["flops"]:
+            row.update(bound="tensor", achieved=round(d["flops"] / d["ms"] / 1e9, 2), unit="TFLOP/s",
+                       frac=round(d["flops"] / d["ms"] / 1e9 / pk["tf_sust"], 4))
+        elif d["bytes"]:
+            row.update(bound="hbm", achieved=round(d["bytes"] / d["ms"] / 1e6, 1), unit="GB/s",
+                       frac=round(d["bytes"] / d["ms"] / 1e6 / pk["hbm"], 4))
+        table.append(row)
+    top = next((r for r in table if "bound" in r), None)
+    roof = None
+    if top:
+        roof = dict(kernel=top["kernel"], bound=top["bound"], achieved=top["achieved"],
+                    peak=pk["tf_sust"] if top["bound"] == "tensor" else pk["hbm"], unit=top["unit"], frac=top["frac"],
+                    traffic=None, peak_source=pk["src"] + (" sustained bf16" if top["bound"] == "tensor" else " copy"),
+                    share_of_step=top["share"], launches_per_step=top["launches"])
+    return roof, table, total
+
+
+def cpu_reference_step(workload, batch, steps, warmup, threads=None):
+    """The CPU restatement of the reference's step (oracle, torch-CPU oneDNN, fp32): the reference's
+    own TensorFlow CPU path is unavailable on this box (TensorFlow is not installed)."""
+    import torch
+    from oracle import resnet_oracle as ro
+    wl = WORKLOADS[workload]
+    torch.set_num_threads(threads or os.cpu_count())
+    torch.set_flush_denormal(True)
+    g = torch.Generator().manual_seed(1000)
+    x = torch.randn(batch, wl["size"], wl["size"], 3, generator=g)
+    y = torch.eye(wl["classes"])[torch.randint(0, wl["classes"], (batch,), generator=g)]
+    net = ro.OfficialResNetV2(wl["dataset"], 50, wl["classes"], dtype=torch.float32, seed=0)
+    tr = ro.Trainer(net, wl["wd"], "mom")
+    times = []
+    for i in range(warmup + steps):
+        t0 = time.perf_counter()
+        tr.step([(x, y)], 0.1)
+        if i >= warmup:
+            times.append(time.perf_counter() - t0)
+    dt = sum(times) / len(times)
+    return batch / dt, dt, torch.get_num_threads()
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    wl = WORKLOADS[args.workload]
+    batch = 8 if args.workload == "imagenet50" else 64
+    steps = max(1, min(args.steps, 5))
+    warm = 1
+    ips, dt, threads = cpu_reference_step(args.workload, batch, steps, warm)
+    line = {
+        "impl": "reference", "metric": "train images/sec", "value": round(ips, 3), "unit": "images/s",
+        "n_gpus": args.gpus, "steps": steps, "warmup": warm, "ms_per_step": round(dt * 1e3, 2),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": args.workload, "description": wl["desc"], "sample_batch": batch},
+        "cpu_baseline": {"value": round(ips, 3), "unit": "images/s", "cores": threads, "kind": "port",
+                         "sample": "%d timed steps of a %d-image batch of the same net/shape (oracle, torch-CPU fp32); "
+                                   "the reference's TF CPU path is unavailable on this box" % (steps, batch)},
+        "e2e": {"value": round(ips, 3), "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from distributed_tensorflow_resnet_b200 import resnet_model, FLAGS, _lib
+    wl = WORKLOADS[args.workload]
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    if world != args.gpus and rank == 0:
+        sys.stderr.write("warning: --gpus %d but WORLD_SIZE %d\n" % (args.gpus, world))
+    B = args.batch or wl["batch"]
+    dev = torch.device("cuda", local)
+    dt = torch.bfloat16 if args.dtype == "bf16" else torch.float32
+    FLAGS.reset()
+    FLAGS.update(dataset=wl["dataset"], compute_dtype=args.dtype, use_cuda_graph=not args.no_graph, resnet_size=50,
+                 seed=0, sync_replicas=True, job_name="worker" if world > 1 else None, replicas_to_aggregate=world)
+    gen = torch.Generator().manual_seed(1000 + rank)
+    host_img = torch.randn(B, wl["size"], wl["size"], 3, generator=gen).pin_memory()        # fp32, as tf.data yields
+    lab = torch.randint(0, wl["classes"], (B,), generator=gen)
+    host_lab = torch.zeros(B, wl["classes"]).pin_memory()
+    host_lab[torch.arange(B), lab] = 1.0
+    images = torch.empty(B, wl["size"], wl["size"], 3, dtype=torch.float32, device=dev)   # model casts to bf16 itself
+    labels = torch.empty(B, wl["classes"], dtype=torch.float32, device=dev)
+    images.copy_(host_img)
+    labels.copy_(host_lab)
+    hps = resnet_model.HParams(num_classes=wl["classes"], lrn_rate=0.1, weight_decay_rate=wl["wd"], optimizer='mom')
+    model = resnet_model.ResNet(hps, images, labels, 'train')
+    model.build_graph()
+    ex = model.executor
+    model.lrn_rate = 0.1
+    pk = peaks()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident throughput -----------------------------------------------------
+    for _ in range(args.warmup):
+        model.train_op()
+    barrier()
+    sampler = ClockSampler(local) if rank == 0 else None
+    if sampler:
+        sampler.start()
+    l0 = _lib.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        model.train_op()
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1)
+    clocks = sampler.stop() if sampler else None
+    launched_live = _lib.launch_count() - l0
+    t = torch.tensor([ms], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = t.item()
+    value = world * B * args.steps / (ms / 1e3)
+
+    # ---- end to end through the public API with host buffers ------------------------------
+    copy_stream = torch.cuda.Stream()
+    stage_i = [torch.empty_like(images) for _ in range(2)]
+    stage_l = [torch.empty_like(labels) for _ in range(2)]
+    ready = [torch.cuda.Event() for _ in range(2)]
+    consumed = [torch.cuda.Event() for _ in range(2)]
+    out_host = torch.zeros(2, dtype=torch.float32).pin_memory()
+
+    def e2e_steps(k):
+        cur = torch.cuda.current_stream()
+        for i in range(k):
+            sl = i % 2
+            with torch.cuda.stream(copy_stream):
+                copy_stream.wait_event(consumed[sl])
+                stage_i[sl].copy_(host_img, non_blocking=True)          # H2D from pinned host memory
+                stage_l[sl].copy_(host_lab, non_blocking=True)
+                ready[sl].record(copy_stream)
+            cur.wait_event(ready[sl])
+            images.copy_(stage_i[sl], non_blocking=True)
+            labels.copy_(stage_l[sl], non_blocking=True)
+            consumed[sl].record(cur)
+            model.train_op()
+            out_host.copy_(model._loss[1].buf, non_blocking=True)      # D2H of the step's loss / precision
+        torch.cuda.current_stream().synchronize()
+        return float(out_host[0])
+
+    for ev in consumed:
+        ev.record(torch.cuda.current_stream())
+    e2e_steps(2)
+    barrier()
+    e0.record()
+    last_loss = e2e_steps(args.steps)
+    e1.record()
+    barrier()
+    t = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_ms = t.item()
+    e2e_value = world * B * args.steps / (e2e_ms / 1e3)
+    h2d = host_img.numel() * 4 + host_lab.numel() * 4
+    d2h = 8
+
+    line = None
+    if rank == 0:
+        # ---- per-kernel roofline (un-captured launch list, CUDA events per launch) ------------
+        per_launch = profile_step(ex, model.graph, iters=2)
+        roof, table, prof_total = roofline_report(ex, model.graph, per_launch, pk)
+        cpu = None
+        if not args.no_cpu_baseline:
+            cb = 8 if args.workload == "imagenet50" else 64
+            ips, cdt, threads = cpu_reference_step(args.workload, cb, 2, 1)
+            cpu = {"value": round(ips, 3), "unit": "images/s", "cores": threads, "kind": "port",
+                   "sample": "2 timed steps of a %d-image batch of the same net/shape (oracle, torch-CPU fp32, %.1f s/step); "
+                             "reference TF CPU path unavailable on this box" % (cb, cdt)}
+        conv_ms = sum(r["ms"] for r in table if r["kernel"].startswith("conv_"))
+        conv_fl = sum(f * (3 if rg else 2) for f, rg in conv_flops(model.graph).values())
+        line = {
+            "metric": "train images/sec", "value": round(value, 2), "unit": "images/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms / args.steps, 4),
+            "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": (round(value / PUBLISHED[(args.workload, world)], 3)
+                            if (args.workload, world) in PUBLISHED and B == wl["batch"] else None),
+            "dtype": args.dtype, "data": "synthetic",
+            "config": {"workload": args.workload, "description": wl["desc"], "per_gpu_batch": B,
+                       "global_batch": B * world, "parallelism": "dp%d" % world,
+                       "optimizer": "momentum 0.9 + L2 wd %g, lr 0.1" % wl["wd"],
+                       "cuda_graph": not args.no_graph,
+                       "cache": "working set (activations + gradients, GBs) far exceeds the 126 MB L2; no explicit flush",
+                       "conv_impl": sorted({family(n) for n, _ in ex.fwd + ex.bwd if n.startswith("conv_")})},
+            "e2e": {"value": round(e2e_value, 2), "unit": "images/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "ms_per_step": round(e2e_ms / args.steps, 4), "last_loss": last_loss},
+            "gpu_launches": int(ex.count_launches() * args.steps),
+            "gpu_launches_outside_graph": int(launched_live),
+            "clocks": clocks,
+            "roofline": roof,
+            "conv": {"tflops_all_conv_kernels": round(conv_fl / conv_ms / 1e9, 2) if conv_ms else None,
+                     "frac_of_sustained_peak": round(conv_fl / conv_ms / 1e9 / pk["tf_sust"], 4) if conv_ms else None,
+                     "gflop_per_step": round(conv_fl / 1e9, 2)},
+            "kernels": table,
+            "profiled_step_ms": round(prof_total, 3),
+            "cpu_baseline": cpu,
+            "loss": {"xent": ex.scalars()[0], "cost": ex.scalars()[2]},
+        }
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    if line is not None:
+        print(json.dumps(line))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="imagenet50", choices=sorted(WORKLOADS))
+    ap.add_argument("--dtype", default="bf16", choices=["bf16", "f32"])
+    ap.add_argument("--batch", type=int, default=0, help="per-GPU batch (default: the workload's)")
+    ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.warmup < 3 and args.impl == "ours":
+        args.warmup = 3
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

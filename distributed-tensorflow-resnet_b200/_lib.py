@@ -1,0 +1,103 @@
+"""ctypes binding of librn_b200.so (the C ABI declared in include/rn_b200.h).
+
+There is NO fallback: if the shared library cannot be built or loaded, importing this module
+raises, and every compute call raises on a non-zero status with the library's own message.
+"""
+import ctypes as C
+import os
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+SO_PATH = os.path.join(HERE, "librn_b200.so")
+
+RN_F32, RN_BF16 = 0, 1
+
+
+class RnError(RuntimeError):
+    pass
+
+
+class ConvDesc(C.Structure):
+    """rn_conv_desc (include/rn_b200.h)."""
+    _fields_ = [(n, C.c_int32) for n in
+                ("N", "H", "W", "Cin", "Ho", "Wo", "Cout", "k", "stride", "pad", "dtype")]
+
+
+def _load():
+    if not os.path.exists(SO_PATH):
+        # build in-tree (needs nvcc); raises if impossible
+        import importlib.util
+        spec = importlib.util.spec_from_file_location("_rn_build", os.path.join(HERE, "build.py"))
+        mod = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(mod)
+        mod.build(verbose=False)
+    if not os.path.exists(SO_PATH):
+        raise RnError("librn_b200.so is missing and could not be built; there is no CPU fallback")
+    return C.CDLL(SO_PATH)
+
+
+_so = _load()
+
+vp, i32, i64, f32, sz, u32 = C.c_void_p, C.c_int32, C.c_int64, C.c_float, C.c_size_t, C.c_uint32
+pdesc = C.POINTER(ConvDesc)
+
+# name -> (restype, argtypes); every symbol declared in include/rn_b200.h must appear here
+SIGNATURES = {
+    "rn_last_error": (C.c_char_p, []),
+    "rn_abi_version": (C.c_int, []),
+    "rn_launch_count": (C.c_uint64, []),
+    "rn_conv2d_fprop": (C.c_int, [pdesc, vp, vp, vp, vp]),
+    "rn_conv2d_dgrad": (C.c_int, [pdesc, vp, vp, vp, f32, vp]),
+    "rn_conv2d_wgrad_scratch_bytes": (sz, [pdesc]),
+    "rn_conv2d_wgrad": (C.c_int, [pdesc, vp, vp, vp, vp, sz, vp]),
+    "rn_convtc_supported": (C.c_int, [pdesc, C.c_int]),
+    "rn_convtc_scratch_bytes": (sz, [pdesc, C.c_int]),
+    "rn_convtc_plan_create": (C.c_int, [pdesc, C.c_int, vp, vp, vp, vp, sz, C.POINTER(vp)]),
+    "rn_convtc_run": (C.c_int, [vp, f32, vp]),
+    "rn_convtc_plan_destroy": (C.c_int, [vp]),
+    "rn_weights_to_bf16": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, vp, vp, vp]),
+    "rn_bn_scratch_bytes": (sz, [i64, i32]),
+    "rn_bn_stats_fwd": (C.c_int, [vp, vp, vp, i64, i32, i32, f32, f32, i32, vp, vp, vp, vp, vp, sz, vp]),
+    "rn_bn_apply_act_fwd": (C.c_int, [vp, vp, i64, i32, i32, vp, vp, vp, vp, i32, f32, f32, vp]),
+    "rn_bn_act_bwd_reduce": (C.c_int, [vp, vp, i64, i32, i32, vp, vp, vp, vp, f32, vp, vp, vp, sz, vp]),
+    "rn_bn_act_bwd_apply": (C.c_int, [vp, vp, vp, vp, i64, i32, i32, vp, vp, vp, vp, vp, vp, f32, vp]),
+    "rn_maxpool3x3s2_fwd": (C.c_int, [vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, vp]),
+    "rn_maxpool3x3s2_bwd": (C.c_int, [vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, f32, vp]),
+    "rn_avgpool_fwd": (C.c_int, [vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, i32, i32, vp]),
+    "rn_avgpool_bwd": (C.c_int, [vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, i32, i32, f32, vp]),
+    "rn_dense_fwd": (C.c_int, [vp, vp, vp, vp, i32, i32, i32, vp]),
+    "rn_dense_bwd": (C.c_int, [vp, vp, vp, vp, vp, vp, i32, i32, i32, vp]),
+    "rn_softmax_xent": (C.c_int, [vp, vp, i32, i32, vp, vp, vp, vp]),
+    "rn_optimizer_scratch_bytes": (sz, [i64]),
+    "rn_sgd_momentum_fused": (C.c_int, [vp, vp, vp, vp, i64, vp, vp, f32, f32, f32, i32, vp, vp, sz, vp]),
+    "rn_l2_sumsq": (C.c_int, [vp, i64, vp, vp, vp, sz, vp]),
+    "rn_cifar_decode": (C.c_int, [vp, i64, i32, i32, i32, vp, i32, i32, i32, u32, u32, u32, vp, vp, i32, vp, vp, vp, vp]),
+    "rn_cast": (C.c_int, [vp, vp, i64, i32, i32, vp]),
+    "rn_add_inplace": (C.c_int, [vp, vp, i64, i32, vp]),
+    "rn_add": (C.c_int, [vp, vp, vp, i64, i32, vp]),
+    "rn_pad_channels": (C.c_int, [vp, vp, i64, i32, i32, i32, i32, vp]),
+}
+
+for _name, (_res, _args) in SIGNATURES.items():
+    _fn = getattr(_so, _name)   # AttributeError here == a declared symbol is not exported
+    _fn.restype = _res
+    _fn.argtypes = _args
+
+lib = _so
+
+
+def last_error():
+    return _so.rn_last_error().decode(errors="replace")
+
+
+def check(rc, what=""):
+    if rc != 0:
+        raise RnError("%s failed (status %d): %s" % (what or "librn_b200 call", rc, last_error()))
+
+
+def launch_count():
+    return int(_so.rn_launch_count())
+
+
+def ptr(t):
+    """Device (or host) address of a torch tensor, or None."""
+    return None if t is None else t.data_ptr()

@@ -1,0 +1,472 @@
+// Batch-norm (+ leaky ReLU, + residual add) forward / backward: HBM-streaming kernels.
+//
+// x is viewed as [M = N*H*W rows, C channels] (NHWC).  Every thread owns ONE 128-bit column
+// group (4 fp32 or 8 bf16 channels) and walks down the rows, so per-channel constants live in
+// registers and every warp reads up to 512 contiguous bytes per row.  Per-channel reductions:
+// registers -> warp shuffles (when several rows share a warp) -> shared memory -> one fp32
+// partial per CTA in caller scratch -> the last CTA of each channel chunk (atomic ticket)
+// finalises in fp64 in a fixed order (deterministic).
+//
+// Algorithmic HBM bytes (s = bytes/element, E = M*C):
+//   stats            : E*s            (+2*E*s when the residual add is fused: read addend, write z)
+//   apply+act        : 2*E*s
+//   bwd reduce       : 2*E*s          (dy, x)
+//   bwd apply        : 3*E*s          (+E*s with the shortcut-gradient addend)
+#include "rn_common.cuh"
+
+namespace rn {
+
+constexpr int BN_THREADS = 256;
+constexpr int BN_MAX_CHUNKS = 64;       // counters reserved at the head of scratch
+constexpr int BN_MAX_G = RN_NUM_SMS * 4;  // row-CTAs per channel chunk (upper bound)
+
+struct BnLayout {
+  int CV;     // column groups per row
+  int CW;     // column groups per CTA
+  int RY;     // rows per CTA iteration
+  int gridY;  // channel chunks
+  int G;      // row CTAs
+};
+
+template <typename T>
+static BnLayout bn_layout(int64_t M, int C, int waves) {
+  BnLayout L;
+  constexpr int V = Vec<T>::N;
+  L.CV = C / V;
+  L.CW = L.CV < 32 ? L.CV : 32;
+  L.RY = BN_THREADS / L.CW;
+  L.gridY = (L.CV + L.CW - 1) / L.CW;
+  int64_t want = (M + (int64_t)L.RY * 4 - 1) / ((int64_t)L.RY * 4);
+  int64_t cap = (int64_t)RN_NUM_SMS * waves / L.gridY;
+  if (cap < 1) cap = 1;
+  if (cap > BN_MAX_G) cap = BN_MAX_G;
+  L.G = (int)(want < 1 ? 1 : (want > cap ? cap : want));
+  return L;
+}
+
+// Reduce NV*2 per-thread accumulators over the rows of the CTA; thread (ty == 0) of each column
+// group ends up with the CTA total.  smem: [RY][CW][2*V] floats.
+template <int V>
+__device__ __forceinline__ void cta_reduce_cols(float (&a)[V], float (&b)[V], int tx, int ty, int CW, int RY,
+                                                bool active, float* smem) {
+  // warp-shuffle stage: when CW is a power of two below 32, lanes l and l ^ (CW*j) hold the
+  // same column group for different rows of the same warp.
+  const bool pow2 = (CW & (CW - 1)) == 0;
+  int rows_in_warp = 1;
+  if (pow2 && CW < 32) {
+    rows_in_warp = 32 / CW;
+    for (int o = 16; o >= CW; o >>= 1) {
+#pragma unroll
+      for (int i = 0; i < V; ++i) {
+        a[i] += __shfl_xor_sync(0xffffffffu, a[i], o);
+        b[i] += __shfl_xor_sync(0xffffffffu, b[i], o);
+      }
+    }
+  }
+  const bool writer = active && (ty % rows_in_warp == 0);
+  if (writer) {
+    float* p = smem + ((size_t)(ty / rows_in_warp) * CW + tx) * 2 * V;
+#pragma unroll
+    for (int i = 0; i < V; ++i) { p[i] = a[i]; p[V + i] = b[i]; }
+  }
+  __syncthreads();
+  if (active && ty == 0) {
+    const int nrow = (RY + rows_in_warp - 1) / rows_in_warp;
+    for (int r = 1; r < nrow; ++r) {
+      const float* p = smem + ((size_t)r * CW + tx) * 2 * V;
+#pragma unroll
+      for (int i = 0; i < V; ++i) { a[i] += p[i]; b[i] += p[V + i]; }
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// forward statistics (+ fused residual add)
+// ------------------------------------------------------------------------------------------
+template <typename T, bool ADD>
+__global__ void __launch_bounds__(BN_THREADS)
+bn_stats_kernel(const T* __restrict__ x, const T* __restrict__ addend, T* __restrict__ sum_out, int64_t M, int C,
+                BnLayout L, float eps, float decay, int unbiased, float* __restrict__ mean_out,
+                float* __restrict__ rstd_out, float* moving_mean, float* moving_var, unsigned* counters,
+                float* partials) {
+  constexpr int V = Vec<T>::N;
+  extern __shared__ float smem[];
+  const int tx = threadIdx.x % L.CW, ty = threadIdx.x / L.CW;
+  const int cg = blockIdx.y * L.CW + tx;
+  const bool active = ty < L.RY && cg < L.CV;
+  float s[V], q[V];
+#pragma unroll
+  for (int i = 0; i < V; ++i) { s[i] = 0.f; q[i] = 0.f; }
+  if (active) {
+    const int64_t stride = (int64_t)gridDim.x * L.RY;
+    for (int64_t r = (int64_t)blockIdx.x * L.RY + ty; r < M; r += stride) {
+      Vec<T> v;
+      float f[V];
+      const int64_t off = r * C + (int64_t)cg * V;
+      v.load(x + off);
+      v.unpack(f);
+      if (ADD) {
+        Vec<T> w;
+        float g[V];
+        w.load(addend + off);
+        w.unpack(g);
+#pragma unroll
+        for (int i = 0; i < V; ++i) f[i] += g[i];
+        Vec<T> o;
+        o.pack(f);
+        o.store(sum_out + off);
+        o.unpack(f);  // statistics of the value as stored (matters in bf16 mode)
+      }
+#pragma unroll
+      for (int i = 0; i < V; ++i) { s[i] += f[i]; q[i] = fmaf(f[i], f[i], q[i]); }
+    }
+  }
+  cta_reduce_cols<V>(s, q, tx, ty, L.CW, L.RY, active, smem);
+  const int chunkC = L.CW * V;
+  float* my = partials + ((size_t)blockIdx.y * gridDim.x + blockIdx.x) * 2 * chunkC;
+  if (active && ty == 0) {
+#pragma unroll
+    for (int i = 0; i < V; ++i) { my[tx * V + i] = s[i]; my[chunkC + tx * V + i] = q[i]; }
+  }
+  __shared__ bool is_last;
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    unsigned t = atomicAdd(&counters[blockIdx.y], 1u);
+    is_last = (t == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (!is_last) return;
+  __threadfence();
+  const int c_local = threadIdx.x;
+  const int c = blockIdx.y * chunkC + c_local;
+  if (c_local < chunkC && c < C) {
+    double S = 0.0, Q = 0.0;
+    const float* base = partials + (size_t)blockIdx.y * gridDim.x * 2 * chunkC;
+    for (unsigned b = 0; b < gridDim.x; ++b) {
+      S += (double)__ldcg(base + (size_t)b * 2 * chunkC + c_local);
+      Q += (double)__ldcg(base + (size_t)b * 2 * chunkC + chunkC + c_local);
+    }
+    const double mean = S / (double)M;
+    double var = Q / (double)M - mean * mean;
+    if (var < 0.0) var = 0.0;
+    mean_out[c] = (float)mean;
+    rstd_out[c] = (float)(1.0 / sqrt(var + (double)eps));
+    if (moving_mean != nullptr) {
+      const double mv = unbiased ? var * ((double)M / (double)(M > 1 ? M - 1 : 1)) : var;
+      const float om = 1.f - decay;
+      moving_mean[c] -= (moving_mean[c] - (float)mean) * om;
+      moving_var[c] -= (moving_var[c] - (float)mv) * om;
+    }
+  }
+  if (threadIdx.x == 0) counters[blockIdx.y] = 0;  // leave scratch clean for the next launch
+}
+
+// ------------------------------------------------------------------------------------------
+// forward apply + activation
+// ------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(BN_THREADS)
+bn_apply_kernel(const T* __restrict__ x, T* __restrict__ y, int64_t M, int C, BnLayout L,
+                const float* __restrict__ gamma, const float* __restrict__ beta, const float* __restrict__ mean,
+                const float* __restrict__ rstd, int stats_are_moving, float eps, float leak) {
+  constexpr int V = Vec<T>::N;
+  const int tx = threadIdx.x % L.CW, ty = threadIdx.x / L.CW;
+  const int cg = blockIdx.y * L.CW + tx;
+  if (!(ty < L.RY && cg < L.CV)) return;
+  float a[V], b[V];
+#pragma unroll
+  for (int i = 0; i < V; ++i) {
+    const int c = cg * V + i;
+    const float rs = stats_are_moving ? rsqrtf(rstd[c] + eps) : rstd[c];
+    a[i] = gamma[c] * rs;
+    b[i] = beta[c] - mean[c] * a[i];
+  }
+  const int64_t stride = (int64_t)gridDim.x * L.RY;
+  for (int64_t r = (int64_t)blockIdx.x * L.RY + ty; r < M; r += stride) {
+    const int64_t off = r * C + (int64_t)cg * V;
+    Vec<T> v;
+    float f[V];
+    v.load_stream(x + off);
+    v.unpack(f);
+#pragma unroll
+    for (int i = 0; i < V; ++i) f[i] = act_fn(fmaf(f[i], a[i], b[i]), leak);
+    v.pack(f);
+    v.store(y + off);
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// backward: reductions
+// ------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(BN_THREADS)
+bn_bwd_reduce_kernel(const T* __restrict__ dy, const T* __restrict__ x, int64_t M, int C, BnLayout L,
+                     const float* __restrict__ gamma, const float* __restrict__ beta, const float* __restrict__ mean,
+                     const float* __restrict__ rstd, float leak, float* __restrict__ dgamma, float* __restrict__ dbeta,
+                     unsigned* counters, float* partials) {
+  constexpr int V = Vec<T>::N;
+  extern __shared__ float smem[];
+  const int tx = threadIdx.x % L.CW, ty = threadIdx.x / L.CW;
+  const int cg = blockIdx.y * L.CW + tx;
+  const bool active = ty < L.RY && cg < L.CV;
+  float sb[V], sg[V], a[V], b[V], mu[V], rs[V];
+#pragma unroll
+  for (int i = 0; i < V; ++i) { sb[i] = 0.f; sg[i] = 0.f; }
+  if (active) {
+#pragma unroll
+    for (int i = 0; i < V; ++i) {
+      const int c = cg * V + i;
+      rs[i] = rstd[c];
+      mu[i] = mean[c];
+      a[i] = gamma[c] * rs[i];
+      b[i] = beta[c] - mu[i] * a[i];
+    }
+    const int64_t stride = (int64_t)gridDim.x * L.RY;
+    for (int64_t r = (int64_t)blockIdx.x * L.RY + ty; r < M; r += stride) {
+      const int64_t off = r * C + (int64_t)cg * V;
+      Vec<T> vx, vg;
+      float fx[V], fg[V];
+      vx.load(x + off);
+      vg.load(dy + off);
+      vx.unpack(fx);
+      vg.unpack(fg);
+#pragma unroll
+      for (int i = 0; i < V; ++i) {
+        const float pre = fmaf(fx[i], a[i], b[i]);
+        const float g = pre < 0.f ? leak * fg[i] : fg[i];
+        sb[i] += g;
+        sg[i] = fmaf(g, (fx[i] - mu[i]) * rs[i], sg[i]);
+      }
+    }
+  }
+  cta_reduce_cols<V>(sb, sg, tx, ty, L.CW, L.RY, active, smem);
+  const int chunkC = L.CW * V;
+  float* my = partials + ((size_t)blockIdx.y * gridDim.x + blockIdx.x) * 2 * chunkC;
+  if (active && ty == 0) {
+#pragma unroll
+    for (int i = 0; i < V; ++i) { my[tx * V + i] = sb[i]; my[chunkC + tx * V + i] = sg[i]; }
+  }
+  __shared__ bool is_last;
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    unsigned t = atomicAdd(&counters[blockIdx.y], 1u);
+    is_last = (t == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (!is_last) return;
+  __threadfence();
+  const int c_local = threadIdx.x;
+  const int c = blockIdx.y * chunkC + c_local;
+  if (c_local < chunkC && c < C) {
+    double B = 0.0, G = 0.0;
+    const float* base = partials + (size_t)blockIdx.y * gridDim.x * 2 * chunkC;
+    for (unsigned bb = 0; bb < gridDim.x; ++bb) {
+      B += (double)__ldcg(base + (size_t)bb * 2 * chunkC + c_local);
+      G += (double)__ldcg(base + (size_t)bb * 2 * chunkC + chunkC + c_local);
+    }
+    dbeta[c] = (float)B;
+    dgamma[c] = (float)G;
+  }
+  if (threadIdx.x == 0) counters[blockIdx.y] = 0;
+}
+
+// ------------------------------------------------------------------------------------------
+// backward: dx
+// ------------------------------------------------------------------------------------------
+template <typename T, bool ADD>
+__global__ void __launch_bounds__(BN_THREADS)
+bn_bwd_apply_kernel(const T* __restrict__ dy, const T* __restrict__ x, T* dx, const T* dx_addend, int64_t M, int C,
+                    BnLayout L, const float* __restrict__ gamma, const float* __restrict__ beta,
+                    const float* __restrict__ mean, const float* __restrict__ rstd, const float* __restrict__ dgamma,
+                    const float* __restrict__ dbeta, float leak) {
+  constexpr int V = Vec<T>::N;
+  const int tx = threadIdx.x % L.CW, ty = threadIdx.x / L.CW;
+  const int cg = blockIdx.y * L.CW + tx;
+  if (!(ty < L.RY && cg < L.CV)) return;
+  float a[V], b[V], mu[V], rs[V], k1[V], k2[V];
+  const float invM = 1.f / (float)M;
+#pragma unroll
+  for (int i = 0; i < V; ++i) {
+    const int c = cg * V + i;
+    rs[i] = rstd[c];
+    mu[i] = mean[c];
+    a[i] = gamma[c] * rs[i];
+    b[i] = beta[c] - mu[i] * a[i];
+    k1[i] = dbeta[c] * invM;
+    k2[i] = dgamma[c] * invM;
+  }
+  const int64_t stride = (int64_t)gridDim.x * L.RY;
+  for (int64_t r = (int64_t)blockIdx.x * L.RY + ty; r < M; r += stride) {
+    const int64_t off = r * C + (int64_t)cg * V;
+    Vec<T> vx, vg;
+    float fx[V], fg[V], fo[V];
+    vx.load_stream(x + off);
+    vg.load_stream(dy + off);
+    vx.unpack(fx);
+    vg.unpack(fg);
+    if (ADD) {
+      Vec<T> va;
+      va.load(dx_addend + off);
+      va.unpack(fo);
+    }
+#pragma unroll
+    for (int i = 0; i < V; ++i) {
+      const float pre = fmaf(fx[i], a[i], b[i]);
+      const float g = pre < 0.f ? leak * fg[i] : fg[i];
+      const float xhat = (fx[i] - mu[i]) * rs[i];
+      const float d = a[i] * (g - k1[i] - xhat * k2[i]);
+      fo[i] = ADD ? fo[i] + d : d;
+    }
+    Vec<T> vo;
+    vo.pack(fo);
+    vo.store(dx + off);
+  }
+}
+
+template <typename T>
+static int check_bn_args(int64_t M, int C) {
+  if (M <= 0 || C <= 0) return fail(RN_ERR_INVALID, "bn: M=%lld C=%d must be positive", (long long)M, C);
+  if (C % Vec<T>::N != 0) return fail(RN_ERR_UNSUPPORTED, "bn: C=%d must be a multiple of %d", C, Vec<T>::N);
+  if ((C / Vec<T>::N + 31) / 32 > BN_MAX_CHUNKS) return fail(RN_ERR_UNSUPPORTED, "bn: C=%d too large", C);
+  return RN_OK;
+}
+
+static size_t bn_scratch_bytes(int64_t M, int C) {
+  (void)M;
+  (void)C;
+  // 256 B of ticket counters + one [2][<=256 channels] fp32 partial per CTA; the layouts above
+  // never launch more than BN_MAX_G + BN_MAX_CHUNKS CTAs in total.
+  return 256 + (size_t)(BN_MAX_G + BN_MAX_CHUNKS) * 2 * 256 * sizeof(float);
+}
+
+template <typename T>
+static int bn_stats_launch(const void* x, const void* addend, void* sum_out, int64_t M, int C, float eps, float decay,
+                           int unbiased, float* mean, float* rstd, float* mm, float* mv, void* scratch,
+                           size_t scratch_bytes, cudaStream_t st) {
+  int rc = check_bn_args<T>(M, C);
+  if (rc) return rc;
+  BnLayout L = bn_layout<T>(M, C, 4);
+  const size_t need = 256 + (size_t)L.gridY * L.G * 2 * L.CW * Vec<T>::N * sizeof(float);
+  if (scratch == nullptr || scratch_bytes < need)
+    return fail(RN_ERR_SCRATCH, "bn_stats: scratch %zu < %zu bytes", scratch_bytes, need);
+  unsigned* counters = (unsigned*)scratch;
+  float* partials = (float*)((char*)scratch + 256);
+  dim3 grid(L.G, L.gridY);
+  size_t smem = (size_t)L.RY * L.CW * 2 * Vec<T>::N * sizeof(float);
+  if (addend != nullptr) {
+    RN_REQUIRE(sum_out != nullptr, "bn_stats: addend given but sum_out is NULL");
+    bn_stats_kernel<T, true><<<grid, BN_THREADS, smem, st>>>((const T*)x, (const T*)addend, (T*)sum_out, M, C, L, eps,
+                                                             decay, unbiased, mean, rstd, mm, mv, counters, partials);
+  } else {
+    bn_stats_kernel<T, false><<<grid, BN_THREADS, smem, st>>>((const T*)x, nullptr, nullptr, M, C, L, eps, decay,
+                                                              unbiased, mean, rstd, mm, mv, counters, partials);
+  }
+  return check_launch("bn_stats_kernel");
+}
+
+}  // namespace rn
+
+using namespace rn;
+
+extern "C" size_t rn_bn_scratch_bytes(int64_t M, int32_t C) { return bn_scratch_bytes(M, C); }
+
+extern "C" int rn_bn_stats_fwd(const void* x, const void* addend, void* sum_out, int64_t M, int32_t C, int32_t dtype,
+                               float eps, float decay, int32_t unbiased, float* mean, float* rstd, float* moving_mean,
+                               float* moving_var, void* scratch, size_t scratch_bytes, void* stream) {
+  RN_REQUIRE(x && mean && rstd, "bn_stats: NULL pointer");
+  RN_REQUIRE((moving_mean == nullptr) == (moving_var == nullptr), "bn_stats: moving_mean/var must both be set or NULL");
+  if (dtype == RN_F32)
+    return bn_stats_launch<float>(x, addend, sum_out, M, C, eps, decay, unbiased, mean, rstd, moving_mean, moving_var,
+                                  scratch, scratch_bytes, as_stream(stream));
+  if (dtype == RN_BF16)
+    return bn_stats_launch<__nv_bfloat16>(x, addend, sum_out, M, C, eps, decay, unbiased, mean, rstd, moving_mean,
+                                          moving_var, scratch, scratch_bytes, as_stream(stream));
+  return fail(RN_ERR_INVALID, "bn_stats: bad dtype %d", dtype);
+}
+
+template <typename T>
+static int bn_apply_launch(const void* x, void* y, int64_t M, int C, const float* gamma, const float* beta,
+                           const float* mean, const float* rstd, int moving, float eps, float leak, cudaStream_t st) {
+  int rc = check_bn_args<T>(M, C);
+  if (rc) return rc;
+  BnLayout L = bn_layout<T>(M, C, 8);
+  bn_apply_kernel<T><<<dim3(L.G, L.gridY), BN_THREADS, 0, st>>>((const T*)x, (T*)y, M, C, L, gamma, beta, mean, rstd,
+                                                               moving, eps, leak);
+  return check_launch("bn_apply_kernel");
+}
+
+extern "C" int rn_bn_apply_act_fwd(const void* x, void* y, int64_t M, int32_t C, int32_t dtype, const float* gamma,
+                                   const float* beta, const float* mean, const float* rstd, int32_t stats_are_moving,
+                                   float eps, float leak, void* stream) {
+  RN_REQUIRE(x && y && gamma && beta && mean && rstd, "bn_apply: NULL pointer");
+  if (dtype == RN_F32)
+    return bn_apply_launch<float>(x, y, M, C, gamma, beta, mean, rstd, stats_are_moving, eps, leak, as_stream(stream));
+  if (dtype == RN_BF16)
+    return bn_apply_launch<__nv_bfloat16>(x, y, M, C, gamma, beta, mean, rstd, stats_are_moving, eps, leak,
+                                          as_stream(stream));
+  return fail(RN_ERR_INVALID, "bn_apply: bad dtype %d", dtype);
+}
+
+template <typename T>
+static int bn_bwd_reduce_launch(const void* dy, const void* x, int64_t M, int C, const float* gamma, const float* beta,
+                                const float* mean, const float* rstd, float leak, float* dgamma, float* dbeta,
+                                void* scratch, size_t scratch_bytes, cudaStream_t st) {
+  int rc = check_bn_args<T>(M, C);
+  if (rc) return rc;
+  BnLayout L = bn_layout<T>(M, C, 4);
+  const size_t need = 256 + (size_t)L.gridY * L.G * 2 * L.CW * Vec<T>::N * sizeof(float);
+  if (scratch == nullptr || scratch_bytes < need)
+    return fail(RN_ERR_SCRATCH, "bn_bwd_reduce: scratch %zu < %zu bytes", scratch_bytes, need);
+  size_t smem = (size_t)L.RY * L.CW * 2 * Vec<T>::N * sizeof(float);
+  bn_bwd_reduce_kernel<T><<<dim3(L.G, L.gridY), BN_THREADS, smem, st>>>(
+      (const T*)dy, (const T*)x, M, C, L, gamma, beta, mean, rstd, leak, dgamma, dbeta, (unsigned*)scratch,
+      (float*)((char*)scratch + 256));
+  return check_launch("bn_bwd_reduce_kernel");
+}
+
+extern "C" int rn_bn_act_bwd_reduce(const void* dy, const void* x, int64_t M, int32_t C, int32_t dtype,
+                                    const float* gamma, const float* beta, const float* mean, const float* rstd,
+                                    float leak, float* dgamma, float* dbeta, void* scratch, size_t scratch_bytes,
+                                    void* stream) {
+  RN_REQUIRE(dy && x && gamma && beta && mean && rstd && dgamma && dbeta, "bn_bwd_reduce: NULL pointer");
+  if (dtype == RN_F32)
+    return bn_bwd_reduce_launch<float>(dy, x, M, C, gamma, beta, mean, rstd, leak, dgamma, dbeta, scratch,
+                                       scratch_bytes, as_stream(stream));
+  if (dtype == RN_BF16)
+    return bn_bwd_reduce_launch<__nv_bfloat16>(dy, x, M, C, gamma, beta, mean, rstd, leak, dgamma, dbeta, scratch,
+                                               scratch_bytes, as_stream(stream));
+  return fail(RN_ERR_INVALID, "bn_bwd_reduce: bad dtype %d", dtype);
+}
+
+template <typename T>
+static int bn_bwd_apply_launch(const void* dy, const void* x, void* dx, const void* addend, int64_t M, int C,
+                               const float* gamma, const float* beta, const float* mean, const float* rstd,
+                               const float* dgamma, const float* dbeta, float leak, cudaStream_t st) {
+  int rc = check_bn_args<T>(M, C);
+  if (rc) return rc;
+  BnLayout L = bn_layout<T>(M, C, 8);
+  dim3 grid(L.G, L.gridY);
+  if (addend)
+    bn_bwd_apply_kernel<T, true><<<grid, BN_THREADS, 0, st>>>((const T*)dy, (const T*)x, (T*)dx, (const T*)addend, M, C,
+                                                             L, gamma, beta, mean, rstd, dgamma, dbeta, leak);
+  else
+    bn_bwd_apply_kernel<T, false><<<grid, BN_THREADS, 0, st>>>((const T*)dy, (const T*)x, (T*)dx, nullptr, M, C, L,
+                                                              gamma, beta, mean, rstd, dgamma, dbeta, leak);
+  return check_launch("bn_bwd_apply_kernel");
+}
+
+extern "C" int rn_bn_act_bwd_apply(const void* dy, const void* x, void* dx, const void* dx_addend, int64_t M, int32_t C,
+                                   int32_t dtype, const float* gamma, const float* beta, const float* mean,
+                                   const float* rstd, const float* dgamma, const float* dbeta, float leak,
+                                   void* stream) {
+  RN_REQUIRE(dy && x && dx && gamma && beta && mean && rstd && dgamma && dbeta, "bn_bwd_apply: NULL pointer");
+  if (dtype == RN_F32)
+    return bn_bwd_apply_launch<float>(dy, x, dx, dx_addend, M, C, gamma, beta, mean, rstd, dgamma, dbeta, leak,
+                                      as_stream(stream));
+  if (dtype == RN_BF16)
+    return bn_bwd_apply_launch<__nv_bfloat16>(dy, x, dx, dx_addend, M, C, gamma, beta, mean, rstd, dgamma, dbeta, leak,
+                                              as_stream(stream));
+  return fail(RN_ERR_INVALID, "bn_bwd_apply: bad dtype %d", dtype);
+}

@@ -1,0 +1,194 @@
+// Pooling kernels (HBM-bound, NHWC; one thread per output/input element, channels fastest so
+// every warp touches contiguous memory).
+#include "rn_common.cuh"
+
+namespace rn {
+
+// 3x3 stride-2 max pool.  Padding cells never win (TF pads with -inf).  The first maximum in
+// row-major window order wins ties; its window position (0..8) is kept for the backward pass.
+template <typename T>
+__global__ void maxpool_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, uint8_t* __restrict__ argmax, int N,
+                                   int H, int W, int C, int Ho, int Wo, int pad) {
+  const int64_t total = (int64_t)N * Ho * Wo * C;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int c = (int)(i % C);
+    int64_t p = i / C;
+    const int wo = (int)(p % Wo);
+    p /= Wo;
+    const int ho = (int)(p % Ho);
+    const int n = (int)(p / Ho);
+    float best = -INFINITY;
+    int bi = 0;
+    bool any = false;
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+      const int h = ho * 2 - pad + r;
+      if (h < 0 || h >= H) continue;
+#pragma unroll
+      for (int s = 0; s < 3; ++s) {
+        const int w = wo * 2 - pad + s;
+        if (w < 0 || w >= W) continue;
+        const float v = to_f<T>(x[(((int64_t)n * H + h) * W + w) * C + c]);
+        if (!any || v > best) { best = v; bi = r * 3 + s; any = true; }
+      }
+    }
+    y[i] = from_f<T>(best);
+    argmax[i] = (uint8_t)bi;
+  }
+}
+
+// Gather form of MaxPoolGrad: every input element sums the gradients of the (at most 2x2)
+// windows whose recorded argmax points at it.  No atomics, deterministic.
+template <typename T>
+__global__ void maxpool_bwd_kernel(const T* __restrict__ dy, const uint8_t* __restrict__ argmax, T* dx, int N, int H,
+                                   int W, int C, int Ho, int Wo, int pad, float beta) {
+  const int64_t total = (int64_t)N * H * W * C;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int c = (int)(i % C);
+    int64_t p = i / C;
+    const int w = (int)(p % W);
+    p /= W;
+    const int h = (int)(p % H);
+    const int n = (int)(p / H);
+    float acc = 0.f;
+    // windows with ho*2 - pad + r == h, r in [0,3)
+    for (int r = 0; r < 3; ++r) {
+      const int t = h + pad - r;
+      if (t < 0 || (t & 1)) continue;
+      const int ho = t >> 1;
+      if (ho >= Ho) continue;
+      for (int s = 0; s < 3; ++s) {
+        const int u = w + pad - s;
+        if (u < 0 || (u & 1)) continue;
+        const int wo = u >> 1;
+        if (wo >= Wo) continue;
+        const int64_t o = (((int64_t)n * Ho + ho) * Wo + wo) * C + c;
+        if (argmax[o] == (uint8_t)(r * 3 + s)) acc += to_f<T>(dy[o]);
+      }
+    }
+    dx[i] = from_f<T>(beta != 0.f ? to_f<T>(dx[i]) + acc : acc);
+  }
+}
+
+template <typename TI, typename TO>
+__global__ void avgpool_fwd_kernel(const TI* __restrict__ x, TO* __restrict__ y, int N, int H, int W, int C, int k,
+                                   int s, int Ho, int Wo, int Cout, int cb) {
+  const int64_t total = (int64_t)N * Ho * Wo * Cout;
+  const float inv = 1.f / (float)(k * k);
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int co = (int)(i % Cout);
+    int64_t p = i / Cout;
+    const int wo = (int)(p % Wo);
+    p /= Wo;
+    const int ho = (int)(p % Ho);
+    const int n = (int)(p / Ho);
+    const int c = co - cb;
+    float acc = 0.f;
+    if (c >= 0 && c < C) {
+      for (int r = 0; r < k; ++r)
+        for (int q = 0; q < k; ++q)
+          acc += to_f<TI>(x[(((int64_t)n * H + ho * s + r) * W + wo * s + q) * C + c]);
+      acc *= inv;
+    }
+    y[i] = from_f<TO>(acc);
+  }
+}
+
+template <typename TI, typename TO>
+__global__ void avgpool_bwd_kernel(const TO* __restrict__ dy, TI* dx, int N, int H, int W, int C, int k, int s, int Ho,
+                                   int Wo, int Cout, int cb, float beta) {
+  const int64_t total = (int64_t)N * H * W * C;
+  const float inv = 1.f / (float)(k * k);
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int c = (int)(i % C);
+    int64_t p = i / C;
+    const int w = (int)(p % W);
+    p /= W;
+    const int h = (int)(p % H);
+    const int n = (int)(p / H);
+    float acc = 0.f;
+    // windows (ho, wo) with ho*s <= h < ho*s + k
+    const int ho_lo = h - k + 1 <= 0 ? 0 : (h - k + 1 + s - 1) / s;
+    const int wo_lo = w - k + 1 <= 0 ? 0 : (w - k + 1 + s - 1) / s;
+    for (int ho = ho_lo; ho < Ho && ho * s <= h; ++ho)
+      for (int wo = wo_lo; wo < Wo && wo * s <= w; ++wo)
+        acc += to_f<TO>(dy[(((int64_t)n * Ho + ho) * Wo + wo) * Cout + cb + c]);
+    acc *= inv;
+    dx[i] = from_f<TI>(beta != 0.f ? to_f<TI>(dx[i]) + acc : acc);
+  }
+}
+
+}  // namespace rn
+using namespace rn;
+
+extern "C" int rn_maxpool3x3s2_fwd(const void* x, void* y, uint8_t* argmax, int32_t N, int32_t H, int32_t W, int32_t C,
+                                   int32_t Ho, int32_t Wo, int32_t pad, int32_t dtype, void* stream) {
+  RN_REQUIRE(x && y && argmax && N > 0 && H > 0 && W > 0 && C > 0 && Ho > 0 && Wo > 0 && pad >= 0 && pad <= 2,
+             "maxpool_fwd: bad arguments");
+  RN_REQUIRE((Ho - 1) * 2 - pad < H && (Wo - 1) * 2 - pad < W, "maxpool_fwd: empty window");
+  const int g = grid_for((int64_t)N * Ho * Wo * C, 256);
+  if (dtype == RN_F32)
+    maxpool_fwd_kernel<float><<<g, 256, 0, as_stream(stream)>>>((const float*)x, (float*)y, argmax, N, H, W, C, Ho, Wo, pad);
+  else if (dtype == RN_BF16)
+    maxpool_fwd_kernel<__nv_bfloat16><<<g, 256, 0, as_stream(stream)>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)y,
+                                                                        argmax, N, H, W, C, Ho, Wo, pad);
+  else
+    return fail(RN_ERR_INVALID, "maxpool_fwd: bad dtype %d", dtype);
+  return check_launch("maxpool_fwd_kernel");
+}
+
+extern "C" int rn_maxpool3x3s2_bwd(const void* dy, const uint8_t* argmax, void* dx, int32_t N, int32_t H, int32_t W,
+                                   int32_t C, int32_t Ho, int32_t Wo, int32_t pad, int32_t dtype, float beta,
+                                   void* stream) {
+  RN_REQUIRE(dy && dx && argmax && N > 0 && H > 0 && W > 0 && C > 0 && Ho > 0 && Wo > 0, "maxpool_bwd: bad arguments");
+  const int g = grid_for((int64_t)N * H * W * C, 256);
+  if (dtype == RN_F32)
+    maxpool_bwd_kernel<float><<<g, 256, 0, as_stream(stream)>>>((const float*)dy, argmax, (float*)dx, N, H, W, C, Ho, Wo,
+                                                                pad, beta);
+  else if (dtype == RN_BF16)
+    maxpool_bwd_kernel<__nv_bfloat16><<<g, 256, 0, as_stream(stream)>>>((const __nv_bfloat16*)dy, argmax,
+                                                                        (__nv_bfloat16*)dx, N, H, W, C, Ho, Wo, pad, beta);
+  else
+    return fail(RN_ERR_INVALID, "maxpool_bwd: bad dtype %d", dtype);
+  return check_launch("maxpool_bwd_kernel");
+}
+
+extern "C" int rn_avgpool_fwd(const void* x, void* y, int32_t N, int32_t H, int32_t W, int32_t C, int32_t k, int32_t s,
+                              int32_t Cout, int32_t cb, int32_t idt, int32_t odt, void* stream) {
+  RN_REQUIRE(x && y && N > 0 && C > 0 && k > 0 && s > 0 && H >= k && W >= k && cb >= 0 && Cout >= C + cb,
+             "avgpool_fwd: bad arguments");
+  const int Ho = (H - k) / s + 1, Wo = (W - k) / s + 1;
+  const int g = grid_for((int64_t)N * Ho * Wo * Cout, 256);
+  cudaStream_t st = as_stream(stream);
+  if (idt == RN_F32 && odt == RN_F32)
+    avgpool_fwd_kernel<float, float><<<g, 256, 0, st>>>((const float*)x, (float*)y, N, H, W, C, k, s, Ho, Wo, Cout, cb);
+  else if (idt == RN_BF16 && odt == RN_F32)
+    avgpool_fwd_kernel<__nv_bfloat16, float><<<g, 256, 0, st>>>((const __nv_bfloat16*)x, (float*)y, N, H, W, C, k, s, Ho,
+                                                               Wo, Cout, cb);
+  else if (idt == RN_BF16 && odt == RN_BF16)
+    avgpool_fwd_kernel<__nv_bfloat16, __nv_bfloat16><<<g, 256, 0, st>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)y, N, H,
+                                                                       W, C, k, s, Ho, Wo, Cout, cb);
+  else
+    return fail(RN_ERR_INVALID, "avgpool_fwd: bad dtypes %d -> %d", idt, odt);
+  return check_launch("avgpool_fwd_kernel");
+}
+
+extern "C" int rn_avgpool_bwd(const void* dy, void* dx, int32_t N, int32_t H, int32_t W, int32_t C, int32_t k, int32_t s,
+                              int32_t Cout, int32_t cb, int32_t idt, int32_t odt, float beta, void* stream) {
+  RN_REQUIRE(dy && dx && N > 0 && C > 0 && k > 0 && s > 0 && H >= k && W >= k && cb >= 0 && Cout >= C + cb,
+             "avgpool_bwd: bad arguments");
+  const int Ho = (H - k) / s + 1, Wo = (W - k) / s + 1;
+  const int g = grid_for((int64_t)N * H * W * C, 256);
+  cudaStream_t st = as_stream(stream);
+  if (idt == RN_F32 && odt == RN_F32)
+    avgpool_bwd_kernel<float, float><<<g, 256, 0, st>>>((const float*)dy, (float*)dx, N, H, W, C, k, s, Ho, Wo, Cout, cb, beta);
+  else if (idt == RN_BF16 && odt == RN_F32)
+    avgpool_bwd_kernel<__nv_bfloat16, float><<<g, 256, 0, st>>>((const float*)dy, (__nv_bfloat16*)dx, N, H, W, C, k, s,
+                                                               Ho, Wo, Cout, cb, beta);
+  else if (idt == RN_BF16 && odt == RN_BF16)
+    avgpool_bwd_kernel<__nv_bfloat16, __nv_bfloat16><<<g, 256, 0, st>>>((const __nv_bfloat16*)dy, (__nv_bfloat16*)dx, N,
+                                                                       H, W, C, k, s, Ho, Wo, Cout, cb, beta);
+  else
+    return fail(RN_ERR_INVALID, "avgpool_bwd: bad dtypes %d -> %d", idt, odt);
+  return check_launch("avgpool_bwd_kernel");
+}

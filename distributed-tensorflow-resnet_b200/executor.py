@@ -1,0 +1,704 @@
+"""Static executor: turns a `graph.Graph` into flat HBM buffers and an ordered list of CUDA
+kernel launches (forward, backward, aggregation, optimizer) through the C ABI of librn_b200.so.
+
+PyTorch is only the shell here: `torch.empty` for device memory, `data_ptr()` for addresses,
+`torch.cuda.current_stream()` for the stream handle, `torch.cuda.CUDAGraph` to replay the launch
+list, and `torch.distributed` (NCCL) for the gradient all-reduce.  No torch operator computes
+anything on the hot path, and there is no CPU fallback.
+
+HBM layout
+  W   fp32 [n]   all trainable variables, TF creation order, each start aligned to 64 elements
+  G   fp32 [n]   gradients, same offsets (the fusion buffer that is all-reduced, SUM over ranks)
+  Mom fp32 [n]   momentum slots, same offsets
+  Wb  bf16 [n]   bf16 copy of W (bf16 mode), same offsets, refreshed by the optimizer kernel
+  S   fp32       non-trainable state: BN moving_mean / moving_variance
+  per-BN saved batch mean / rstd, activations (NHWC) and their gradients: one buffer each.
+"""
+import ctypes as C
+import math
+from collections import OrderedDict
+
+import numpy as np
+import torch
+
+from . import graph as G
+from . import _lib
+from ._lib import lib, check, ptr, ConvDesc, RN_F32, RN_BF16
+
+GRANULE = 64
+
+
+def _align(n, a):
+    return (n + a - 1) // a * a
+
+
+def init_variable(var, gen):
+    """Initialisers pinned by the training-graph fixture (tests/golden/cifar50_train_graph.json):
+    conv kernels truncated normal (2 sigma) with stddev sqrt(1/fan_in)/0.8796; dense kernel
+    Glorot uniform; gamma / moving_variance ones; the rest zeros.  Upstream builders use
+    random_normal / uniform_unit_scaling."""
+    k = var.init["kind"]
+    if k == "zeros":
+        return torch.zeros(var.shape, dtype=torch.float32)
+    if k == "ones":
+        return torch.ones(var.shape, dtype=torch.float32)
+    if k == "truncated_normal":
+        std = var.init["stddev"]
+        t = torch.empty(var.shape, dtype=torch.float32)
+        torch.nn.init.trunc_normal_(t, 0.0, std, -2 * std, 2 * std, generator=gen)
+        return t
+    if k == "normal":
+        return torch.randn(var.shape, dtype=torch.float32, generator=gen) * var.init["stddev"]
+    if k == "uniform":
+        lim = var.init["limit"]
+        return (torch.rand(var.shape, dtype=torch.float32, generator=gen) * 2 - 1) * lim
+    raise ValueError("unknown initialiser %r" % k)
+
+
+class _Slot:
+    """A gradient buffer, possibly shared by several tensors (the residual-stream gradient)."""
+
+    def __init__(self, buf):
+        self.buf = buf
+        self.written = False
+        self.members = []
+
+
+class Executor:
+    def __init__(self, graph, *, device=None, dtype="bf16", weight_decay=0.0, optimizer="mom", momentum=0.9,
+                 lrn_rate=0.1, train=True, seed=0, process_group=None, world_size=1, rank=0,
+                 bucket_bytes=32 << 20, use_tensor_cores=True, loss=None, init_values=None):
+        if not torch.cuda.is_available():
+            raise _lib.RnError("no CUDA device: this framework has no CPU path")
+        self.g = graph
+        self.dev = torch.device(device if device is not None else "cuda:%d" % torch.cuda.current_device())
+        self.bf16 = dtype in ("bf16", torch.bfloat16)
+        self.adt = torch.bfloat16 if self.bf16 else torch.float32
+        self.rn_dt = RN_BF16 if self.bf16 else RN_F32
+        self.wd = float(weight_decay)
+        self.opt_kind = optimizer
+        if optimizer not in ("sgd", "mom"):
+            raise ValueError("optimizer must be 'sgd' or 'mom'")
+        self.momentum = float(momentum)
+        self.train = train
+        self.pg = process_group
+        self.world = int(world_size)
+        self.rank = int(rank)
+        self.use_tc = bool(use_tensor_cores) and self.bf16
+        self.loss = loss   # (probs, scalars) tensors from graph.softmax_xent
+        self.global_step = 0
+        self.launches_per_step = 0
+        self._graph_exec = None
+        self._plans = []
+        self._keep = []
+        self._layout(seed, init_values)
+        self._alloc_activations()
+        self._build_forward()
+        if train:
+            self._build_backward()
+            self._build_update(bucket_bytes)
+        self.set_lr(lrn_rate)
+        if self.world > 1:
+            self.broadcast_from_rank0()
+
+    # ------------------------------------------------------------------ parameters
+    def _layout(self, seed, init_values):
+        tv = self.g.trainable_variables()
+        off = 0
+        for v in tv:
+            v.offset = off
+            off += _align(v.size, GRANULE)
+        self.n_flat = max(off, GRANULE)
+        sv = [v for v in self.g.variables.values() if not v.trainable]
+        soff = 0
+        for v in sv:
+            v.offset = soff
+            soff += _align(v.size, 4)
+        dev = self.dev
+        self.W = torch.zeros(self.n_flat, dtype=torch.float32, device=dev)
+        self.S = torch.zeros(max(soff, 4), dtype=torch.float32, device=dev)
+        self.Wb = torch.zeros(self.n_flat, dtype=torch.bfloat16, device=dev) if self.bf16 else None
+        if self.train:
+            self.Gd = torch.zeros(self.n_flat, dtype=torch.float32, device=dev)
+            self.Mom = torch.zeros(self.n_flat, dtype=torch.float32, device=dev)
+        mask = np.zeros(self.n_flat // GRANULE, dtype=np.uint8)
+        gen = torch.Generator().manual_seed(seed)
+        hostW = torch.zeros(self.n_flat, dtype=torch.float32)
+        hostS = torch.zeros(self.S.numel(), dtype=torch.float32)
+        for v in self.g.variables.values():
+            if init_values is not None and v.name in init_values:
+                val = torch.as_tensor(np.asarray(init_values[v.name]), dtype=torch.float32).reshape(v.shape)
+            else:
+                val = init_variable(v, gen)
+            if v.trainable:
+                hostW[v.offset:v.offset + v.size] = val.reshape(-1)
+                if v.decay:
+                    mask[v.offset // GRANULE:(v.offset + _align(v.size, GRANULE)) // GRANULE] = 1
+            else:
+                hostS[v.offset:v.offset + v.size] = val.reshape(-1)
+        self.W.copy_(hostW)
+        self.S.copy_(hostS)
+        if self.Wb is not None:
+            self.Wb.copy_(hostW.to(torch.bfloat16))   # set-up only; per step the optimizer kernel refreshes it
+        self.all_decay = bool(mask.all())
+        self.mask = None if self.all_decay else torch.from_numpy(mask).to(dev)
+        self.hyper = torch.zeros(4, dtype=torch.float32, device=dev)
+        self._hyper_host = torch.zeros(4, dtype=torch.float32).pin_memory()
+        self.sumsq = torch.zeros(1, dtype=torch.float32, device=dev)
+        nbytes = max(lib.rn_bn_scratch_bytes(1, 8), lib.rn_optimizer_scratch_bytes(self.n_flat))
+        self.scratch = torch.zeros(nbytes, dtype=torch.uint8, device=dev)     # ticket counters start at 0
+        self.scratch_bytes = nbytes
+
+    def var_view(self, name, which="W"):
+        v = self.g.variables[name]
+        base = {"W": self.W, "G": getattr(self, "Gd", None), "M": getattr(self, "Mom", None), "S": self.S}[
+            which if v.trainable else "S"]
+        return base[v.offset:v.offset + v.size].view(v.shape)
+
+    def _wptr(self, v, which="W"):
+        base = {"W": self.W, "G": getattr(self, "Gd", None), "S": self.S, "Wb": self.Wb}[which]
+        return base.data_ptr() + v.offset * base.element_size()
+
+    def state_dict(self):
+        """All variables by TF name (weights, BN moving stats) + momentum slots + global_step."""
+        out = OrderedDict()
+        for v in self.g.variables.values():
+            out[v.name] = self.var_view(v.name).detach().cpu().numpy().copy()
+            if v.trainable and self.train:
+                out[v.name + "/Momentum"] = self.var_view(v.name, "M").detach().cpu().numpy().copy()
+        out["global_step"] = np.int64(self.global_step)
+        return out
+
+    def load_state_dict(self, sd):
+        for v in self.g.variables.values():
+            if v.name in sd:
+                self.var_view(v.name).copy_(torch.as_tensor(np.asarray(sd[v.name]), dtype=torch.float32).reshape(v.shape))
+            if v.trainable and self.train and v.name + "/Momentum" in sd:
+                self.var_view(v.name, "M").copy_(torch.as_tensor(np.asarray(sd[v.name + "/Momentum"]),
+                                                                 dtype=torch.float32).reshape(v.shape))
+        if "global_step" in sd:
+            self.global_step = int(sd["global_step"])
+        self.refresh_shadow_weights()
+
+    def refresh_shadow_weights(self):
+        """Rebuild the bf16 operand copies from W (set-up / checkpoint restore only)."""
+        st = torch.cuda.current_stream().cuda_stream
+        if self.Wb is not None:
+            check(lib.rn_cast(ptr(self.W), ptr(self.Wb), self.n_flat, RN_F32, RN_BF16, st), "rn_cast")
+        for fn in getattr(self, "_relayout", []):
+            fn(st)
+
+    # ------------------------------------------------------------------ activations
+    def _alloc_activations(self):
+        for t in self.g.tensors.values():
+            dt = self.adt if t.dtype == G.ACT else torch.float32
+            bound = getattr(t, "bound", None)
+            if bound is not None and bound.dtype == dt and bound.is_contiguous() and bound.device == self.dev:
+                t.buf = bound
+                t.cast_from = None
+            else:
+                t.buf = torch.zeros(t.shape, dtype=dt, device=self.dev)
+                t.cast_from = bound
+        # requires_grad propagation
+        for t in self.g.tensors.values():
+            t.requires_grad = False
+        for n in self.g.nodes:
+            rg = any(v.trainable for v in n.vars.values()) or any(t.requires_grad for t in n.inputs)
+            for t in n.outputs:
+                t.requires_grad = rg
+
+    # ------------------------------------------------------------------ forward
+    def _desc(self, n):
+        x, y = n.inputs[0], n.outputs[0]
+        N, H, W, Cin = x.shape
+        _, Ho, Wo, Cout = y.shape
+        return ConvDesc(N, H, W, Cin, Ho, Wo, Cout, n.attrs["k"], n.attrs["stride"], n.attrs["pad"], self.rn_dt)
+
+    def _fused_add_for(self, bn_node):
+        """The `add` node whose output this training-mode BN normalises, if the add can be folded
+        into the statistics pass (BN must be the first reader of the sum)."""
+        x = bn_node.inputs[0]
+        p = x.producer
+        if p is not None and p.op == "add" and bn_node.attrs["is_training"] and x.consumers and x.consumers[0] is bn_node:
+            return p
+        return None
+
+    def _build_forward(self):
+        fwd = []
+        g = self.g
+        self._saved = {}
+        fused_adds = set()
+        for n in g.nodes:
+            if n.op == "bn_act":
+                a = self._fused_add_for(n)
+                if a is not None:
+                    fused_adds.add(id(a))
+        self._fused_adds = fused_adds
+        for t in g.placeholders.values():
+            src = getattr(t, "cast_from", None)
+            if src is not None:
+                sdt = RN_BF16 if src.dtype == torch.bfloat16 else RN_F32
+                ddt = RN_BF16 if t.buf.dtype == torch.bfloat16 else RN_F32
+                if src.dtype not in (torch.float32, torch.bfloat16):
+                    raise ValueError("placeholder %s: unsupported dtype %s" % (t.name, src.dtype))
+                fwd.append(("cast:" + t.name, lambda s, a=ptr(src), b=ptr(t.buf), k=t.numel, sd=sdt, dd=ddt:
+                            check(lib.rn_cast(a, b, k, sd, dd, s), "rn_cast")))
+                self._keep.append(src)
+        for n in g.nodes:
+            if n.op == "conv2d":
+                fwd.append(self._conv_fprop(n))
+            elif n.op == "bn_act":
+                fwd.extend(self._bn_fwd(n))
+            elif n.op == "add":
+                if id(n) in fused_adds:
+                    continue
+                a, b = n.inputs
+                y = n.outputs[0]
+                dt = RN_BF16 if y.buf.dtype == torch.bfloat16 else RN_F32
+                fwd.append(("add:" + y.name, lambda s, pa=ptr(a.buf), pb=ptr(b.buf), py=ptr(y.buf), k=y.numel, dt=dt:
+                            check(lib.rn_add(pa, pb, py, k, dt, s), "rn_add")))
+            elif n.op == "maxpool":
+                x, y = n.inputs[0], n.outputs[0]
+                n.argmax = torch.zeros(y.shape, dtype=torch.uint8, device=self.dev)
+                N, H, W, Cc = x.shape
+                fwd.append(("maxpool:" + y.name,
+                            lambda s, px=ptr(x.buf), py=ptr(y.buf), pa=ptr(n.argmax), d=(N, H, W, Cc, y.shape[1], y.shape[2], n.attrs["pad"]):
+                            check(lib.rn_maxpool3x3s2_fwd(px, py, pa, *d, self.rn_dt, s), "rn_maxpool3x3s2_fwd")))
+            elif n.op == "avgpool":
+                x, y = n.inputs[0], n.outputs[0]
+                N, H, W, Cc = x.shape
+                idt = RN_BF16 if x.buf.dtype == torch.bfloat16 else RN_F32
+                odt = RN_BF16 if y.buf.dtype == torch.bfloat16 else RN_F32
+                fwd.append(("avgpool:" + y.name,
+                            lambda s, px=ptr(x.buf), py=ptr(y.buf), d=(N, H, W, Cc, n.attrs["k"], n.attrs["s"], y.shape[3], n.attrs["c_before"], idt, odt):
+                            check(lib.rn_avgpool_fwd(px, py, *d, s), "rn_avgpool_fwd")))
+            elif n.op == "dense":
+                x, y = n.inputs[0], n.outputs[0]
+                if x.buf.dtype != torch.float32:
+                    raise ValueError("dense expects fp32 features (use avg_pool(out_dtype=F32))")
+                B = x.shape[0]
+                D = x.numel // B
+                K = y.shape[1]
+                fwd.append(("dense:" + y.name,
+                            lambda s, px=ptr(x.buf), pw=self._wptr(n.vars["kernel"]), pb=self._wptr(n.vars["bias"]), py=ptr(y.buf), d=(B, D, K):
+                            check(lib.rn_dense_fwd(px, pw, pb, py, *d, s), "rn_dense_fwd")))
+            elif n.op == "softmax_xent":
+                logits, labels = n.inputs
+                probs, scal = n.outputs
+                B, K = logits.shape
+                if self.train and logits.requires_grad:
+                    n.dlogits = torch.zeros(logits.shape, dtype=torch.float32, device=self.dev)
+                else:
+                    n.dlogits = None
+                fwd.append(("softmax_xent",
+                            lambda s, pl=ptr(logits.buf), py=ptr(labels.buf), pp=ptr(probs.buf), pd=ptr(n.dlogits), ps=ptr(scal.buf), d=(B, K):
+                            check(lib.rn_softmax_xent(pl, py, d[0], d[1], pp, pd, ps, s), "rn_softmax_xent")))
+            else:
+                raise ValueError("unknown op " + n.op)
+        self.fwd = fwd
+
+    def _conv_impl(self, n, kind):
+        d = self._desc(n)
+        if self.use_tc and lib.rn_convtc_supported(C.byref(d), kind):
+            return "tc"
+        return "simt"
+
+    def _conv_fprop(self, n):
+        x, y = n.inputs[0], n.outputs[0]
+        d = self._desc(n)
+        self._keep.append(d)
+        kv = n.vars["kernel"]
+        if self._conv_impl(n, 0) == "tc":
+            return ("conv_fprop_tc:" + y.name, self._tc_plan(n, d, 0, x.buf, y.buf))
+        w = self._wptr(kv, "Wb" if self.bf16 else "W")
+        return ("conv_fprop:" + y.name, lambda s, d=d, px=ptr(x.buf), py=ptr(y.buf), w=w:
+                check(lib.rn_conv2d_fprop(C.byref(d), px, w, py, s), "rn_conv2d_fprop"))
+
+    # tensor-core plans -------------------------------------------------------------------
+    def _tc_weights(self, n):
+        """bf16 operand layouts of one conv kernel for the tcgen05 path, refreshed after every
+        optimizer step by rn_weights_to_bf16."""
+        if not hasattr(n, "_tcw"):
+            kv = n.vars["kernel"]
+            k, _, Cin, Cout = kv.shape
+            wf = torch.zeros(k * k * Cout * Cin, dtype=torch.bfloat16, device=self.dev)
+            wd = torch.zeros(k * k * Cin * Cout, dtype=torch.bfloat16, device=self.dev)
+            n._tcw = (wf, wd)
+            fn = (lambda s, pw=self._wptr(kv), k=k, ci=Cin, co=Cout, a=ptr(wf), b=ptr(wd):
+                  check(lib.rn_weights_to_bf16(pw, k, ci, co, a, b, s), "rn_weights_to_bf16"))
+            if not hasattr(self, "_relayout"):
+                self._relayout = []
+            self._relayout.append(fn)
+            fn(torch.cuda.current_stream().cuda_stream)
+        return n._tcw
+
+    def _tc_plan(self, n, d, kind, a_buf, out_ptr_or_buf, b_buf=None):
+        wf, wd = self._tc_weights(n)
+        if kind == 0:
+            b = wf
+        elif kind == 1:
+            b = wd
+        else:
+            b = b_buf
+        nbytes = lib.rn_convtc_scratch_bytes(C.byref(d), kind)
+        scratch = torch.zeros(max(nbytes, 16), dtype=torch.uint8, device=self.dev)
+        self._keep.append(scratch)
+        plan = C.c_void_p()
+        outp = out_ptr_or_buf if isinstance(out_ptr_or_buf, int) else ptr(out_ptr_or_buf)
+        check(lib.rn_convtc_plan_create(C.byref(d), kind, ptr(a_buf), ptr(b), outp, ptr(scratch), nbytes,
+                                        C.byref(plan)), "rn_convtc_plan_create")
+        self._plans.append(plan)
+        return lambda s, p=plan, beta=0.0: check(lib.rn_convtc_run(p, beta, s), "rn_convtc_run")
+
+    def _bn_fwd(self, n):
+        x, y = n.inputs[0], n.outputs[0]
+        C_ = x.shape[-1]
+        M = x.numel // C_
+        a = n.attrs
+        v = n.vars
+        out = []
+        if a["is_training"]:
+            saved = torch.zeros(2, C_, dtype=torch.float32, device=self.dev)
+            n.saved = saved
+            mean_p, rstd_p = saved[0].data_ptr(), saved[1].data_ptr()
+            add = self._fused_add_for(n)
+            if add is not None:
+                px, pa, pz = ptr(add.inputs[0].buf), ptr(add.inputs[1].buf), ptr(x.buf)
+            else:
+                px, pa, pz = ptr(x.buf), None, None
+            mm, mv = self._wptr(v["moving_mean"], "S"), self._wptr(v["moving_variance"], "S")
+            if not self.train:
+                mm = mv = None       # forward-only with batch statistics: leave moving stats alone
+            out.append(("bn_stats:" + a["scope"],
+                        lambda s, args=(px, pa, pz, M, C_, self.rn_dt, a["eps"], a["decay"], int(a["unbiased"]), mean_p, rstd_p, mm, mv):
+                        check(lib.rn_bn_stats_fwd(*args, ptr(self.scratch), self.scratch_bytes, s), "rn_bn_stats_fwd")))
+            out.append(("bn_apply:" + a["scope"],
+                        lambda s, args=(ptr(x.buf), ptr(y.buf), M, C_, self.rn_dt, self._wptr(v["gamma"]), self._wptr(v["beta"]), mean_p, rstd_p, 0, a["eps"], a["leak"]):
+                        check(lib.rn_bn_apply_act_fwd(*args, s), "rn_bn_apply_act_fwd")))
+        else:
+            out.append(("bn_infer:" + a["scope"],
+                        lambda s, args=(ptr(x.buf), ptr(y.buf), M, C_, self.rn_dt, self._wptr(v["gamma"]), self._wptr(v["beta"]),
+                                        self._wptr(v["moving_mean"], "S"), self._wptr(v["moving_variance"], "S"), 1, a["eps"], a["leak"]):
+                        check(lib.rn_bn_apply_act_fwd(*args, s), "rn_bn_apply_act_fwd")))
+        return out
+
+    # ------------------------------------------------------------------ backward
+    def _slot_of(self, t):
+        return getattr(t, "gradslot", None)
+
+    def _new_slot(self, t):
+        s = _Slot(torch.zeros(t.shape, dtype=t.buf.dtype, device=self.dev))
+        s.members.append(t)
+        t.gradslot = s
+        return s
+
+    def _safe_inplace(self, t, slot, done):
+        return all((m is t) or (m.producer is None) or (id(m.producer) in done) for m in slot.members)
+
+    def _target(self, t, done, bwd):
+        """Where a backward kernel must put d(loss)/d(t): returns (buffer, beta)."""
+        s = self._slot_of(t)
+        if s is None:
+            s = self._new_slot(t)
+        if not s.written:
+            s.written = True
+            return s.buf, 0.0
+        if not self._safe_inplace(t, s, done):
+            # another reader of the shared buffer has not run yet: give t a private copy
+            ns = _Slot(torch.zeros(t.shape, dtype=t.buf.dtype, device=self.dev))
+            ns.members.append(t)
+            ns.written = True
+            dt = RN_BF16 if ns.buf.dtype == torch.bfloat16 else RN_F32
+            bwd.append(("grad_copy:" + t.name, lambda st, a=ptr(s.buf), b=ptr(ns.buf), k=t.numel, dt=dt:
+                        check(lib.rn_cast(a, b, k, dt, dt, st), "rn_cast")))
+            s.members.remove(t)
+            t.gradslot = ns
+            s = ns
+        return s.buf, 1.0
+
+    def _route(self, t, src_slot, done, bwd):
+        """d(t) += d(src): alias when t has no gradient yet, else accumulate."""
+        if not t.requires_grad:
+            return
+        s = self._slot_of(t)
+        if s is None:
+            t.gradslot = src_slot
+            src_slot.members.append(t)
+            return
+        buf, beta = self._target(t, done, bwd)
+        dt = RN_BF16 if buf.dtype == torch.bfloat16 else RN_F32
+        if beta == 0.0:
+            bwd.append(("grad_copy:" + t.name, lambda st, a=ptr(src_slot.buf), b=ptr(buf), k=t.numel, dt=dt:
+                        check(lib.rn_cast(a, b, k, dt, dt, st), "rn_cast")))
+        else:
+            bwd.append(("grad_add:" + t.name, lambda st, a=ptr(buf), b=ptr(src_slot.buf), k=t.numel, dt=dt:
+                        check(lib.rn_add_inplace(a, b, k, dt, st), "rn_add_inplace")))
+
+    def _build_backward(self):
+        bwd = []
+        done = set()
+        self.grad_ready_after = {}   # variable name -> index in bwd after which its gradient is final
+        for n in reversed(self.g.nodes):
+            self._node_backward(n, bwd, done)
+            done.add(id(n))
+            for v in n.vars.values():
+                if v.trainable:
+                    self.grad_ready_after[v.name] = len(bwd)
+        self.bwd = bwd
+
+    def _node_backward(self, n, bwd, done):
+        if n.op == "softmax_xent":
+            logits = n.inputs[0]
+            if n.dlogits is not None:
+                s = _Slot(n.dlogits)
+                s.written = True
+                s.members.append(logits)
+                logits.gradslot = s
+            return
+        y = n.outputs[0]
+        ys = self._slot_of(y)
+        if ys is None or not ys.written:
+            if any(v.trainable for v in n.vars.values()):
+                raise RuntimeError("node %s/%s has trainable variables but no gradient reaches it" % (n.op, y.name))
+            return
+        dy = ys.buf
+        if n.op == "dense":
+            x = n.inputs[0]
+            B = x.shape[0]
+            D = x.numel // B
+            K = y.shape[1]
+            dxp = None
+            if x.requires_grad:
+                dxb, beta = self._target(x, done, bwd)
+                if beta != 0.0:
+                    raise NotImplementedError("dense input gradient fan-in")
+                dxp = ptr(dxb)
+            bwd.append(("dense_bwd:" + y.name,
+                        lambda s, args=(ptr(x.buf), self._wptr(n.vars["kernel"]), ptr(dy), self._wptr(n.vars["kernel"], "G"),
+                                        self._wptr(n.vars["bias"], "G"), dxp, B, D, K):
+                        check(lib.rn_dense_bwd(*args, s), "rn_dense_bwd")))
+        elif n.op == "avgpool":
+            x = n.inputs[0]
+            if not x.requires_grad:
+                return
+            N, H, W, Cc = x.shape
+            dxb, beta = self._target(x, done, bwd)
+            idt = RN_BF16 if x.buf.dtype == torch.bfloat16 else RN_F32
+            odt = RN_BF16 if y.buf.dtype == torch.bfloat16 else RN_F32
+            bwd.append(("avgpool_bwd:" + y.name,
+                        lambda s, args=(ptr(dy), ptr(dxb), N, H, W, Cc, n.attrs["k"], n.attrs["s"], y.shape[3], n.attrs["c_before"], idt, odt, beta):
+                        check(lib.rn_avgpool_bwd(*args, s), "rn_avgpool_bwd")))
+        elif n.op == "maxpool":
+            x = n.inputs[0]
+            if not x.requires_grad:
+                return
+            N, H, W, Cc = x.shape
+            dxb, beta = self._target(x, done, bwd)
+            bwd.append(("maxpool_bwd:" + y.name,
+                        lambda s, args=(ptr(dy), ptr(n.argmax), ptr(dxb), N, H, W, Cc, y.shape[1], y.shape[2], n.attrs["pad"], self.rn_dt, beta):
+                        check(lib.rn_maxpool3x3s2_bwd(*args, s), "rn_maxpool3x3s2_bwd")))
+        elif n.op == "add":
+            for t in n.inputs:
+                self._route(t, ys, done, bwd)
+        elif n.op == "bn_act":
+            x = n.inputs[0]
+            a, v = n.attrs, n.vars
+            if not a["is_training"]:
+                raise NotImplementedError("backward through inference-mode batch norm")
+            C_ = x.shape[-1]
+            M = x.numel // C_
+            mean_p, rstd_p = n.saved[0].data_ptr(), n.saved[1].data_ptr()
+            gp, bp = self._wptr(v["gamma"]), self._wptr(v["beta"])
+            dgp, dbp = self._wptr(v["gamma"], "G"), self._wptr(v["beta"], "G")
+            bwd.append(("bn_bwd_reduce:" + a["scope"],
+                        lambda s, args=(ptr(dy), ptr(x.buf), M, C_, self.rn_dt, gp, bp, mean_p, rstd_p, a["leak"], dgp, dbp):
+                        check(lib.rn_bn_act_bwd_reduce(*args, ptr(self.scratch), self.scratch_bytes, s), "rn_bn_act_bwd_reduce")))
+            if x.requires_grad:
+                dxb, beta = self._target(x, done, bwd)
+                addp = ptr(dxb) if beta != 0.0 else None
+                bwd.append(("bn_bwd_apply:" + a["scope"],
+                            lambda s, args=(ptr(dy), ptr(x.buf), ptr(dxb), addp, M, C_, self.rn_dt, gp, bp, mean_p, rstd_p, dgp, dbp, a["leak"]):
+                            check(lib.rn_bn_act_bwd_apply(*args, s), "rn_bn_act_bwd_apply")))
+        elif n.op == "conv2d":
+            x = n.inputs[0]
+            d = self._desc(n)
+            self._keep.append(d)
+            kv = n.vars["kernel"]
+            if x.requires_grad:
+                dxb, beta = self._target(x, done, bwd)
+                if self._conv_impl(n, 1) == "tc":
+                    run = self._tc_plan(n, d, 1, dy, dxb)
+                    bwd.append(("conv_dgrad_tc:" + y.name, lambda s, run=run, beta=beta: run(s, beta=beta)))
+                else:
+                    w = self._wptr(kv, "Wb" if self.bf16 else "W")
+                    bwd.append(("conv_dgrad:" + y.name, lambda s, d=d, pdy=ptr(dy), w=w, pdx=ptr(dxb), beta=beta:
+                                check(lib.rn_conv2d_dgrad(C.byref(d), pdy, w, pdx, beta, s), "rn_conv2d_dgrad")))
+            if self._conv_impl(n, 2) == "tc":
+                run = self._tc_plan(n, d, 2, x.buf, self._wptr(kv, "G"), b_buf=dy)
+                bwd.append(("conv_wgrad_tc:" + y.name, run))
+            else:
+                nb = lib.rn_conv2d_wgrad_scratch_bytes(C.byref(d))
+                if not hasattr(self, "_wg_scratch") or self._wg_scratch.numel() < nb:
+                    self._wg_scratch = torch.zeros(max(nb, 16), dtype=torch.uint8, device=self.dev)
+                    self._wg_rebind = True
+                bwd.append(("conv_wgrad:" + y.name, ("wgrad", d, ptr(x.buf), ptr(dy), self._wptr(kv, "G"))))
+        else:
+            raise ValueError("unknown op " + n.op)
+
+    def _finalize_wgrad(self):
+        """SIMT wgrad launches share one split-K scratch buffer whose final size is only known
+        after the whole backward list is built."""
+        out = []
+        sp, sb = ptr(self._wg_scratch) if hasattr(self, "_wg_scratch") else None, \
+            self._wg_scratch.numel() if hasattr(self, "_wg_scratch") else 0
+        for name, fn in self.bwd:
+            if isinstance(fn, tuple) and fn[0] == "wgrad":
+                _, d, px, pdy, pdw = fn
+                fn = (lambda s, d=d, px=px, pdy=pdy, pdw=pdw:
+                      check(lib.rn_conv2d_wgrad(C.byref(d), px, pdy, pdw, sp, sb, s), "rn_conv2d_wgrad"))
+            out.append((name, fn))
+        self.bwd = out
+
+    # ------------------------------------------------------------------ aggregation + optimizer
+    def _build_update(self, bucket_bytes):
+        self._finalize_wgrad()
+        # buckets: contiguous ranges of the flat gradient buffer, filled from the END (gradients
+        # become final in reverse creation order), each reduced as soon as it is complete.
+        tv = self.g.trainable_variables()
+        self.buckets = []
+        if self.world > 1 and tv:
+            from .parallel import plan_buckets
+            self.buckets = plan_buckets([v.offset for v in tv], self.n_flat,
+                                        [self.grad_ready_after[v.name] for v in tv],
+                                        max(bucket_bytes // 4, GRANULE), len(self.bwd))
+            self.comm_stream = torch.cuda.Stream(device=self.dev)
+        use_mom = 1 if self.opt_kind == "mom" else 0
+        inv_R = 1.0 / float(self.world)
+        self.update = [("sgd_momentum_fused",
+                        lambda s: check(lib.rn_sgd_momentum_fused(
+                            ptr(self.W), ptr(self.Gd), ptr(self.Mom), ptr(self.Wb), self.n_flat, ptr(self.mask),
+                            ptr(self.hyper), inv_R, self.wd, self.momentum, use_mom, ptr(self.sumsq),
+                            ptr(self.scratch), self.scratch_bytes, s), "rn_sgd_momentum_fused"))]
+        for i, fn in enumerate(getattr(self, "_relayout", [])):
+            self.update.append(("weights_to_bf16:%d" % i, fn))
+
+    def set_lr(self, lr):
+        """The reference feeds the learning rate every step (resnet_cifar_train.py:297-299); here
+        it lives in device memory and is only re-uploaded when the value changes."""
+        lr = float(lr)
+        if getattr(self, "lrn_rate", None) == lr:
+            return
+        self.lrn_rate = lr
+        torch.cuda.current_stream().synchronize()   # the pinned staging word may still be in flight
+        self._hyper_host[0] = lr
+        self.hyper.copy_(self._hyper_host, non_blocking=True)
+
+    def broadcast_from_rank0(self):
+        """hvd.BroadcastGlobalVariablesHook(0) (resnet_cifar_train_horovod.py:313): weights, BN
+        moving stats and momentum slots from rank 0 (one flat ncclBroadcast each)."""
+        import torch.distributed as dist
+        for buf in (self.W, self.S) + ((self.Mom,) if self.train else ()):
+            dist.broadcast(buf, src=dist.get_global_rank(self.pg, 0) if self.pg is not None else 0, group=self.pg)
+        self.refresh_shadow_weights()
+
+    # ------------------------------------------------------------------ running
+    def _run_list(self, lst, st):
+        for _, fn in lst:
+            fn(st)
+
+    def forward(self):
+        st = torch.cuda.current_stream().cuda_stream
+        self._run_list(self.fwd, st)
+
+    def _step_launches(self):
+        import torch.distributed as dist
+        cur = torch.cuda.current_stream()
+        st = cur.cuda_stream
+        self._run_list(self.fwd, st)
+        if self.world > 1:
+            bi = 0
+            for i, (_, fn) in enumerate(self.bwd):
+                fn(st)
+                while bi < len(self.buckets) and self.buckets[bi][2] <= i + 1:
+                    self._reduce_bucket(bi, cur, dist)
+                    bi += 1
+            while bi < len(self.buckets):
+                self._reduce_bucket(bi, cur, dist)
+                bi += 1
+            cur.wait_stream(self.comm_stream)
+        else:
+            self._run_list(self.bwd, st)
+        self._run_list(self.update, st)
+
+    def _reduce_bucket(self, bi, cur, dist):
+        lo, hi, _ = self.buckets[bi]
+        self.comm_stream.wait_stream(cur)
+        with torch.cuda.stream(self.comm_stream):
+            dist.all_reduce(self.Gd[lo:hi], op=dist.ReduceOp.SUM, group=self.pg)
+
+    def count_launches(self):
+        n = len(self.fwd)
+        if self.train:
+            n += len(self.bwd) + len(self.update)
+            # split-K wgrad issues a second (reduce) kernel
+            n += sum(1 for name, _ in self.bwd if name.startswith("conv_wgrad:"))
+        return n
+
+    def capture(self):
+        """Capture one full step (forward, backward, all-reduce, update) in a CUDA graph."""
+        if self._graph_exec is not None:
+            return
+        torch.cuda.synchronize(self.dev)
+        side = torch.cuda.Stream(device=self.dev)
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):      # warm-up outside capture (lazy module loading, NCCL set-up)
+            if self.train:
+                snap = (self.W.clone(), self.Mom.clone(), self.S.clone(), None if self.Wb is None else self.Wb.clone())
+                self._step_launches()
+                torch.cuda.synchronize(self.dev)
+                self.W.copy_(snap[0]); self.Mom.copy_(snap[1]); self.S.copy_(snap[2])
+                if self.Wb is not None:
+                    self.Wb.copy_(snap[3])
+                for fn in getattr(self, "_relayout", []):
+                    fn(side.cuda_stream)
+            else:
+                self.forward()
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize(self.dev)
+        gexec = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(gexec):
+            if self.train:
+                self._step_launches()
+            else:
+                self.forward()
+        self._graph_exec = gexec
+
+    def step(self):
+        """One synchronous training step (== sess.run(train_op), resnet_cifar_train.py:343-344)."""
+        if not self.train:
+            raise RuntimeError("executor was built with train=False")
+        if self._graph_exec is not None:
+            self._graph_exec.replay()
+        else:
+            self._step_launches()
+        self.global_step += 1
+
+    def run_forward(self):
+        if self._graph_exec is not None and not self.train:
+            self._graph_exec.replay()
+        else:
+            self.forward()
+
+    # ------------------------------------------------------------------ results
+    def scalars(self):
+        """(xent, precision, cost) of the last step — one small D2H read (synchronises)."""
+        if self.loss is None:
+            raise RuntimeError("graph has no loss")
+        xs = self.loss[1].buf.tolist()
+        cost = xs[0] + self.wd * 0.5 * float(self.sumsq.item()) if self.train else xs[0]
+        return xs[0], xs[1], cost
+
+    def close(self):
+        for p in self._plans:
+            lib.rn_convtc_plan_destroy(p)
+        self._plans = []

@@ -1,0 +1,90 @@
+"""ImageNet-shape trainer with the flags / loop / LR schedule of the reference's
+resnet_imagenet_train.py (flags :33-99, train() :206-281, main() :283-338).  There is no dataset
+or network here, so the TFRecord + JPEG + vgg_preprocessing input (:105-187) is replaced by
+synthetic standard-normal 224x224x3 images resident on the device.
+
+    torchrun --nproc-per-node 8 -m distributed_tensorflow_resnet_b200.resnet_imagenet_train \
+        --batch_size 128 --train_steps 100
+"""
+import argparse
+import os
+import sys
+import time
+
+import torch
+
+from . import resnet_model
+from . import resnet_cifar_train as _cifar
+from .flags import FLAGS
+
+_WEIGHT_DECAY = 1e-4       # reference :288-291
+_NUM_CLASSES = 1000
+
+
+def imagenet_learning_rate(train_step):
+    """_LearningRateSetterHook.after_run (reference :236-260): Intel-Caffe 8-node schedule —
+    warm-up 0.1 -> 0.4 over 6240 steps, then x0.1 at 37440 / 74880 / 99840."""
+    if train_step < 6240:
+        return 0.1 + 0.3 * train_step / 6240.0
+    elif train_step < 37440:
+        return 0.4
+    elif train_step < 74880:
+        return 0.4 * 0.1
+    elif train_step < 99840:
+        return 0.4 * 0.01
+    return 0.4 * 0.001
+
+
+def synthetic_batch(batch_size, image_size, num_classes, rank, dtype, device):
+    """Standard-normal images (seed 1000 + rank) and random labels, generated once."""
+    gen = torch.Generator().manual_seed(1000 + rank)
+    img = torch.randn(batch_size, image_size, image_size, 3, generator=gen)
+    lab = torch.randint(0, num_classes, (batch_size,), generator=gen)
+    onehot = torch.zeros(batch_size, num_classes)
+    onehot[torch.arange(batch_size), lab] = 1.0
+    return img.to(device=device, dtype=dtype), onehot.to(device)
+
+
+def train(hps, out=sys.stdout, log_every=40):
+    rank, world = _cifar.init_distributed()
+    dev = torch.device("cuda", torch.cuda.current_device())
+    dt = torch.bfloat16 if FLAGS.compute_dtype == "bf16" else torch.float32
+    images, labels = synthetic_batch(FLAGS.batch_size, FLAGS.image_size, hps.num_classes, rank, dt, dev)
+    model = resnet_model.ResNet(hps, images, labels, FLAGS.mode)
+    model.build_graph()
+    lrn_rate = 0.4                        # _LearningRateSetterHook.begin (reference :241)
+    t0 = time.time()
+    it = 0
+    while model.global_step < FLAGS.train_steps:
+        model.lrn_rate = lrn_rate
+        model.train_op()
+        it += 1
+        step = model.global_step
+        if it % log_every == 0 or step >= FLAGS.train_steps:
+            xent, prec, cost = model.executor.scalars()
+            el = time.time() - t0
+            out.write("step = %d, loss = %.6f, precision = %.4f, lr = %g (%.1f images/sec)\n" %
+                      (step, cost, prec, lrn_rate, it * FLAGS.batch_size * world / max(el, 1e-9)))
+            out.flush()
+        lrn_rate = imagenet_learning_rate(step)
+    torch.cuda.synchronize()
+    return model
+
+
+def main(argv=None):
+    parser = argparse.ArgumentParser(description=__doc__, formatter_class=argparse.RawDescriptionHelpFormatter)
+    _cifar.define_flags(parser)
+    parser.add_argument('--num_epochs', type=int, default=90)
+    parser.set_defaults(dataset='imagenet', image_size=224, batch_size=128, train_steps=200)
+    args = parser.parse_args(argv)
+    FLAGS.update(**vars(args))
+    if FLAGS.job_name == 'ps':
+        print("job_name=ps: there are no parameter servers in the NCCL build; exiting.")
+        return None
+    FLAGS.replicas_to_aggregate = int(os.environ.get("WORLD_SIZE", "1"))   # reference :307-308
+    hps = resnet_model.HParams(num_classes=_NUM_CLASSES, lrn_rate=0.1, weight_decay_rate=_WEIGHT_DECAY, optimizer='mom')
+    return train(hps)
+
+
+if __name__ == '__main__':
+    main()

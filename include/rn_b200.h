@@ -1,0 +1,215 @@
+/*
+ * rn_b200.h — C ABI of librn_b200.so: hand-written sm_100a CUDA kernels for the synchronous
+ * data-parallel ResNet training step of michaelwfc/distributed-tensorflow-resnet.
+ *
+ * The reference has NO plugin / FFI interface for this path (it is pure TF-1.x Python; every op
+ * below runs inside un-vendored TensorFlow).  Each entry point therefore cites the reference call
+ * site whose TensorFlow op it replaces (file:line relative to the reference root).
+ *
+ * Conventions
+ *   - extern "C", plain pointers and sizes; no C++ / torch types.
+ *   - every compute entry returns 0 on success or a negative rn_status; rn_last_error() gives a
+ *     thread-local message.  No exceptions cross the boundary.
+ *   - the CALLER owns every buffer (device pointers); kernels are stateless and stream-ordered on
+ *     `stream` (a cudaStream_t passed as void*; NULL = legacy default stream).  Scratch memory is
+ *     passed in with its size; query it with the matching *_scratch_bytes().
+ *   - activations are NHWC; conv kernels HWIO [k,k,Cin,Cout] exactly as TF stores them.
+ *   - `dtype` selects the storage type of activations: RN_F32 (verification mode) or RN_BF16
+ *     (bf16 in HBM, fp32 arithmetic/accumulation).  Parameters, statistics, gradients of
+ *     parameters and optimizer state are always fp32.
+ */
+#ifndef RN_B200_H_
+#define RN_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum { RN_F32 = 0, RN_BF16 = 1 } rn_dtype;
+
+typedef enum {
+  RN_OK = 0,
+  RN_ERR_INVALID = -1,     /* bad argument (shape, alignment, dtype, NULL pointer)            */
+  RN_ERR_SCRATCH = -2,     /* scratch buffer too small                                        */
+  RN_ERR_CUDA = -3,        /* a CUDA runtime / driver call failed; see rn_last_error()        */
+  RN_ERR_UNSUPPORTED = -4  /* valid request that this build does not implement                */
+} rn_status;
+
+const char* rn_last_error(void);
+/* ABI version; bumped whenever a signature changes. */
+int rn_abi_version(void);
+/* Number of kernel launches issued through this library by the calling process (all threads). */
+uint64_t rn_launch_count(void);
+
+/* ------------------------------------------------------------------------------------------
+ * Convolution (Conv2D / Conv2DBackpropInput / Conv2DBackpropFilter)
+ *   replaces tf.layers.conv2d at resnet_model_official.py:87-91 (+ fixed_padding :53-77 folded
+ *   into `pad`) and its autodiff ops created by optimizer.minimize, models/resnet_model.py:125.
+ *   y[n,ho,wo,co] = sum_{r,s,ci} x[n, ho*stride - pad + r, wo*stride - pad + s, ci] * w[r,s,ci,co]
+ *   with zero fill outside the image.  `pad` is the number of zero rows/cols BEFORE the image:
+ *   (k-1)/2 for the official model (SAME at stride 1; symmetric fixed_padding + VALID at stride 2)
+ *   and TF-SAME's pad_before for the upstream `_conv`.
+ * ------------------------------------------------------------------------------------------ */
+typedef struct {
+  int32_t N, H, W, Cin;     /* input  [N,H,W,Cin]   */
+  int32_t Ho, Wo, Cout;     /* output [N,Ho,Wo,Cout] */
+  int32_t k, stride, pad;
+  int32_t dtype;            /* rn_dtype of x / y / dy / dx */
+} rn_conv_desc;
+
+/* CUDA-core (FFMA) implicit-GEMM path: the fp32 verification mode, and the fallback for shapes
+ * the tensor-core path does not take.  In RN_BF16 mode `w` is a bf16 HWIO copy of the weights; in
+ * RN_F32 mode it is the fp32 master. */
+int rn_conv2d_fprop(const rn_conv_desc* d, const void* x, const void* w, void* y, void* stream);
+/* dx = beta*dx + dgrad(dy, w); beta is 0 or 1 (gradient fan-in at residual forks, AddN). */
+int rn_conv2d_dgrad(const rn_conv_desc* d, const void* dy, const void* w, void* dx, float beta, void* stream);
+/* dw (fp32 HWIO) = wgrad(x, dy).  Deterministic split-K: partials in `scratch`, fixed-order sum. */
+size_t rn_conv2d_wgrad_scratch_bytes(const rn_conv_desc* d);
+int rn_conv2d_wgrad(const rn_conv_desc* d, const void* x, const void* dy, float* dw,
+                    void* scratch, size_t scratch_bytes, void* stream);
+
+/* tcgen05 / TMA / TMEM implicit-GEMM path (bf16 operands, fp32 accumulation in tensor memory).
+ * A plan owns the CUtensorMap descriptors (which embed the buffer addresses) for one conv layer
+ * and one of its three GEMMs; it is created once at graph-build time and run every step.
+ *   kind 0: fprop  a = x  [N,H,W,Cin] bf16,  b = w as [k*k][Cout][Cin] bf16,   out = y  bf16
+ *   kind 1: dgrad  a = dy [N,Ho,Wo,Cout] bf16, b = w as [k*k][Cin][Cout] bf16, out = dx bf16
+ *   kind 2: wgrad  a = x, b = dy, out = dw fp32 HWIO (split-K partials in caller scratch)
+ * rn_convtc_supported() says whether the shape is handled (else use the CUDA-core path). */
+typedef struct rn_convtc_plan rn_convtc_plan;
+int rn_convtc_supported(const rn_conv_desc* d, int kind);
+size_t rn_convtc_scratch_bytes(const rn_conv_desc* d, int kind);
+int rn_convtc_plan_create(const rn_conv_desc* d, int kind, const void* a, const void* b, void* out,
+                          void* scratch, size_t scratch_bytes, rn_convtc_plan** plan);
+/* beta (dgrad only): 0 overwrite, 1 accumulate into `out`. */
+int rn_convtc_run(rn_convtc_plan* plan, float beta, void* stream);
+int rn_convtc_plan_destroy(rn_convtc_plan* plan);
+/* Re-layout of the fp32 HWIO master weights into the two bf16 operand layouts above
+ * ([k*k][Cout][Cin] for fprop, [k*k][Cin][Cout] for dgrad). Either output may be NULL. */
+int rn_weights_to_bf16(const float* w_hwio, int k, int Cin, int Cout, void* w_fprop, void* w_dgrad, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Batch normalisation + (leaky) ReLU (+ residual add)
+ *   replaces tf.layers.batch_normalization(fused=True) + tf.nn.relu, resnet_model_official.py:41-50
+ *   (FusedBatchNorm epsilon 1.001e-5, decay 0.997, moving variance from the UNBIASED batch
+ *   variance), the residual `inputs + shortcut` at :130 / :175, and FusedBatchNormGrad + ReluGrad
+ *   + AddN from autodiff.  Also serves the upstream `_batch_norm` / `_relu(leakiness)` (biased
+ *   moving variance, eps 1e-3, decay 0.9).  x viewed as [M = N*H*W, C]; C % 4 == 0 (f32) or
+ *   C % 8 == 0 (bf16) for the vector path, any C otherwise.
+ * ------------------------------------------------------------------------------------------ */
+size_t rn_bn_scratch_bytes(int64_t M, int32_t C);
+/* Training statistics.  If `addend` != NULL the statistics are of z = x + addend and z is written
+ * to `sum_out` (the residual add fused into the statistics pass).  Writes mean[C], rstd[C]
+ * (= 1/sqrt(biased_var + eps)) and, if moving_mean != NULL, updates
+ * mov -= (mov - batch) * (1 - decay) with the unbiased (unbiased != 0) or biased variance. */
+int rn_bn_stats_fwd(const void* x, const void* addend, void* sum_out, int64_t M, int32_t C, int32_t dtype,
+                    float eps, float decay, int32_t unbiased, float* mean, float* rstd,
+                    float* moving_mean, float* moving_var, void* scratch, size_t scratch_bytes, void* stream);
+/* y = act(gamma * (x - mean) * rstd + beta), act(v) = v < 0 ? leak * v : v.
+ * If stats_are_moving != 0, `rstd` holds a VARIANCE and rstd = 1/sqrt(var + eps) is formed on the
+ * fly (inference mode: mean/var are the moving statistics). */
+int rn_bn_apply_act_fwd(const void* x, void* y, int64_t M, int32_t C, int32_t dtype, const float* gamma,
+                        const float* beta, const float* mean, const float* rstd, int32_t stats_are_moving,
+                        float eps, float leak, void* stream);
+/* g = dy * act'(pre);  dbeta = sum g;  dgamma = sum g * xhat.  (pre is recomputed from x.) */
+int rn_bn_act_bwd_reduce(const void* dy, const void* x, int64_t M, int32_t C, int32_t dtype,
+                         const float* gamma, const float* beta, const float* mean, const float* rstd, float leak,
+                         float* dgamma, float* dbeta, void* scratch, size_t scratch_bytes, void* stream);
+/* dx = gamma * rstd * (g - dbeta/M - xhat * dgamma/M) [+ dx_addend].  dx may alias dx_addend. */
+int rn_bn_act_bwd_apply(const void* dy, const void* x, void* dx, const void* dx_addend, int64_t M, int32_t C,
+                        int32_t dtype, const float* gamma, const float* beta, const float* mean, const float* rstd,
+                        const float* dgamma, const float* dbeta, float leak, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Pooling
+ *   max: tf.layers.max_pooling2d(3, 2, 'SAME'), resnet_model_official.py:314-316 (+ MaxPoolGrad)
+ *   avg: tf.layers.average_pooling2d(8|7, 1, 'VALID') :269-271 / :337-339 (+ AvgPoolGrad); also the
+ *        upstream `_residual` shortcut avg_pool(stride, stride, 'VALID') + channel zero-pad and
+ *        `_global_avg_pool`.
+ * ------------------------------------------------------------------------------------------ */
+int rn_maxpool3x3s2_fwd(const void* x, void* y, uint8_t* argmax, int32_t N, int32_t H, int32_t W, int32_t C,
+                        int32_t Ho, int32_t Wo, int32_t pad, int32_t dtype, void* stream);
+int rn_maxpool3x3s2_bwd(const void* dy, const uint8_t* argmax, void* dx, int32_t N, int32_t H, int32_t W, int32_t C,
+                        int32_t Ho, int32_t Wo, int32_t pad, int32_t dtype, float beta, void* stream);
+/* VALID k x k stride s average; output channel c_before + c (Cout >= C + c_before, rest zero). */
+int rn_avgpool_fwd(const void* x, void* y, int32_t N, int32_t H, int32_t W, int32_t C, int32_t k, int32_t s,
+                   int32_t Cout, int32_t c_before, int32_t in_dtype, int32_t out_dtype, void* stream);
+int rn_avgpool_bwd(const void* dy, void* dx, int32_t N, int32_t H, int32_t W, int32_t C, int32_t k, int32_t s,
+                   int32_t Cout, int32_t c_before, int32_t in_dtype, int32_t out_dtype, float beta, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Classifier head and loss
+ *   dense:  tf.layers.dense, resnet_model_official.py:274 / :343 (MatMul + BiasAdd and their grads)
+ *   xent:   tf.nn.softmax + tf.losses.softmax_cross_entropy, models/resnet_model.py:79-83
+ *           (Sum / num_present reduction), d logits = (softmax * sum(y) - y) / B; plus the
+ *           trainers' precision metric mean(argmax(pred) == argmax(label)),
+ *           resnet_cifar_train.py:271-273.  All fp32.
+ * ------------------------------------------------------------------------------------------ */
+int rn_dense_fwd(const float* x, const float* w, const float* b, float* y, int32_t B, int32_t D, int32_t K, void* stream);
+int rn_dense_bwd(const float* x, const float* w, const float* dy, float* dw, float* db, float* dx,
+                 int32_t B, int32_t D, int32_t K, void* stream);
+/* out_scalars[0] = mean xent, out_scalars[1] = precision. probs / dlogits may be NULL. */
+int rn_softmax_xent(const float* logits, const float* onehot, int32_t B, int32_t K, float* probs, float* dlogits,
+                    float* out_scalars, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Gradient aggregation epilogue + optimizer over the flat fp32 buffers
+ *   replaces SyncReplicasOptimizer's ConditionalAccumulator.take_grad(R) mean
+ *   (models/resnet_model.py:104-116) / hvd.DistributedOptimizer's average (:118-120), the L2
+ *   weight-decay gradient (:88-89; AddN(wgrad, wd*v)) and ApplyMomentum(use_nesterov=False) /
+ *   ApplyGradientDescent (:98-101), in ONE pass:
+ *     g' = g * inv_R + wd * mask * w ;  m = momentum * m + g' ;  w -= lr * m   (sgd: w -= lr * g')
+ *   `g` holds the SUM over R replicas (ncclAllReduce sum).  lr is read from device memory
+ *   (hyper[0]) so the step can live in a CUDA graph while the host LR hook
+ *   (resnet_cifar_train.py:291-311) changes it.  granule_mask (nullable) has one byte per 64
+ *   parameters: 1 = weight decay applies (all ones for the reference; 'DW' only upstream).
+ *   If w_bf16 != NULL a bf16 copy of the updated weights is written (same offsets).
+ *   If sumsq_out != NULL, sumsq_out[0] = sum(mask * w_old^2) (for cost = xent + wd * sumsq / 2),
+ *   reduced deterministically through `scratch`.
+ * ------------------------------------------------------------------------------------------ */
+size_t rn_optimizer_scratch_bytes(int64_t n);
+int rn_sgd_momentum_fused(float* w, const float* g, float* m, void* w_bf16, int64_t n, const uint8_t* granule_mask,
+                          const float* hyper, float inv_R, float wd, float momentum, int32_t use_momentum,
+                          float* sumsq_out, void* scratch, size_t scratch_bytes, void* stream);
+/* out[0] = sum(mask * w^2) without updating anything (eval / reporting). */
+int rn_l2_sumsq(const float* w, int64_t n, const uint8_t* granule_mask, float* out, void* scratch,
+                size_t scratch_bytes, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * CIFAR binary-record decode + augmentation
+ *   replaces cifar_input.build_input (cifar_input.py:25-119; pad 2 -> 36x36) and
+ *   parse_record / preprocess_image (resnet_cifar_train.py:158-202; pad 4 -> 40x40):
+ *   label byte -> one-hot; CHW uint8 -> HWC float; zero-pad; random crop 32x32; random
+ *   left-right flip; per-image standardisation (x - mean) / max(stddev, 1/sqrt(3072)).
+ *   records: uint8 [n_records][record_bytes] resident in HBM; indices[B] selects the batch.
+ *   Random draws: Philox4x32-10, key (seed_lo, seed_hi), counter (record index, epoch, 0, 0);
+ *   words 0,1 -> crop offsets (u32 % (2^31-1)) % (2*pad+1), word 3 -> flip iff
+ *   bitcast((u & 0x7fffff)|0x3f800000) - 1 < 0.5.  If draws_in != NULL its int32 [B][3]
+ *   (oy, ox, flip) are used instead.  draws_out (nullable) receives the (oy, ox, flip) used.
+ *   train == 0: no pad/crop/flip (eval path, standardise only).
+ * ------------------------------------------------------------------------------------------ */
+int rn_cifar_decode(const uint8_t* records, int64_t n_records, int32_t record_bytes, int32_t label_offset,
+                    int32_t classes, const int32_t* indices, int32_t B, int32_t train, int32_t pad,
+                    uint32_t seed_lo, uint32_t seed_hi, uint32_t epoch, const int32_t* draws_in,
+                    void* out_img, int32_t out_dtype, float* out_onehot, int32_t* out_labels,
+                    int32_t* draws_out, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Small utilities used by the host graph executor (no reference counterpart beyond tf.cast /
+ * AddN / tf.pad at the call sites above).
+ * ------------------------------------------------------------------------------------------ */
+int rn_cast(const void* src, void* dst, int64_t n, int32_t src_dtype, int32_t dst_dtype, void* stream);
+/* dst = beta*dst + src  (AddN of gradients when no fused path applies) */
+int rn_add_inplace(void* dst, const void* src, int64_t n, int32_t dtype, void* stream);
+/* y = a + b (forward residual add when it cannot be fused into a BN statistics pass) */
+int rn_add(const void* a, const void* b, void* y, int64_t n, int32_t dtype, void* stream);
+/* NHWC channel pad/copy: dst[..., 0:Cdst] = src[..., 0:Csrc] zero-extended (stem 3 -> 8 channels). */
+int rn_pad_channels(const void* src, void* dst, int64_t pixels, int32_t Csrc, int32_t Cdst, int32_t src_dtype,
+                    int32_t dst_dtype, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RN_B200_H_ */

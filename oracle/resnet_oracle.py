@@ -138,8 +138,13 @@ class Net:
 
         def bwd():
             g = out.grad.permute(0, 3, 1, 2)
-            gx = torch.nn.grad.conv2d_input(xp.shape, wt, g, stride=stride)
-            gw = torch.nn.grad.conv2d_weight(xp, wt.shape, g, stride=stride)
+            # pad the cropped rows/cols of the VALID output back with zeros, then the native
+            # (oneDNN) backward kernels: dgrad = transposed conv, wgrad = correlation of x and dy
+            full = F.conv2d(xp[:1, :1], wt[:1, :1], stride=stride).shape[-2:]
+            if tuple(full) != (Ho, Wo):
+                g = F.pad(g, (0, full[1] - Wo, 0, full[0] - Ho))
+            gx, gw, _ = torch.ops.aten.convolution_backward(
+                g.contiguous(), xp, wt, None, [stride, stride], [0, 0], [1, 1], False, [0, 0], 1, [True, True, False])
             gx = gx[:, :, pad_before:pad_before + H, pad_before:pad_before + W]
             x.add_grad(gx.permute(0, 2, 3, 1).contiguous())
             self._pgrad(w_name, gw.permute(2, 3, 1, 0).contiguous())
@@ -219,8 +224,11 @@ class Net:
 
         def bwd():
             g = out.grad.permute(0, 3, 1, 2).contiguous()
-            gx = F.max_unpool2d(g, idx, 3, 2, output_size=xp.shape[-2:])
-            gx = gx[:, :, ph:ph + H, pw:pw + W]
+            # overlapping windows: one input cell can win several windows -> accumulate
+            Hp, Wp = xp.shape[-2:]
+            gx = torch.zeros((N, C, Hp * Wp), dtype=g.dtype)
+            gx.scatter_add_(2, idx.reshape(N, C, -1), g.reshape(N, C, -1))
+            gx = gx.reshape(N, C, Hp, Wp)[:, :, ph:ph + H, pw:pw + W]
             x.add_grad(gx.permute(0, 2, 3, 1).contiguous())
         self.tape.append(bwd)
         return out
