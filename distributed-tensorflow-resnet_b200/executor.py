@@ -91,6 +91,7 @@ class Executor:
         self._graph_exec = None
         self._plans = []
         self._keep = []
+        self.meta = {}      # launch name -> tensors it reads / writes (for the step-through verifier in tests/)
         self._layout(seed, init_values)
         self._alloc_activations()
         self._build_forward()
@@ -295,6 +296,9 @@ class Executor:
                             check(lib.rn_softmax_xent(pl, py, d[0], d[1], pp, pd, ps, s), "rn_softmax_xent")))
             else:
                 raise ValueError("unknown op " + n.op)
+            for nm, _ in fwd:
+                if nm not in self.meta:
+                    self.meta[nm] = dict(node=None if nm.startswith("cast:") else n)
         self.fwd = fwd
 
     def _conv_impl(self, n, kind):
@@ -446,6 +450,10 @@ class Executor:
                     self.grad_ready_after[v.name] = len(bwd)
         self.bwd = bwd
 
+    def _emit(self, bwd, name, fn, **meta):
+        bwd.append((name, fn))
+        self.meta[name] = meta
+
     def _node_backward(self, n, bwd, done):
         if n.op == "softmax_xent":
             logits = n.inputs[0]
@@ -473,10 +481,11 @@ class Executor:
                 if beta != 0.0:
                     raise NotImplementedError("dense input gradient fan-in")
                 dxp = ptr(dxb)
-            bwd.append(("dense_bwd:" + y.name,
-                        lambda s, args=(ptr(x.buf), self._wptr(n.vars["kernel"]), ptr(dy), self._wptr(n.vars["kernel"], "G"),
-                                        self._wptr(n.vars["bias"], "G"), dxp, B, D, K):
-                        check(lib.rn_dense_bwd(*args, s), "rn_dense_bwd")))
+            self._emit(bwd, "dense_bwd:" + y.name,
+                       lambda s, args=(ptr(x.buf), self._wptr(n.vars["kernel"]), ptr(dy), self._wptr(n.vars["kernel"], "G"),
+                                       self._wptr(n.vars["bias"], "G"), dxp, B, D, K):
+                       check(lib.rn_dense_bwd(*args, s), "rn_dense_bwd"),
+                       node=n, dy=dy, dx=dxb if x.requires_grad else None, beta=0.0)
         elif n.op == "avgpool":
             x = n.inputs[0]
             if not x.requires_grad:
@@ -485,18 +494,18 @@ class Executor:
             dxb, beta = self._target(x, done, bwd)
             idt = RN_BF16 if x.buf.dtype == torch.bfloat16 else RN_F32
             odt = RN_BF16 if y.buf.dtype == torch.bfloat16 else RN_F32
-            bwd.append(("avgpool_bwd:" + y.name,
-                        lambda s, args=(ptr(dy), ptr(dxb), N, H, W, Cc, n.attrs["k"], n.attrs["s"], y.shape[3], n.attrs["c_before"], idt, odt, beta):
-                        check(lib.rn_avgpool_bwd(*args, s), "rn_avgpool_bwd")))
+            self._emit(bwd, "avgpool_bwd:" + y.name,
+                       lambda s, args=(ptr(dy), ptr(dxb), N, H, W, Cc, n.attrs["k"], n.attrs["s"], y.shape[3], n.attrs["c_before"], idt, odt, beta):
+                       check(lib.rn_avgpool_bwd(*args, s), "rn_avgpool_bwd"), node=n, dy=dy, dx=dxb, beta=beta)
         elif n.op == "maxpool":
             x = n.inputs[0]
             if not x.requires_grad:
                 return
             N, H, W, Cc = x.shape
             dxb, beta = self._target(x, done, bwd)
-            bwd.append(("maxpool_bwd:" + y.name,
-                        lambda s, args=(ptr(dy), ptr(n.argmax), ptr(dxb), N, H, W, Cc, y.shape[1], y.shape[2], n.attrs["pad"], self.rn_dt, beta):
-                        check(lib.rn_maxpool3x3s2_bwd(*args, s), "rn_maxpool3x3s2_bwd")))
+            self._emit(bwd, "maxpool_bwd:" + y.name,
+                       lambda s, args=(ptr(dy), ptr(n.argmax), ptr(dxb), N, H, W, Cc, y.shape[1], y.shape[2], n.attrs["pad"], self.rn_dt, beta):
+                       check(lib.rn_maxpool3x3s2_bwd(*args, s), "rn_maxpool3x3s2_bwd"), node=n, dy=dy, dx=dxb, beta=beta)
         elif n.op == "add":
             for t in n.inputs:
                 self._route(t, ys, done, bwd)
@@ -510,15 +519,16 @@ class Executor:
             mean_p, rstd_p = n.saved[0].data_ptr(), n.saved[1].data_ptr()
             gp, bp = self._wptr(v["gamma"]), self._wptr(v["beta"])
             dgp, dbp = self._wptr(v["gamma"], "G"), self._wptr(v["beta"], "G")
-            bwd.append(("bn_bwd_reduce:" + a["scope"],
-                        lambda s, args=(ptr(dy), ptr(x.buf), M, C_, self.rn_dt, gp, bp, mean_p, rstd_p, a["leak"], dgp, dbp):
-                        check(lib.rn_bn_act_bwd_reduce(*args, ptr(self.scratch), self.scratch_bytes, s), "rn_bn_act_bwd_reduce")))
+            self._emit(bwd, "bn_bwd_reduce:" + a["scope"],
+                       lambda s, args=(ptr(dy), ptr(x.buf), M, C_, self.rn_dt, gp, bp, mean_p, rstd_p, a["leak"], dgp, dbp):
+                       check(lib.rn_bn_act_bwd_reduce(*args, ptr(self.scratch), self.scratch_bytes, s), "rn_bn_act_bwd_reduce"),
+                       node=n, dy=dy)
             if x.requires_grad:
                 dxb, beta = self._target(x, done, bwd)
                 addp = ptr(dxb) if beta != 0.0 else None
-                bwd.append(("bn_bwd_apply:" + a["scope"],
-                            lambda s, args=(ptr(dy), ptr(x.buf), ptr(dxb), addp, M, C_, self.rn_dt, gp, bp, mean_p, rstd_p, dgp, dbp, a["leak"]):
-                            check(lib.rn_bn_act_bwd_apply(*args, s), "rn_bn_act_bwd_apply")))
+                self._emit(bwd, "bn_bwd_apply:" + a["scope"],
+                           lambda s, args=(ptr(dy), ptr(x.buf), ptr(dxb), addp, M, C_, self.rn_dt, gp, bp, mean_p, rstd_p, dgp, dbp, a["leak"]):
+                           check(lib.rn_bn_act_bwd_apply(*args, s), "rn_bn_act_bwd_apply"), node=n, dy=dy, dx=dxb, beta=beta)
         elif n.op == "conv2d":
             x = n.inputs[0]
             d = self._desc(n)
@@ -528,20 +538,22 @@ class Executor:
                 dxb, beta = self._target(x, done, bwd)
                 if self._conv_impl(n, 1) == "tc":
                     run = self._tc_plan(n, d, 1, dy, dxb)
-                    bwd.append(("conv_dgrad_tc:" + y.name, lambda s, run=run, beta=beta: run(s, beta=beta)))
+                    self._emit(bwd, "conv_dgrad_tc:" + y.name, lambda s, run=run, beta=beta: run(s, beta=beta),
+                               node=n, dy=dy, dx=dxb, beta=beta)
                 else:
                     w = self._wptr(kv, "Wb" if self.bf16 else "W")
-                    bwd.append(("conv_dgrad:" + y.name, lambda s, d=d, pdy=ptr(dy), w=w, pdx=ptr(dxb), beta=beta:
-                                check(lib.rn_conv2d_dgrad(C.byref(d), pdy, w, pdx, beta, s), "rn_conv2d_dgrad")))
+                    self._emit(bwd, "conv_dgrad:" + y.name, lambda s, d=d, pdy=ptr(dy), w=w, pdx=ptr(dxb), beta=beta:
+                               check(lib.rn_conv2d_dgrad(C.byref(d), pdy, w, pdx, beta, s), "rn_conv2d_dgrad"),
+                               node=n, dy=dy, dx=dxb, beta=beta)
             if self._conv_impl(n, 2) == "tc":
                 run = self._tc_plan(n, d, 2, x.buf, self._wptr(kv, "G"), b_buf=dy)
-                bwd.append(("conv_wgrad_tc:" + y.name, run))
+                self._emit(bwd, "conv_wgrad_tc:" + y.name, run, node=n, dy=dy)
             else:
                 nb = lib.rn_conv2d_wgrad_scratch_bytes(C.byref(d))
                 if not hasattr(self, "_wg_scratch") or self._wg_scratch.numel() < nb:
                     self._wg_scratch = torch.zeros(max(nb, 16), dtype=torch.uint8, device=self.dev)
                     self._wg_rebind = True
-                bwd.append(("conv_wgrad:" + y.name, ("wgrad", d, ptr(x.buf), ptr(dy), self._wptr(kv, "G"))))
+                self._emit(bwd, "conv_wgrad:" + y.name, ("wgrad", d, ptr(x.buf), ptr(dy), self._wptr(kv, "G")), node=n, dy=dy)
         else:
             raise ValueError("unknown op " + n.op)
 

@@ -28,16 +28,19 @@ BN_EPS_UPSTREAM = 0.001
 
 
 class Var:
-    """A tape value: NHWC activation (or [N, D] matrix) with an accumulated gradient."""
-    __slots__ = ("val", "grad", "name")
+    """A tape value: NHWC activation (or [N, D] matrix) with an accumulated gradient.
+    `q` is the storage rounding of the CUDA path being checked (identity, or bf16 round-trip)."""
+    __slots__ = ("val", "grad", "name", "q")
 
-    def __init__(self, val, name=None):
+    def __init__(self, val, name=None, q=None):
         self.val = val
         self.grad = None
         self.name = name
+        self.q = q
 
     def add_grad(self, g):
-        self.grad = g if self.grad is None else self.grad + g
+        g = g if self.grad is None else self.grad + g
+        self.grad = self.q(g) if self.q is not None else g
 
 
 def tf_same_pad(size, k, s):
@@ -50,8 +53,13 @@ def tf_same_pad(size, k, s):
 class Net:
     """Holds parameters (TF names, creation order), BN moving stats and the tape."""
 
-    def __init__(self, dtype=torch.float32, seed=0, params=None):
+    def __init__(self, dtype=torch.float32, seed=0, params=None, storage=None):
+        """storage=torch.bfloat16 emulates the bf16 mode of the CUDA path: activations, activation
+        gradients and conv weights are rounded to bf16 wherever that path stores them in HBM
+        (arithmetic stays in `dtype`), so the comparison isolates kernel error from the
+        precision choice itself."""
         self.dtype = dtype
+        self.storage = storage
         self.params = OrderedDict()      # trainable, creation order == tf.trainable_variables()
         self.param_grads = OrderedDict()
         self.state = OrderedDict()       # moving_mean / moving_variance
@@ -96,8 +104,15 @@ class Net:
         self.param_grads = OrderedDict()
         self.bn_updates = OrderedDict()
 
-    def _rec(self, var, name):
+    def _round(self, t):
+        return t if self.storage is None else t.to(self.storage).to(self.dtype)
+
+    def _rec(self, var, name, stored=True):
+        """Register an op output; `stored` = the CUDA path keeps it in the activation dtype."""
         var.name = name
+        if stored and self.storage is not None:
+            var.val = self._round(var.val)
+            var.q = self._round
         self.acts[name] = var
         return var
 
@@ -125,7 +140,7 @@ class Net:
         """Conv2D NHWC/HWIO, no bias.  `pad_before` zero rows/cols precede the image; the trailing
         pad is whatever `out_hw` needs (zero fill).  Follows tf.layers.conv2d as called at
         resnet_model_official.py:87-91 and tf.nn.conv2d at upstream `_conv`."""
-        w = self.get_param(w_name, (k, k, cin, cout), init, decay=True)
+        w = self._round(self.get_param(w_name, (k, k, cin, cout), init, decay=True))
         xv = x.val
         N, H, W, C = xv.shape
         Ho, Wo = out_hw
@@ -160,9 +175,14 @@ class Net:
         and the 0.9 moving average, eps 1e-3; `_relu`: where(x<0, leak*x, x)."""
         xv = x.val
         C = xv.shape[-1]
-        gamma = self.get_param(scope + "/gamma", (C,), lambda s: torch.ones(s, dtype=torch.float64), decay=self._bn_decay_flag)
-        beta = self.get_param(scope + "/beta", (C,), lambda s: torch.zeros(s, dtype=torch.float64), decay=self._bn_decay_flag)
-        # upstream creates beta before gamma, but both are non-'DW' so order only affects naming
+        mk_gamma = lambda: self.get_param(scope + "/gamma", (C,), lambda s: torch.ones(s, dtype=torch.float64), decay=self._bn_decay_flag)
+        mk_beta = lambda: self.get_param(scope + "/beta", (C,), lambda s: torch.zeros(s, dtype=torch.float64), decay=self._bn_decay_flag)
+        if self._beta_first:      # upstream `_batch_norm` creates beta before gamma; tf.layers the reverse
+            beta = mk_beta()
+            gamma = mk_gamma()
+        else:
+            gamma = mk_gamma()
+            beta = mk_beta()
         mm = self.get_state(scope + "/moving_mean", (C,), 0.0)
         mv = self.get_state(scope + "/moving_variance", (C,), 1.0)
         M = xv.numel() // C
@@ -177,7 +197,7 @@ class Net:
         rstd = 1.0 / torch.sqrt(var + eps)
         xhat = (x2 - mean) * rstd
         pre = (xhat * gamma + beta).reshape(xv.shape)
-        bn_out = self._rec(Var(pre), opnames[0])
+        bn_out = self._rec(Var(pre), opnames[0], stored=False)
         act = torch.where(pre < 0, leak * pre, pre)
         out = self._rec(Var(act), opnames[1])
         g_name, b_name = scope + "/gamma", scope + "/beta"
@@ -233,12 +253,12 @@ class Net:
         self.tape.append(bwd)
         return out
 
-    def avg_pool(self, x, k, s, opname):
+    def avg_pool(self, x, k, s, opname, stored=True):
         """VALID average pooling, window k stride s (global pool when k == H; the upstream
         `_residual` shortcut uses k == s == stride)."""
         xv = x.val
         y = F.avg_pool2d(xv.permute(0, 3, 1, 2), k, s)
-        out = self._rec(Var(y.permute(0, 2, 3, 1).contiguous()), opname)
+        out = self._rec(Var(y.permute(0, 2, 3, 1).contiguous()), opname, stored=stored)
         N, H, W, C = xv.shape
 
         def bwd():
@@ -266,7 +286,7 @@ class Net:
         w = self.get_param(w_name, (din, dout), w_init, decay=True)
         b = self.get_param(b_name, (dout,), lambda s: torch.zeros(s, dtype=torch.float64), decay=decay_bias)
         x2 = x.val.reshape(x.val.shape[0], -1)
-        out = self._rec(Var(x2 @ w + b), opname)
+        out = self._rec(Var(x2 @ w + b), opname, stored=False)
 
         def bwd():
             g = out.grad
@@ -297,6 +317,7 @@ class Net:
             fn()
 
     _bn_decay_flag = True
+    _beta_first = False
 
 
 # ======================================================================================
@@ -375,7 +396,7 @@ class OfficialResNetV2(Net):
             x = self.block_layer(x, 32, False, n, 2, is_training)
             x = self.block_layer(x, 64, False, n, 2, is_training)
             x = self.batch_norm_relu(x, is_training)
-            x = self.avg_pool(x, 8, 1, "average_pooling2d/AvgPool")
+            x = self.avg_pool(x, 8, 1, "average_pooling2d/AvgPool", stored=False)
             feat = 64
         else:                                                           # :281-366
             table = {18: (False, [2, 2, 2, 2]), 34: (False, [3, 4, 6, 3]), 50: (True, [3, 4, 6, 3]),
@@ -388,7 +409,7 @@ class OfficialResNetV2(Net):
             for i, (f, s) in enumerate(zip([64, 128, 256, 512], [1, 2, 2, 2])):
                 x = self.block_layer(x, f, bott, layers[i], s, is_training)
             x = self.batch_norm_relu(x, is_training)
-            x = self.avg_pool(x, x.val.shape[1], 1, "average_pooling2d/AvgPool")
+            x = self.avg_pool(x, x.val.shape[1], 1, "average_pooling2d/AvgPool", stored=False)
             feat = 2048 if bott else 512
         logits = self.dense(x, "dense/kernel", "dense/bias", feat, self.num_classes,
                             self.init_glorot_uniform, "dense/BiasAdd", decay_bias=True)
@@ -410,6 +431,7 @@ class UpstreamResNet(Net):
         self.leak = relu_leakiness
         self.filters = filters or ([16, 64, 128, 256] if use_bottleneck else [16, 16, 32, 64])
         self._bn_decay_flag = False   # `_decay` only decays names containing 'DW'
+        self._beta_first = True
 
     def _init_conv(self, shape):
         n = shape[0] * shape[1] * shape[3]
@@ -441,8 +463,8 @@ class UpstreamResNet(Net):
         x = self._bn_relu(s + "/sub2/bn2", x, is_training)
         x = self._conv(s + "/sub2/conv2", x, 3, cout, cout, 1)
         if cin != cout:
-            if stride > 1:
-                orig = self.avg_pool(orig, stride, stride, s + "/sub_add/AvgPool")
+            if stride > 1:      # (avg_pool + channel pad is ONE kernel in the CUDA path: one rounding)
+                orig = self.avg_pool(orig, stride, stride, s + "/sub_add/AvgPool", stored=False)
             orig = self.pad_channels(orig, (cout - cin) // 2, (cout - cin) // 2, s + "/sub_add/Pad")
         return self.add(x, orig, s + "/sub_add/add")
 
@@ -475,7 +497,7 @@ class UpstreamResNet(Net):
             for i in range(1, self.units):
                 x = res("unit_%d_%d" % (stage + 1, i), x, f[stage + 1], f[stage + 1], 1, False, is_training)
         x = self._bn_relu("unit_last/final_bn", x, is_training)
-        x = self.avg_pool(x, x.val.shape[1], 1, "unit_last/global_avg_pool")
+        x = self.avg_pool(x, x.val.shape[1], 1, "unit_last/global_avg_pool", stored=False)
         return self.dense(x, "logit/DW", "logit/biases", f[3], self.num_classes, self._init_fc,
                           "logit/xw_plus_b", decay_bias=False)
 
