@@ -57,6 +57,7 @@ SIGNATURES = {
     "rn_weights_to_bf16": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, vp, vp, vp]),
     "rn_bn_scratch_bytes": (sz, [i64, i32]),
     "rn_bn_stats_fwd": (C.c_int, [vp, vp, vp, i64, i32, i32, f32, f32, i32, vp, vp, vp, vp, vp, sz, vp]),
+    "rn_bn_stats_fwd_noalloc": (C.c_int, [vp, vp, vp, i64, i32, i32, f32, f32, i32, vp, vp, vp, vp, vp]),
     "rn_bn_apply_act_fwd": (C.c_int, [vp, vp, i64, i32, i32, vp, vp, vp, vp, i32, f32, f32, vp]),
     "rn_bn_act_bwd_reduce": (C.c_int, [vp, vp, i64, i32, i32, vp, vp, vp, vp, f32, vp, vp, vp, sz, vp]),
     "rn_bn_act_bwd_apply": (C.c_int, [vp, vp, vp, vp, i64, i32, i32, vp, vp, vp, vp, vp, vp, f32, vp]),

@@ -470,3 +470,106 @@ extern "C" int rn_bn_act_bwd_apply(const void* dy, const void* x, void* dx, cons
                                               as_stream(stream));
   return fail(RN_ERR_INVALID, "bn_bwd_apply: bad dtype %d", dtype);
 }
+
+// ------------------------------------------------------------------------------------------
+// rn_bn_stats_fwd_noalloc — the forward statistics pass for callers that cannot hand us scratch.
+//
+// rn_bn_stats_fwd needs a caller-allocated scratch buffer for its per-CTA partial sums and ticket
+// counters.  Some hosts have no way to provide one: a plugin loaded into a process whose framework
+// has already claimed (nearly) all device memory for its own pool (TensorFlow 1.x, the reference's
+// runtime, does this by default, so a cudaMalloc from a side library fails), or a latency-critical
+// loop that must not risk cudaMalloc's implicit device-wide synchronisation.  For them the scratch
+// lives in the fixed device array below, which is part of the library image: every GPU that loads
+// librn_b200.so holds these 512 KiB until the process exits, whether or not the entry is used.
+//
+// The array's name is only a host-side handle; its device address is looked up once per device
+// (with that device current) through cudaGetSymbolAddress on the FIRST call made on that device —
+// make that first call during set-up, before any stream capture is begun.  The entry point calls
+// no cudaMalloc / cudaFree and no allocating library routine.
+//
+// All calls on a device share the one array and it keeps whatever the previous call left behind:
+// the ticket counters are cleared at the start of every call (stream-ordered memset), the partial
+// sums are fully overwritten before they are read.  Two calls that overlap on the GPU (different
+// streams, or different host threads without ordering) race on it — serialise them.
+// Limits: C <= RN_BN_NOALLOC_MAX_C channels (any M); larger C is rejected with RN_ERR_INVALID.
+// ------------------------------------------------------------------------------------------
+#include <mutex>
+
+#define RN_BN_NOALLOC_SCRATCH_BYTES (512 * 1024)
+#define RN_BN_NOALLOC_MAX_C 4096
+#define RN_BN_NOALLOC_MAX_DEVICES 64
+
+static __device__ __align__(256) unsigned char g_bn_noalloc_scratch[RN_BN_NOALLOC_SCRATCH_BYTES];
+
+namespace rn {
+static std::mutex g_noalloc_mu;
+static void* g_noalloc_dev_ptr[RN_BN_NOALLOC_MAX_DEVICES] = {nullptr};
+
+// Device address of the static scratch on the CURRENT device (resolved once per device).
+static int bn_noalloc_scratch_ptr(void** out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return fail(RN_ERR_CUDA, "bn_stats_noalloc: cudaGetDevice: %s", cudaGetErrorString(e));
+  if (dev < 0 || dev >= RN_BN_NOALLOC_MAX_DEVICES)
+    return fail(RN_ERR_UNSUPPORTED, "bn_stats_noalloc: device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lock(g_noalloc_mu);
+  if (g_noalloc_dev_ptr[dev] == nullptr) {
+    void* p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_bn_noalloc_scratch);
+    if (e != cudaSuccess || p == nullptr)
+      return fail(RN_ERR_CUDA, "bn_stats_noalloc: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+    g_noalloc_dev_ptr[dev] = p;
+  }
+  *out = g_noalloc_dev_ptr[dev];
+  return RN_OK;
+}
+
+template <typename T>
+static int bn_stats_noalloc_launch(const void* x, const void* addend, void* sum_out, int64_t M, int C, float eps,
+                                   float decay, int unbiased, float* mean, float* rstd, float* mm, float* mv,
+                                   cudaStream_t st) {
+  int rc = check_bn_args<T>(M, C);
+  if (rc) return rc;
+  BnLayout L = bn_layout<T>(M, C, 4);
+  // shrink the number of row CTAs until the partial sums fit the fixed array
+  const size_t per_cta = (size_t)2 * L.CW * Vec<T>::N * sizeof(float);
+  const size_t max_g = (RN_BN_NOALLOC_SCRATCH_BYTES - 256) / ((size_t)L.gridY * per_cta);
+  if (max_g < 1) return fail(RN_ERR_INVALID, "bn_stats_noalloc: C=%d does not fit the static scratch", C);
+  if ((size_t)L.G > max_g) L.G = (int)max_g;
+  void* base = nullptr;
+  rc = bn_noalloc_scratch_ptr(&base);
+  if (rc) return rc;
+  cudaError_t e = cudaMemsetAsync(base, 0, 256, st);   // ticket counters must start at zero
+  if (e != cudaSuccess) return fail(RN_ERR_CUDA, "bn_stats_noalloc: cudaMemsetAsync: %s", cudaGetErrorString(e));
+  unsigned* counters = (unsigned*)base;
+  float* partials = (float*)((char*)base + 256);
+  dim3 grid(L.G, L.gridY);
+  const size_t smem = (size_t)L.RY * L.CW * 2 * Vec<T>::N * sizeof(float);
+  if (addend != nullptr)
+    bn_stats_kernel<T, true><<<grid, BN_THREADS, smem, st>>>((const T*)x, (const T*)addend, (T*)sum_out, M, C, L, eps,
+                                                             decay, unbiased, mean, rstd, mm, mv, counters, partials);
+  else
+    bn_stats_kernel<T, false><<<grid, BN_THREADS, smem, st>>>((const T*)x, nullptr, nullptr, M, C, L, eps, decay,
+                                                              unbiased, mean, rstd, mm, mv, counters, partials);
+  return check_launch("bn_stats_kernel (static scratch)");
+}
+}  // namespace rn
+
+extern "C" int rn_bn_stats_fwd_noalloc(const void* x, const void* addend, void* sum_out, int64_t M, int32_t C,
+                                       int32_t dtype, float eps, float decay, int32_t unbiased, float* mean,
+                                       float* rstd, float* moving_mean, float* moving_var, void* stream) {
+  RN_REQUIRE(x && mean && rstd, "bn_stats_noalloc: NULL pointer");
+  RN_REQUIRE((moving_mean == nullptr) == (moving_var == nullptr),
+             "bn_stats_noalloc: moving_mean/var must both be set or NULL");
+  RN_REQUIRE(addend == nullptr || sum_out != nullptr, "bn_stats_noalloc: addend given but sum_out is NULL");
+  if (C > RN_BN_NOALLOC_MAX_C)
+    return fail(RN_ERR_INVALID, "bn_stats_noalloc: C=%d exceeds the static-scratch limit of %d channels; use "
+                "rn_bn_stats_fwd with caller scratch", C, RN_BN_NOALLOC_MAX_C);
+  if (dtype == RN_F32)
+    return bn_stats_noalloc_launch<float>(x, addend, sum_out, M, C, eps, decay, unbiased, mean, rstd, moving_mean,
+                                          moving_var, as_stream(stream));
+  if (dtype == RN_BF16)
+    return bn_stats_noalloc_launch<__nv_bfloat16>(x, addend, sum_out, M, C, eps, decay, unbiased, mean, rstd,
+                                                  moving_mean, moving_var, as_stream(stream));
+  return fail(RN_ERR_INVALID, "bn_stats_noalloc: bad dtype %d", dtype);
+}

@@ -107,6 +107,21 @@ size_t rn_bn_scratch_bytes(int64_t M, int32_t C);
 int rn_bn_stats_fwd(const void* x, const void* addend, void* sum_out, int64_t M, int32_t C, int32_t dtype,
                     float eps, float decay, int32_t unbiased, float* mean, float* rstd,
                     float* moving_mean, float* moving_var, void* scratch, size_t scratch_bytes, void* stream);
+/* Same statistics pass for hosts that cannot supply scratch memory — no counterpart in the
+ * reference; it exists for embedders, e.g. a plugin living inside a TensorFlow-1.x process whose
+ * allocator has already taken (almost) all device memory so that cudaMalloc fails, or a loop that
+ * must never hit cudaMalloc's device-wide synchronisation.  The partial sums and ticket counters
+ * live in a 512 KiB device array that is part of the library image (held by every GPU that loads the
+ * library until the process exits).  The entry point performs no allocation of any kind.
+ * Its first call on a device looks the array's address up (cudaGetSymbolAddress, that device
+ * current): make that call during set-up, before starting any stream capture.  All calls on a
+ * device share the array; counters are re-zeroed at the start of each call, but calls that overlap
+ * on the GPU race with each other — keep them ordered.  C is limited to 4096 channels (any M);
+ * beyond that the call fails with RN_ERR_INVALID and rn_bn_stats_fwd must be used.
+ * Arguments and results are those of rn_bn_stats_fwd without the scratch pair. */
+int rn_bn_stats_fwd_noalloc(const void* x, const void* addend, void* sum_out, int64_t M, int32_t C, int32_t dtype,
+                            float eps, float decay, int32_t unbiased, float* mean, float* rstd,
+                            float* moving_mean, float* moving_var, void* stream);
 /* y = act(gamma * (x - mean) * rstd + beta), act(v) = v < 0 ? leak * v : v.
  * If stats_are_moving != 0, `rstd` holds a VARIANCE and rstd = 1/sqrt(var + eps) is formed on the
  * fly (inference mode: mean/var are the moving statistics). */
