@@ -1,0 +1,83 @@
+"""tcgen05 / TMA / TMEM implicit-GEMM convolution (bf16) through the plan API of the C ABI, against
+the CPU oracle on the same bf16-rounded inputs.  Tolerance: the north star's 2e-2 for bf16 mode
+(measured error is the bf16 output rounding, ~4e-3)."""
+import ctypes as C
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from util import rel_err, dev, stream, lib, check, ptr, ConvDesc, RN_BF16  # noqa: E402
+from oracle import resnet_oracle as ro  # noqa: E402
+
+BF = torch.bfloat16
+
+CASES = [
+    # N, H, W, Cin, Cout, k, stride, pad
+    (4, 8, 8, 64, 64, 1, 1, 0),        # plain GEMM, one k-chunk
+    (4, 8, 8, 64, 256, 1, 1, 0),       # N = 256 tile
+    (2, 16, 16, 256, 64, 1, 1, 0),     # 4 k-chunks
+    (4, 16, 16, 64, 64, 3, 1, 1),      # 9 taps, halo zero fill
+    (8, 14, 14, 256, 256, 3, 1, 1),    # C3 stage-3 shape
+    (6, 7, 7, 512, 512, 3, 1, 1),      # C3 stage-4 shape: box 7x7x2 (98 of 128 rows), ragged N
+    (2, 56, 56, 64, 64, 3, 1, 1),      # C3 stage-1 shape
+    (4, 32, 32, 16, 16, 3, 1, 1),      # CIFAR: 32-byte rows (SW32)
+    (4, 16, 16, 32, 32, 3, 1, 1),      # CIFAR: 64-byte rows (SW64)
+    (3, 9, 11, 24, 48, 3, 1, 1),       # ragged everything: K tail zero-filled by TMA
+    (2, 32, 32, 160, 160, 3, 1, 1),    # WRN width: N = 160 tile, 32-channel store groups, K tail
+    (2, 8, 8, 2048, 512, 1, 1, 0),     # deep K
+]
+
+
+def _weights(w):
+    k, _, cin, cout = w.shape
+    wf = torch.empty(k * k * cout * cin, dtype=BF, device="cuda")
+    wd = torch.empty(k * k * cin * cout, dtype=BF, device="cuda")
+    W32 = dev(w.float())
+    check(lib.rn_weights_to_bf16(ptr(W32), k, cin, cout, ptr(wf), ptr(wd), stream()), "weights_to_bf16")
+    torch.cuda.synchronize()
+    assert torch.equal(wd.view(k, k, cin, cout).cpu(), w.to(BF))
+    assert torch.equal(wf.view(k, k, cout, cin).cpu(), w.to(BF).permute(0, 1, 3, 2))
+    return wf, wd
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_convtc_fprop_and_dgrad(case):
+    N, H, W, Cin, Cout, k, s, pad = case
+    Ho, Wo = H, W
+    g = torch.Generator().manual_seed(sum(case))
+    x = torch.randn(N, H, W, Cin, generator=g).to(BF)
+    w = (torch.randn(k, k, Cin, Cout, generator=g) / (k * k * Cin) ** 0.5).to(BF)
+    dy = torch.randn(N, Ho, Wo, Cout, generator=g).to(BF)
+    net = ro.Net(dtype=torch.float64, params={"w": w.double().numpy()})
+    xv = ro.Var(x.double())
+    yv = net.conv2d(xv, "w", k, Cin, Cout, s, pad, (Ho, Wo), None, "y")
+    yv.grad = dy.double()
+    net.backward()
+    d = ConvDesc(N, H, W, Cin, Ho, Wo, Cout, k, s, pad, RN_BF16)
+    assert lib.rn_convtc_supported(C.byref(d), 0) == 1
+    kinds = (0, 1) if lib.rn_convtc_supported(C.byref(d), 1) else (0,)    # 24 output columns cannot form a UMMA N tile
+    assert len(kinds) == 2 or Cin % 16
+    wf, wd = _weights(w)
+    X, DY = dev(x), dev(dy)
+    Y = torch.full((N, Ho, Wo, Cout), float("nan"), dtype=BF, device="cuda")
+    DX = torch.full((N, H, W, Cin), float("nan"), dtype=BF, device="cuda")
+    for kind, a, b, out, want in ((0, X, wf, Y, yv.val), (1, DY, wd, DX, xv.grad)):
+        if kind not in kinds:
+            continue
+        plan = C.c_void_p()
+        check(lib.rn_convtc_plan_create(C.byref(d), kind, ptr(a), ptr(b), ptr(out), None, 0, C.byref(plan)), "plan")
+        for _ in range(2):      # run twice: barriers / TMEM are per-launch state
+            check(lib.rn_convtc_run(plan, 0.0, stream()), "run")
+        torch.cuda.synchronize()
+        lib.rn_convtc_plan_destroy(plan)
+        assert torch.isfinite(out.float()).all(), "unwritten outputs (kind %d)" % kind
+        assert rel_err(out.float(), want) < 2e-2, ("kind", kind)
+
+
+def test_convtc_rejects_unsupported():
+    d = ConvDesc(2, 8, 8, 3, 8, 8, 16, 3, 1, 1, RN_BF16)       # 3 input channels: 6-byte rows cannot be TMA'd
+    assert lib.rn_convtc_supported(C.byref(d), 0) == 0
+    d = ConvDesc(2, 8, 8, 64, 8, 8, 64, 3, 1, 1, 0)            # fp32 verification mode stays on CUDA cores
+    assert lib.rn_convtc_supported(C.byref(d), 0) == 0
