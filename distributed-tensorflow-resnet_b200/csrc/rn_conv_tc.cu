@@ -203,6 +203,183 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const __grid_con
   if (warp == 1) tmem_dealloc(tmem_base, p.tmem_cols);
 }
 
+
+// ------------------------------------------------------------------------------------------
+// wgrad:  dW[(tap, ci), co] = sum_pixels  X[pixel shifted by tap, ci] * dY[pixel, co]
+// Both operands have the reduction (pixel) dimension as their STRIDED dimension in NHWC, i.e. they
+// are "MN-major" UMMA operands: a TMA box (64 channels x KP pixels) lands as KP rows of 128 bytes,
+// which is exactly the canonical 128B-swizzled MN-major layout (8 pixel rows per 1024-byte atom,
+// SBO = 1024; consecutive 64-channel boxes LBO apart).  No transpose pass over HBM.
+// A CTA accumulates up to four 128 x BLOCK_N fp32 tiles in tensor memory (512 columns) that share
+// the dY tile: A rows are (tap, 64-channel block) pairs, so for 64-channel layers two taps ride in
+// one M = 128 instruction.  Split-K over pixel tiles; partial tiles go to caller scratch and are
+// summed in a fixed order (deterministic).
+// ------------------------------------------------------------------------------------------
+struct TcWgradParams {
+  CUtensorMap x_map[4];
+  CUtensorMap dy_map;
+  float* partial;                 // [splits][taps*Cin][Cout]
+  int Cin, Cout, taps, cin_blocks, RB;
+  int acc;                        // accumulators per CTA; row blocks per CTA = 2 * acc
+  int row_groups, block_n, n_tiles;
+  int PW, PH, PN, tiles_w, tiles_h, tiles_n, k_tiles;
+  int splits, tiles_per_split;
+  int kp, stages;
+  uint32_t box_bytes, stage_bytes, tmem_cols;
+  int8_t tap_map[TC_MAX_TAPS], tap_dw[TC_MAX_TAPS], tap_dh[TC_MAX_TAPS];
+};
+
+__global__ void __launch_bounds__(TC_THREADS, 1) conv_wgrad_tc_kernel(const __grid_constant__ TcWgradParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t base_u32 = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  uint8_t* smem = smem_raw + (base_u32 - smem_u32(smem_raw));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + (size_t)p.stages * p.stage_bytes);
+  uint64_t* full = bars;
+  uint64_t* empty = bars + p.stages;
+  uint64_t* tfull = bars + 2 * p.stages;
+  uint64_t* tempty = tfull + 1;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 1);
+  const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
+  if (warp == 0 && lane == 0) {
+    for (int i = 0; i < p.stages; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+    mbar_init(tfull, 1);
+    mbar_init(tempty, 4);
+    fence_barrier_init();
+    tma_prefetch_desc(&p.x_map[0]);
+    tma_prefetch_desc(&p.dy_map);
+  }
+  if (warp == 1) {
+    tmem_alloc(tmem_slot, p.tmem_cols);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const int total = p.row_groups * p.n_tiles * p.splits;
+  const int rb_per_cta = 2 * p.acc;
+  const int nb = p.block_n / 64;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int it = blockIdx.x; it < total; it += gridDim.x) {
+        const int z = it % p.splits;
+        const int nt = (it / p.splits) % p.n_tiles;
+        const int rg = it / (p.splits * p.n_tiles);
+        int valid = p.RB - rg * rb_per_cta;
+        if (valid > rb_per_cta) valid = rb_per_cta;
+        const int kt_end = min((z + 1) * p.tiles_per_split, p.k_tiles);
+        for (int kt = z * p.tiles_per_split; kt < kt_end; ++kt) {
+          int q = kt;
+          const int w0 = (q % p.tiles_w) * p.PW;
+          q /= p.tiles_w;
+          const int h0 = (q % p.tiles_h) * p.PH;
+          const int n0 = (q / p.tiles_h) * p.PN;
+          mbar_wait(&empty[stage], phase ^ 1);
+          uint8_t* sa = smem + (size_t)stage * p.stage_bytes;
+          mbar_expect_tx(&full[stage], (uint32_t)(valid + nb) * p.box_bytes);
+          for (int j = 0; j < valid; ++j) {
+            const int rb = rg * rb_per_cta + j;
+            const int tap = rb / p.cin_blocks, cb = rb - tap * p.cin_blocks;
+            tma_load_4d(sa + (size_t)j * p.box_bytes, &p.x_map[p.tap_map[tap]], &full[stage], cb * 64,
+                        w0 + p.tap_dw[tap], h0 + p.tap_dh[tap], n0);
+          }
+          uint8_t* sbm = sa + (size_t)rb_per_cta * p.box_bytes;
+          for (int j = 0; j < nb; ++j)
+            tma_load_4d(sbm + (size_t)j * p.box_bytes, &p.dy_map, &full[stage], nt * p.block_n + j * 64, w0, h0, n0);
+          if (++stage == p.stages) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      const uint32_t idesc = make_idesc_bf16(TC_BLOCK_M, p.block_n, 1, 1);
+      const int ksteps = p.kp / 16;
+      int stage = 0;
+      uint32_t phase = 0, tphase = 0;
+      for (int it = blockIdx.x; it < total; it += gridDim.x) {
+        const int z = it % p.splits;
+        const int rg = it / (p.splits * p.n_tiles);
+        int valid = p.RB - rg * rb_per_cta;
+        if (valid > rb_per_cta) valid = rb_per_cta;
+        const int nacc = (valid + 1) / 2;
+        mbar_wait(tempty, tphase ^ 1);
+        tc_fence_after();
+        const int kt_begin = z * p.tiles_per_split, kt_end = min((z + 1) * p.tiles_per_split, p.k_tiles);
+        for (int kt = kt_begin; kt < kt_end; ++kt) {
+          mbar_wait(&full[stage], phase);
+          tc_fence_after();
+          const uint32_t a_addr = base_u32 + (uint32_t)stage * p.stage_bytes;
+          const uint32_t b_addr = a_addr + (uint32_t)rb_per_cta * p.box_bytes;
+          for (int a = 0; a < nacc; ++a) {
+            for (int ks = 0; ks < ksteps; ++ks) {
+              const uint64_t da = make_smem_desc(a_addr + (uint32_t)(2 * a) * p.box_bytes + ks * 2048, p.box_bytes, 1024, 2);
+              const uint64_t db = make_smem_desc(b_addr + ks * 2048, p.box_bytes, 1024, 2);
+              umma_bf16(tmem_base + (uint32_t)(a * p.block_n), da, db, idesc, (kt > kt_begin || ks > 0) ? 1u : 0u);
+            }
+          }
+          umma_commit(&empty[stage]);
+          if (++stage == p.stages) { stage = 0; phase ^= 1; }
+        }
+        umma_commit(tfull);
+        tphase ^= 1;
+      }
+    }
+  } else {
+    const int quad = warp & 3;
+    const int row = quad * 32 + lane;
+    uint32_t tphase = 0;
+    const int64_t rows_total = (int64_t)p.taps * p.Cin;
+    for (int it = blockIdx.x; it < total; it += gridDim.x) {
+      const int z = it % p.splits;
+      const int nt = (it / p.splits) % p.n_tiles;
+      const int rg = it / (p.splits * p.n_tiles);
+      mbar_wait(tfull, tphase);
+      tc_fence_after();
+      for (int a = 0; a < p.acc; ++a) {
+        const int rb = rg * rb_per_cta + 2 * a + (row >> 6);
+        if (rb - (row >> 6) >= p.RB) break;                       // warp-uniform: this accumulator was not computed
+        const bool ok = rb < p.RB;
+        const int tap = ok ? rb / p.cin_blocks : 0;
+        const int cb = rb - tap * p.cin_blocks;
+        const int64_t grow = (int64_t)tap * p.Cin + cb * 64 + (row & 63);
+        float* dst = p.partial + ((int64_t)z * rows_total + grow) * p.Cout + (int64_t)nt * p.block_n;
+        const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(a * p.block_n);
+        for (int c0 = 0; c0 < p.block_n; c0 += 16) {
+          uint32_t v[16];
+          tmem_ld_32x16(taddr + c0, v);
+          tmem_ld_wait();
+          if (ok) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+              *reinterpret_cast<uint4*>(dst + c0 + 4 * i) = make_uint4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(tempty);
+      tphase ^= 1;
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, p.tmem_cols);
+}
+
+__global__ void wgrad_reduce_kernel(const float* __restrict__ part, float* __restrict__ out, int64_t n4, int splits) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
+    float4 s = reinterpret_cast<const float4*>(part)[i];
+    for (int z = 1; z < splits; ++z) {
+      const float4 t = reinterpret_cast<const float4*>(part)[(int64_t)z * n4 + i];
+      s.x += t.x; s.y += t.y; s.z += t.z; s.w += t.w;
+    }
+    reinterpret_cast<float4*>(out)[i] = s;
+  }
+}
+
 // ------------------------------------------------------------------------------------------
 // weight re-layout: fp32 HWIO -> bf16 [tap][Cout][Cin] (fprop B operand) and bf16 [tap][Cin][Cout] (dgrad)
 // ------------------------------------------------------------------------------------------
@@ -283,6 +460,99 @@ static int choose_block_n(int ncols) {
   return 0;
 }
 
+
+// Power-of-two pixel box with exactly `kp` pixels (the K tile of wgrad must be completely written by
+// TMA: out-of-image pixels are zero-filled, but rows the box does not cover would be stale smem).
+static void choose_k_box(int Wo, int Ho, int N, int kp, int* PW, int* PH, int* PN) {
+  long best = -1;
+  int bw = 1, bh = 1, bn = kp;
+  for (int w = 1; w <= kp; w <<= 1)
+    for (int h = 1; w * h <= kp; h <<= 1) {
+      const int n = kp / (w * h);
+      const long tiles = (long)((Wo + w - 1) / w) * ((Ho + h - 1) / h) * ((N + n - 1) / n);
+      if (best < 0 || tiles < best || (tiles == best && w > bw)) { best = tiles; bw = w; bh = h; bn = n; }
+    }
+  *PW = bw; *PH = bh; *PN = bn;
+}
+
+// Activation tensor map(s).  stride 1: one map of [N,H,W,C].  stride 2: one map per (row, col) parity
+// of the input — a strided sub-view with base offset (ph*W + pw)*C and doubled W/H strides — so that a
+// tap (r, s) reads a dense box of view (r-pad)&1, (s-pad)&1 at offset floor((r-pad)/2), floor((s-pad)/2).
+static int encode_activation_maps(CUtensorMap* maps, const void* base, int C, int W, int H, int N, int stride,
+                                  const uint32_t* box, int row_bytes) {
+  if (stride == 1) {
+    const uint64_t dims[4] = {(uint64_t)C, (uint64_t)W, (uint64_t)H, (uint64_t)N};
+    const uint64_t str[3] = {(uint64_t)C * 2, (uint64_t)W * C * 2, (uint64_t)H * W * C * 2};
+    return encode_map(&maps[0], base, 4, dims, str, box, row_bytes, "activation");
+  }
+  for (int ph = 0; ph < 2; ++ph)
+    for (int pw = 0; pw < 2; ++pw) {
+      const int W2 = (W - pw + 1) / 2, H2 = (H - ph + 1) / 2;
+      if (W2 <= 0 || H2 <= 0) continue;
+      const uint64_t dims[4] = {(uint64_t)C, (uint64_t)W2, (uint64_t)H2, (uint64_t)N};
+      const uint64_t str[3] = {(uint64_t)2 * C * 2, (uint64_t)2 * W * C * 2, (uint64_t)H * W * C * 2};
+      const char* b = (const char*)base + ((size_t)ph * W + pw) * C * 2;
+      int rc = encode_map(&maps[ph * 2 + pw], b, 4, dims, str, box, row_bytes, "activation parity view");
+      if (rc) return rc;
+    }
+  return RN_OK;
+}
+
+// tap (r, s) of a forward-style gather at `stride`: which map and which box offset
+static void forward_tap(int r, int s, int pad, int stride, int8_t* map, int8_t* dw, int8_t* dh) {
+  if (stride == 1) { *map = 0; *dw = (int8_t)(s - pad); *dh = (int8_t)(r - pad); return; }
+  const int ah = r - pad, aw = s - pad;
+  const int ph = ah & 1, pw = aw & 1;
+  *map = (int8_t)(ph * 2 + pw);
+  *dh = (int8_t)((ah - ph) / 2);
+  *dw = (int8_t)((aw - pw) / 2);
+}
+
+struct WgradShape {
+  int block_n, n_tiles, acc, cin_blocks, RB, row_groups, kp, stages, PW, PH, PN, tiles_w, tiles_h, tiles_n, k_tiles;
+  int splits, tiles_per_split;
+  uint32_t box_bytes, stage_bytes, tmem_cols;
+  size_t smem, scratch;
+};
+
+static bool wgrad_shape(const rn_conv_desc* d, WgradShape* w) {
+  if (d->Cin % 64 || d->Cout % 64) return false;
+  w->block_n = d->Cout % 256 == 0 ? 256 : (d->Cout % 128 == 0 ? 128 : 64);
+  w->n_tiles = d->Cout / w->block_n;
+  w->acc = 512 / w->block_n;
+  if (w->acc > 4) w->acc = 4;
+  w->cin_blocks = d->Cin / 64;
+  w->RB = d->k * d->k * w->cin_blocks;
+  if (w->acc > (w->RB + 1) / 2) w->acc = (w->RB + 1) / 2;
+  w->row_groups = (w->RB + 2 * w->acc - 1) / (2 * w->acc);
+  const int boxes = 2 * w->acc + w->block_n / 64;
+  w->kp = 64;
+  if ((size_t)boxes * 64 * 128 * 3 > 200 * 1024) w->kp = 32;
+  w->box_bytes = (uint32_t)w->kp * 128;
+  w->stage_bytes = (uint32_t)boxes * w->box_bytes;
+  w->stages = (int)((220 * 1024) / w->stage_bytes);
+  if (w->stages > 8) w->stages = 8;
+  if (w->stages < 2) return false;
+  w->smem = (size_t)w->stages * w->stage_bytes + 2048;
+  uint32_t cols = 32;
+  while (cols < (uint32_t)(w->acc * w->block_n)) cols <<= 1;
+  w->tmem_cols = cols;
+  choose_k_box(d->Wo, d->Ho, d->N, w->kp, &w->PW, &w->PH, &w->PN);
+  w->tiles_w = (d->Wo + w->PW - 1) / w->PW;
+  w->tiles_h = (d->Ho + w->PH - 1) / w->PH;
+  w->tiles_n = (d->N + w->PN - 1) / w->PN;
+  w->k_tiles = w->tiles_w * w->tiles_h * w->tiles_n;
+  const int base = w->row_groups * w->n_tiles;
+  int splits = (RN_NUM_SMS + base - 1) / base;
+  const int max_splits = w->k_tiles / 8 > 0 ? w->k_tiles / 8 : 1;
+  if (splits > max_splits) splits = max_splits;
+  if (splits < 1) splits = 1;
+  w->tiles_per_split = (w->k_tiles + splits - 1) / splits;
+  w->splits = (w->k_tiles + w->tiles_per_split - 1) / w->tiles_per_split;
+  w->scratch = w->splits > 1 ? (size_t)w->splits * d->k * d->k * d->Cin * d->Cout * sizeof(float) : 0;
+  return true;
+}
+
 }  // namespace rn
 
 using namespace rn;
@@ -290,35 +560,40 @@ using namespace rn;
 struct rn_convtc_plan {
   int kind;
   TcConvParams p;
+  TcWgradParams w;
   int grid;
   size_t smem;
+  float* dw;
+  int64_t dw_elems;
 };
 
 extern "C" int rn_convtc_supported(const rn_conv_desc* d, int kind) {
   if (!d || d->dtype != RN_BF16) return 0;
-  if (kind != 0 && kind != 1) return 0;
-  if (d->stride != 1) return 0;
-  if (d->k * d->k > TC_MAX_TAPS) return 0;
+  if (kind < 0 || kind > 2) return 0;
+  if (d->stride != 1 && d->stride != 2) return 0;
+  if (d->k * d->k > TC_MAX_TAPS || d->pad > 8) return 0;
   if (d->Cin % 8 || d->Cout % 8) return 0;
+  if (kind == 2) {
+    WgradShape w;
+    return wgrad_shape(d, &w) ? 1 : 0;
+  }
+  if (kind == 1 && d->stride != 1) return 0;
   const int cred = kind == 0 ? d->Cin : d->Cout;
   const int ncols = kind == 0 ? d->Cout : d->Cin;
   if (cred < 16 || choose_block_n(ncols) == 0) return 0;
-  if (d->pad > 8 || d->k > 2 * d->pad + 1 + 8) return 0;
   return 1;
 }
 
-extern "C" size_t rn_convtc_scratch_bytes(const rn_conv_desc*, int) { return 0; }
+extern "C" size_t rn_convtc_scratch_bytes(const rn_conv_desc* d, int kind) {
+  if (!d || kind != 2) return 0;
+  WgradShape w;
+  if (!wgrad_shape(d, &w)) return 0;
+  return w.scratch;
+}
 
-extern "C" int rn_convtc_plan_create(const rn_conv_desc* d, int kind, const void* a, const void* b, void* out,
-                                     void* scratch, size_t scratch_bytes, rn_convtc_plan** plan) {
-  (void)scratch; (void)scratch_bytes;
-  RN_REQUIRE(d && a && b && out && plan, "convtc_plan_create: NULL pointer");
-  if (!rn_convtc_supported(d, kind)) return fail(RN_ERR_UNSUPPORTED, "convtc: shape/kind not supported");
-  RN_REQUIRE((((uintptr_t)a | (uintptr_t)b | (uintptr_t)out) & 15) == 0, "convtc: pointers must be 16-byte aligned");
-  rn_convtc_plan* pl = new rn_convtc_plan();
-  pl->kind = kind;
+static int create_gemm_plan(const rn_conv_desc* d, int kind, const void* a, const void* b, void* out,
+                            rn_convtc_plan* pl) {
   TcConvParams& p = pl->p;
-  memset(&p, 0, sizeof(p));
   // GEMM view: rows = pixels of the OUTPUT tensor of this GEMM, reduction over (tap, cred), columns = ncols
   const int cred = kind == 0 ? d->Cin : d->Cout;
   const int ncols = kind == 0 ? d->Cout : d->Cin;
@@ -337,10 +612,9 @@ extern "C" int rn_convtc_plan_create(const rn_conv_desc* d, int kind, const void
   for (int r = 0; r < d->k; ++r)
     for (int s = 0; s < d->k; ++s) {
       const int t = r * d->k + s;
-      p.tap_map[t] = 0;
       p.tap_b[t] = (int8_t)t;
-      if (kind == 0) { p.tap_dw[t] = (int8_t)(s - d->pad); p.tap_dh[t] = (int8_t)(r - d->pad); }
-      else           { p.tap_dw[t] = (int8_t)(d->pad - s); p.tap_dh[t] = (int8_t)(d->pad - r); }
+      if (kind == 0) forward_tap(r, s, d->pad, d->stride, &p.tap_map[t], &p.tap_dw[t], &p.tap_dh[t]);
+      else { p.tap_map[t] = 0; p.tap_dw[t] = (int8_t)(d->pad - s); p.tap_dh[t] = (int8_t)(d->pad - r); }
     }
   const int row_bytes = p.kc * 2;
   const uint32_t box_rows = (uint32_t)(p.BW * p.BH * p.BN);
@@ -354,35 +628,81 @@ extern "C" int rn_convtc_plan_create(const rn_conv_desc* d, int kind, const void
   const size_t budget = 227 * 1024;
   int stages = (int)((budget - fixed) / (p.a_bytes + p.b_bytes));
   if (stages > 8) stages = 8;
-  if (stages < 2) { delete pl; return fail(RN_ERR_UNSUPPORTED, "convtc: tile does not fit shared memory"); }
+  if (stages < 2) return fail(RN_ERR_UNSUPPORTED, "convtc: tile does not fit shared memory");
   p.stages = stages;
   pl->smem = fixed + (size_t)stages * (p.a_bytes + p.b_bytes);
   int rc;
-  {  // activation: dims (C, W, H, N)
-    const uint64_t dims[4] = {(uint64_t)cred, (uint64_t)aW, (uint64_t)aH, (uint64_t)d->N};
-    const uint64_t str[3] = {(uint64_t)cred * 2, (uint64_t)aW * cred * 2, (uint64_t)aH * aW * cred * 2};
-    const uint32_t box[4] = {(uint32_t)p.kc, (uint32_t)p.BW, (uint32_t)p.BH, (uint32_t)p.BN};
-    rc = encode_map(&p.a_map[0], a, 4, dims, str, box, row_bytes, "activation");
-    if (rc) { delete pl; return rc; }
-  }
+  const uint32_t abox[4] = {(uint32_t)p.kc, (uint32_t)p.BW, (uint32_t)p.BH, (uint32_t)p.BN};
+  rc = encode_activation_maps(p.a_map, a, cred, aW, aH, d->N, kind == 0 ? d->stride : 1, abox, row_bytes);
+  if (rc) return rc;
   {  // weights: dims (cred, ncols, taps)
     const uint64_t dims[3] = {(uint64_t)cred, (uint64_t)ncols, (uint64_t)p.taps};
     const uint64_t str[2] = {(uint64_t)cred * 2, (uint64_t)ncols * cred * 2};
     const uint32_t box[3] = {(uint32_t)p.kc, (uint32_t)p.block_n, 1u};
     rc = encode_map(&p.b_map, b, 3, dims, str, box, row_bytes, "weights");
-    if (rc) { delete pl; return rc; }
+    if (rc) return rc;
   }
   {  // output: dims (ncols, W, H, N)
     const uint64_t dims[4] = {(uint64_t)ncols, (uint64_t)oW, (uint64_t)oH, (uint64_t)d->N};
     const uint64_t str[3] = {(uint64_t)ncols * 2, (uint64_t)oW * ncols * 2, (uint64_t)oH * oW * ncols * 2};
     const uint32_t box[4] = {(uint32_t)p.gw, (uint32_t)p.BW, (uint32_t)p.BH, (uint32_t)p.BN};
     rc = encode_map(&p.o_map, out, 4, dims, str, box, p.gw * 2, "output");
-    if (rc) { delete pl; return rc; }
+    if (rc) return rc;
   }
   const long total = (long)p.tiles_w * p.tiles_h * p.tiles_n * p.n_tiles;
   pl->grid = (int)(total < RN_NUM_SMS ? total : RN_NUM_SMS);
   cudaError_t e = cudaFuncSetAttribute(conv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024));
-  if (e != cudaSuccess) { delete pl; return fail(RN_ERR_CUDA, "convtc: cudaFuncSetAttribute: %s", cudaGetErrorString(e)); }
+  if (e != cudaSuccess) return fail(RN_ERR_CUDA, "convtc: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+  return RN_OK;
+}
+
+static int create_wgrad_plan(const rn_conv_desc* d, const void* x, const void* dy, void* dw, void* scratch,
+                             size_t scratch_bytes, rn_convtc_plan* pl) {
+  WgradShape ws;
+  if (!wgrad_shape(d, &ws)) return fail(RN_ERR_UNSUPPORTED, "convtc wgrad: shape not supported");
+  if (ws.scratch > 0 && (scratch == nullptr || scratch_bytes < ws.scratch))
+    return fail(RN_ERR_SCRATCH, "convtc wgrad: scratch %zu < %zu bytes", scratch_bytes, ws.scratch);
+  TcWgradParams& w = pl->w;
+  w.Cin = d->Cin; w.Cout = d->Cout; w.taps = d->k * d->k; w.cin_blocks = ws.cin_blocks; w.RB = ws.RB;
+  w.acc = ws.acc; w.row_groups = ws.row_groups; w.block_n = ws.block_n; w.n_tiles = ws.n_tiles;
+  w.PW = ws.PW; w.PH = ws.PH; w.PN = ws.PN; w.tiles_w = ws.tiles_w; w.tiles_h = ws.tiles_h; w.tiles_n = ws.tiles_n;
+  w.k_tiles = ws.k_tiles; w.splits = ws.splits; w.tiles_per_split = ws.tiles_per_split; w.kp = ws.kp;
+  w.stages = ws.stages; w.box_bytes = ws.box_bytes; w.stage_bytes = ws.stage_bytes; w.tmem_cols = ws.tmem_cols;
+  w.partial = ws.splits > 1 ? (float*)scratch : (float*)dw;
+  for (int r = 0; r < d->k; ++r)
+    for (int s = 0; s < d->k; ++s)
+      forward_tap(r, s, d->pad, d->stride, &w.tap_map[r * d->k + s], &w.tap_dw[r * d->k + s], &w.tap_dh[r * d->k + s]);
+  const uint32_t box[4] = {64u, (uint32_t)ws.PW, (uint32_t)ws.PH, (uint32_t)ws.PN};
+  int rc = encode_activation_maps(w.x_map, x, d->Cin, d->W, d->H, d->N, d->stride, box, 128);
+  if (rc) return rc;
+  {
+    const uint64_t dims[4] = {(uint64_t)d->Cout, (uint64_t)d->Wo, (uint64_t)d->Ho, (uint64_t)d->N};
+    const uint64_t str[3] = {(uint64_t)d->Cout * 2, (uint64_t)d->Wo * d->Cout * 2, (uint64_t)d->Ho * d->Wo * d->Cout * 2};
+    rc = encode_map(&w.dy_map, dy, 4, dims, str, box, 128, "dy");
+    if (rc) return rc;
+  }
+  const long total = (long)ws.row_groups * ws.n_tiles * ws.splits;
+  pl->grid = (int)(total < RN_NUM_SMS ? total : RN_NUM_SMS);
+  pl->smem = ws.smem;
+  pl->dw = (float*)dw;
+  pl->dw_elems = (int64_t)d->k * d->k * d->Cin * d->Cout;
+  cudaError_t e = cudaFuncSetAttribute(conv_wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024));
+  if (e != cudaSuccess) return fail(RN_ERR_CUDA, "convtc: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+  return RN_OK;
+}
+
+extern "C" int rn_convtc_plan_create(const rn_conv_desc* d, int kind, const void* a, const void* b, void* out,
+                                     void* scratch, size_t scratch_bytes, rn_convtc_plan** plan) {
+  RN_REQUIRE(d && a && b && out && plan, "convtc_plan_create: NULL pointer");
+  if (!rn_convtc_supported(d, kind)) return fail(RN_ERR_UNSUPPORTED, "convtc: shape/kind not supported");
+  RN_REQUIRE((((uintptr_t)a | (uintptr_t)b | (uintptr_t)out) & 15) == 0, "convtc: pointers must be 16-byte aligned");
+  rn_convtc_plan* pl = new rn_convtc_plan();
+  memset(&pl->p, 0, sizeof(pl->p));
+  memset(&pl->w, 0, sizeof(pl->w));
+  pl->kind = kind;
+  const int rc = kind == 2 ? create_wgrad_plan(d, a, b, out, scratch, scratch_bytes, pl)
+                           : create_gemm_plan(d, kind, a, b, out, pl);
+  if (rc) { delete pl; return rc; }
   *plan = pl;
   return RN_OK;
 }
@@ -390,6 +710,17 @@ extern "C" int rn_convtc_plan_create(const rn_conv_desc* d, int kind, const void
 extern "C" int rn_convtc_run(rn_convtc_plan* plan, float beta, void* stream) {
   RN_REQUIRE(plan, "convtc_run: NULL plan");
   if (beta != 0.f) return fail(RN_ERR_UNSUPPORTED, "convtc_run: accumulation (beta=1) is not supported by this kernel");
+  if (plan->kind == 2) {
+    conv_wgrad_tc_kernel<<<plan->grid, TC_THREADS, plan->smem, as_stream(stream)>>>(plan->w);
+    int rc = check_launch("conv_wgrad_tc_kernel");
+    if (rc) return rc;
+    if (plan->w.splits > 1) {
+      const int64_t n4 = plan->dw_elems / 4;
+      wgrad_reduce_kernel<<<grid_for(n4, 256), 256, 0, as_stream(stream)>>>(plan->w.partial, plan->dw, n4, plan->w.splits);
+      rc = check_launch("wgrad_reduce_kernel");
+    }
+    return rc;
+  }
   conv_tc_kernel<<<plan->grid, TC_THREADS, plan->smem, as_stream(stream)>>>(plan->p);
   return check_launch("conv_tc_kernel");
 }

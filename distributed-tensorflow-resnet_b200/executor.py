@@ -649,12 +649,22 @@ class Executor:
             dist.all_reduce(self.Gd[lo:hi], op=dist.ReduceOp.SUM, group=self.pg)
 
     def count_launches(self):
-        n = len(self.fwd)
-        if self.train:
-            n += len(self.bwd) + len(self.update)
-            # split-K wgrad issues a second (reduce) kernel
-            n += sum(1 for name, _ in self.bwd if name.startswith("conv_wgrad:"))
-        return n
+        """Kernel launches of one step, counted by the library itself during an un-captured run."""
+        if not self.launches_per_step:
+            snap = (self.W.clone(), self.S.clone()) + ((self.Mom.clone(),) if self.train else ())
+            l0 = _lib.launch_count()
+            st = torch.cuda.current_stream().cuda_stream
+            self._run_list(self.fwd, st)
+            if self.train:
+                self._run_list(self.bwd, st)
+                self._run_list(self.update, st)
+            torch.cuda.synchronize(self.dev)
+            self.launches_per_step = _lib.launch_count() - l0
+            self.W.copy_(snap[0]); self.S.copy_(snap[1])
+            if self.train:
+                self.Mom.copy_(snap[2])
+            self.refresh_shadow_weights()
+        return self.launches_per_step
 
     def capture(self):
         """Capture one full step (forward, backward, all-reduce, update) in a CUDA graph."""

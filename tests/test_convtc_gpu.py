@@ -76,6 +76,76 @@ def test_convtc_fprop_and_dgrad(case):
         assert rel_err(out.float(), want) < 2e-2, ("kind", kind)
 
 
+S2_CASES = [
+    # N, H, W, Cin, Cout, k, stride, pad, (Ho, Wo)
+    (4, 16, 16, 64, 128, 3, 2, 1, (8, 8)),       # official 3x3 s2: symmetric fixed_padding + VALID
+    (4, 16, 16, 64, 128, 3, 2, 0, (8, 8)),       # upstream 3x3 s2: TF-SAME (0 before, 1 after)
+    (4, 16, 16, 64, 128, 1, 2, 0, (8, 8)),       # 1x1 s2 projection shortcut
+    (2, 56, 56, 256, 512, 1, 2, 0, (28, 28)),    # C3 stage-2 projection
+    (2, 28, 28, 128, 128, 3, 2, 1, (14, 14)),    # C3 3x3 s2 (stride on the 3x3 of the bottleneck)
+    (3, 15, 13, 64, 64, 3, 2, 1, (8, 7)),        # odd sizes: parity views of different extents
+]
+
+WGRAD_CASES = CASES[0:3] + CASES[3:7] + [CASES[11]] + [
+    (16, 14, 14, 128, 128, 3, 1, 1),             # BLOCK_N = 128, four accumulators
+    (4, 28, 28, 192, 64, 1, 1, 0),               # three 64-channel row blocks
+]
+
+
+@pytest.mark.parametrize("case", S2_CASES)
+def test_convtc_stride2_fprop_and_wgrad(case):
+    _run_fprop_wgrad(case)
+
+
+@pytest.mark.parametrize("case", [c + ((c[1], c[2]),) for c in WGRAD_CASES])
+def test_convtc_wgrad(case):
+    _run_fprop_wgrad(case, fprop=False)
+
+
+def _run_fprop_wgrad(case, fprop=True):
+    N, H, W, Cin, Cout, k, s, pad, (Ho, Wo) = case
+    g = torch.Generator().manual_seed(sum(case[:8]))
+    x = torch.randn(N, H, W, Cin, generator=g).to(BF)
+    w = (torch.randn(k, k, Cin, Cout, generator=g) / (k * k * Cin) ** 0.5).to(BF)
+    dy = torch.randn(N, Ho, Wo, Cout, generator=g).to(BF)
+    net = ro.Net(dtype=torch.float64, params={"w": w.double().numpy()})
+    xv = ro.Var(x.double())
+    yv = net.conv2d(xv, "w", k, Cin, Cout, s, pad, (Ho, Wo), None, "y")
+    yv.grad = dy.double()
+    net.backward()
+    d = ConvDesc(N, H, W, Cin, Ho, Wo, Cout, k, s, pad, RN_BF16)
+    X, DY = dev(x), dev(dy)
+    if fprop:
+        assert lib.rn_convtc_supported(C.byref(d), 0) == 1
+        wf, _ = _weights(w)
+        Y = torch.full((N, Ho, Wo, Cout), float("nan"), dtype=BF, device="cuda")
+        plan = C.c_void_p()
+        check(lib.rn_convtc_plan_create(C.byref(d), 0, ptr(X), ptr(wf), ptr(Y), None, 0, C.byref(plan)), "plan")
+        check(lib.rn_convtc_run(plan, 0.0, stream()), "run")
+        torch.cuda.synchronize()
+        lib.rn_convtc_plan_destroy(plan)
+        assert torch.isfinite(Y.float()).all()
+        assert rel_err(Y.float(), yv.val) < 2e-2
+    assert lib.rn_convtc_supported(C.byref(d), 2) == 1
+    nb = lib.rn_convtc_scratch_bytes(C.byref(d), 2)
+    scratch = torch.empty(max(nb, 16), dtype=torch.uint8, device="cuda")
+    DW = torch.full((k, k, Cin, Cout), float("nan"), dtype=torch.float32, device="cuda")
+    plan = C.c_void_p()
+    check(lib.rn_convtc_plan_create(C.byref(d), 2, ptr(X), ptr(DY), ptr(DW), ptr(scratch), nb, C.byref(plan)), "plan wgrad")
+    outs = []
+    for _ in range(2):
+        check(lib.rn_convtc_run(plan, 0.0, stream()), "run wgrad")
+        torch.cuda.synchronize()
+        outs.append(DW.clone())
+    lib.rn_convtc_plan_destroy(plan)
+    assert torch.isfinite(DW).all()
+    assert torch.equal(outs[0], outs[1])                        # deterministic split-K
+    assert rel_err(DW, net.param_grads["w"]) < 1e-3             # fp32 accumulation of exact bf16 products
+    if nb > 0:
+        plan = C.c_void_p()
+        assert lib.rn_convtc_plan_create(C.byref(d), 2, ptr(X), ptr(DY), ptr(DW), ptr(scratch), nb - 1, C.byref(plan)) == -2
+
+
 def test_convtc_rejects_unsupported():
     d = ConvDesc(2, 8, 8, 3, 8, 8, 16, 3, 1, 1, RN_BF16)       # 3 input channels: 6-byte rows cannot be TMA'd
     assert lib.rn_convtc_supported(C.byref(d), 0) == 0
