@@ -44,6 +44,7 @@ struct TcConvParams {
   uint32_t a_bytes, b_bytes;      // stage buffer sizes (1024-aligned)
   uint32_t tx_bytes;              // bytes TMA delivers per stage
   uint32_t tmem_cols;
+  int accumulate;                 // 1: OUT += result (TMA reduce-add), 0: OUT = result
   int8_t tap_map[TC_MAX_TAPS], tap_dw[TC_MAX_TAPS], tap_dh[TC_MAX_TAPS], tap_b[TC_MAX_TAPS];
 };
 
@@ -185,7 +186,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const __grid_con
         fence_proxy_async();
         asm volatile("bar.sync 1, 128;" ::: "memory");
         if (issuer) {
-          tma_store_4d(&p.o_map, sb, nt * p.block_n + g * p.gw, w0, h0, n0);
+          if (p.accumulate) tma_reduce_add_4d(&p.o_map, sb, nt * p.block_n + g * p.gw, w0, h0, n0);
+          else              tma_store_4d(&p.o_map, sb, nt * p.block_n + g * p.gw, w0, h0, n0);
           tma_store_commit();
         }
         buf ^= 1;
@@ -559,10 +561,15 @@ using namespace rn;
 
 struct rn_convtc_plan {
   int kind;
-  TcConvParams p;
+  int nsub;                 // GEMM sub-problems (4 output-parity classes for a stride-2 dgrad, else 1)
+  TcConvParams p[4];
+  int grid[4];
+  size_t smem_sub[4];
+  void* clear_ptr;          // output to zero first (stride-2 dgrad whose taps do not reach every parity)
+  size_t clear_bytes;
   TcWgradParams w;
-  int grid;
-  size_t smem;
+  int wgrid;
+  size_t wsmem;
   float* dw;
   int64_t dw_elems;
 };
@@ -577,7 +584,6 @@ extern "C" int rn_convtc_supported(const rn_conv_desc* d, int kind) {
     WgradShape w;
     return wgrad_shape(d, &w) ? 1 : 0;
   }
-  if (kind == 1 && d->stride != 1) return 0;
   const int cred = kind == 0 ? d->Cin : d->Cout;
   const int ncols = kind == 0 ? d->Cout : d->Cin;
   if (cred < 16 || choose_block_n(ncols) == 0) return 0;
@@ -591,14 +597,18 @@ extern "C" size_t rn_convtc_scratch_bytes(const rn_conv_desc* d, int kind) {
   return w.scratch;
 }
 
-static int create_gemm_plan(const rn_conv_desc* d, int kind, const void* a, const void* b, void* out,
-                            rn_convtc_plan* pl) {
-  TcConvParams& p = pl->p;
-  // GEMM view: rows = pixels of the OUTPUT tensor of this GEMM, reduction over (tap, cred), columns = ncols
+// One GEMM sub-problem.  `oW,oH` and `ostr` describe the (possibly strided) view of the output that this
+// sub-problem writes; taps[] lists (map, dw, dh, weight tap).
+struct TapSpec { int8_t map, dw, dh, b; };
+
+static int create_sub(const rn_conv_desc* d, int kind, const void* a, const void* b, const void* out_base,
+                      int oW, int oH, const uint64_t* ostr, const TapSpec* taps, int ntaps, TcConvParams* pp,
+                      int* grid, size_t* smem_bytes) {
+  TcConvParams& p = *pp;
+  memset(&p, 0, sizeof(p));
   const int cred = kind == 0 ? d->Cin : d->Cout;
   const int ncols = kind == 0 ? d->Cout : d->Cin;
   const int aW = kind == 0 ? d->W : d->Wo, aH = kind == 0 ? d->H : d->Ho;   // activation tensor that is gathered
-  const int oW = kind == 0 ? d->Wo : d->W, oH = kind == 0 ? d->Ho : d->H;   // tensor that is written
   p.kc = cred >= 64 ? 64 : (cred >= 32 ? 32 : 16);
   p.k_chunks = (cred + p.kc - 1) / p.kc;
   p.block_n = choose_block_n(ncols);
@@ -608,14 +618,10 @@ static int create_gemm_plan(const rn_conv_desc* d, int kind, const void* a, cons
   p.tiles_w = (oW + p.BW - 1) / p.BW;
   p.tiles_h = (oH + p.BH - 1) / p.BH;
   p.tiles_n = (d->N + p.BN - 1) / p.BN;
-  p.taps = d->k * d->k;
-  for (int r = 0; r < d->k; ++r)
-    for (int s = 0; s < d->k; ++s) {
-      const int t = r * d->k + s;
-      p.tap_b[t] = (int8_t)t;
-      if (kind == 0) forward_tap(r, s, d->pad, d->stride, &p.tap_map[t], &p.tap_dw[t], &p.tap_dh[t]);
-      else { p.tap_map[t] = 0; p.tap_dw[t] = (int8_t)(d->pad - s); p.tap_dh[t] = (int8_t)(d->pad - r); }
-    }
+  p.taps = ntaps;
+  for (int t = 0; t < ntaps; ++t) {
+    p.tap_map[t] = taps[t].map; p.tap_dw[t] = taps[t].dw; p.tap_dh[t] = taps[t].dh; p.tap_b[t] = taps[t].b;
+  }
   const int row_bytes = p.kc * 2;
   const uint32_t box_rows = (uint32_t)(p.BW * p.BH * p.BN);
   p.a_bytes = ((uint32_t)TC_BLOCK_M * row_bytes + 1023u) & ~1023u;
@@ -630,29 +636,77 @@ static int create_gemm_plan(const rn_conv_desc* d, int kind, const void* a, cons
   if (stages > 8) stages = 8;
   if (stages < 2) return fail(RN_ERR_UNSUPPORTED, "convtc: tile does not fit shared memory");
   p.stages = stages;
-  pl->smem = fixed + (size_t)stages * (p.a_bytes + p.b_bytes);
+  *smem_bytes = fixed + (size_t)stages * (p.a_bytes + p.b_bytes);
   int rc;
   const uint32_t abox[4] = {(uint32_t)p.kc, (uint32_t)p.BW, (uint32_t)p.BH, (uint32_t)p.BN};
   rc = encode_activation_maps(p.a_map, a, cred, aW, aH, d->N, kind == 0 ? d->stride : 1, abox, row_bytes);
   if (rc) return rc;
   {  // weights: dims (cred, ncols, taps)
-    const uint64_t dims[3] = {(uint64_t)cred, (uint64_t)ncols, (uint64_t)p.taps};
+    const uint64_t dims[3] = {(uint64_t)cred, (uint64_t)ncols, (uint64_t)(d->k * d->k)};
     const uint64_t str[2] = {(uint64_t)cred * 2, (uint64_t)ncols * cred * 2};
     const uint32_t box[3] = {(uint32_t)p.kc, (uint32_t)p.block_n, 1u};
     rc = encode_map(&p.b_map, b, 3, dims, str, box, row_bytes, "weights");
     if (rc) return rc;
   }
-  {  // output: dims (ncols, W, H, N)
+  {  // output view: dims (ncols, oW, oH, N)
     const uint64_t dims[4] = {(uint64_t)ncols, (uint64_t)oW, (uint64_t)oH, (uint64_t)d->N};
-    const uint64_t str[3] = {(uint64_t)ncols * 2, (uint64_t)oW * ncols * 2, (uint64_t)oH * oW * ncols * 2};
     const uint32_t box[4] = {(uint32_t)p.gw, (uint32_t)p.BW, (uint32_t)p.BH, (uint32_t)p.BN};
-    rc = encode_map(&p.o_map, out, 4, dims, str, box, p.gw * 2, "output");
+    rc = encode_map(&p.o_map, out_base, 4, dims, ostr, box, p.gw * 2, "output");
     if (rc) return rc;
   }
   const long total = (long)p.tiles_w * p.tiles_h * p.tiles_n * p.n_tiles;
-  pl->grid = (int)(total < RN_NUM_SMS ? total : RN_NUM_SMS);
+  *grid = (int)(total < RN_NUM_SMS ? total : RN_NUM_SMS);
+  return RN_OK;
+}
+
+static int create_gemm_plan(const rn_conv_desc* d, int kind, const void* a, const void* b, void* out,
+                            rn_convtc_plan* pl) {
   cudaError_t e = cudaFuncSetAttribute(conv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024));
   if (e != cudaSuccess) return fail(RN_ERR_CUDA, "convtc: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+  TapSpec taps[TC_MAX_TAPS];
+  pl->clear_ptr = nullptr;
+  pl->clear_bytes = 0;
+  if (kind == 0 || d->stride == 1) {
+    const int ncols = kind == 0 ? d->Cout : d->Cin;
+    const int oW = kind == 0 ? d->Wo : d->W, oH = kind == 0 ? d->Ho : d->H;
+    for (int r = 0; r < d->k; ++r)
+      for (int s = 0; s < d->k; ++s) {
+        TapSpec& t = taps[r * d->k + s];
+        t.b = (int8_t)(r * d->k + s);
+        if (kind == 0) forward_tap(r, s, d->pad, d->stride, &t.map, &t.dw, &t.dh);
+        else { t.map = 0; t.dw = (int8_t)(d->pad - s); t.dh = (int8_t)(d->pad - r); }
+      }
+    const uint64_t ostr[3] = {(uint64_t)ncols * 2, (uint64_t)oW * ncols * 2, (uint64_t)oH * oW * ncols * 2};
+    pl->nsub = 1;
+    return create_sub(d, kind, a, b, out, oW, oH, ostr, taps, d->k * d->k, &pl->p[0], &pl->grid[0], &pl->smem_sub[0]);
+  }
+  // stride-2 dgrad: dx[2i+ph, 2j+pw] = sum over taps with r = ph+pad, s = pw+pad (mod 2) of
+  //   dy[i + (ph+pad-r)/2, j + (pw+pad-s)/2] * w[r,s]  — one dense GEMM per output parity class, written
+  //   through a strided view of dx.
+  pl->nsub = 0;
+  bool some_empty = false;
+  for (int ph = 0; ph < 2; ++ph)
+    for (int pw = 0; pw < 2; ++pw) {
+      const int W2 = (d->W - pw + 1) / 2, H2 = (d->H - ph + 1) / 2;
+      if (W2 <= 0 || H2 <= 0) continue;
+      int nt = 0;
+      for (int r = 0; r < d->k; ++r)
+        for (int s = 0; s < d->k; ++s) {
+          if (((ph + d->pad - r) & 1) || ((pw + d->pad - s) & 1)) continue;
+          TapSpec& t = taps[nt++];
+          t.map = 0; t.b = (int8_t)(r * d->k + s);
+          t.dh = (int8_t)((ph + d->pad - r) / 2);     // exact: the numerator is even
+          t.dw = (int8_t)((pw + d->pad - s) / 2);
+        }
+      if (nt == 0) { some_empty = true; continue; }
+      const uint64_t ostr[3] = {(uint64_t)2 * d->Cin * 2, (uint64_t)2 * d->W * d->Cin * 2, (uint64_t)d->H * d->W * d->Cin * 2};
+      const char* base = (const char*)out + ((size_t)ph * d->W + pw) * d->Cin * 2;
+      const int i = pl->nsub;
+      int rc = create_sub(d, 1, a, b, base, W2, H2, ostr, taps, nt, &pl->p[i], &pl->grid[i], &pl->smem_sub[i]);
+      if (rc) return rc;
+      pl->nsub++;
+    }
+  if (some_empty) { pl->clear_ptr = out; pl->clear_bytes = (size_t)d->N * d->H * d->W * d->Cin * 2; }
   return RN_OK;
 }
 
@@ -682,8 +736,8 @@ static int create_wgrad_plan(const rn_conv_desc* d, const void* x, const void* d
     if (rc) return rc;
   }
   const long total = (long)ws.row_groups * ws.n_tiles * ws.splits;
-  pl->grid = (int)(total < RN_NUM_SMS ? total : RN_NUM_SMS);
-  pl->smem = ws.smem;
+  pl->wgrid = (int)(total < RN_NUM_SMS ? total : RN_NUM_SMS);
+  pl->wsmem = ws.smem;
   pl->dw = (float*)dw;
   pl->dw_elems = (int64_t)d->k * d->k * d->Cin * d->Cout;
   cudaError_t e = cudaFuncSetAttribute(conv_wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024));
@@ -697,8 +751,7 @@ extern "C" int rn_convtc_plan_create(const rn_conv_desc* d, int kind, const void
   if (!rn_convtc_supported(d, kind)) return fail(RN_ERR_UNSUPPORTED, "convtc: shape/kind not supported");
   RN_REQUIRE((((uintptr_t)a | (uintptr_t)b | (uintptr_t)out) & 15) == 0, "convtc: pointers must be 16-byte aligned");
   rn_convtc_plan* pl = new rn_convtc_plan();
-  memset(&pl->p, 0, sizeof(pl->p));
-  memset(&pl->w, 0, sizeof(pl->w));
+  memset(pl, 0, sizeof(*pl));
   pl->kind = kind;
   const int rc = kind == 2 ? create_wgrad_plan(d, a, b, out, scratch, scratch_bytes, pl)
                            : create_gemm_plan(d, kind, a, b, out, pl);
@@ -709,20 +762,32 @@ extern "C" int rn_convtc_plan_create(const rn_conv_desc* d, int kind, const void
 
 extern "C" int rn_convtc_run(rn_convtc_plan* plan, float beta, void* stream) {
   RN_REQUIRE(plan, "convtc_run: NULL plan");
-  if (beta != 0.f) return fail(RN_ERR_UNSUPPORTED, "convtc_run: accumulation (beta=1) is not supported by this kernel");
+  RN_REQUIRE(beta == 0.f || beta == 1.f, "convtc_run: beta must be 0 or 1");
+  cudaStream_t st = as_stream(stream);
   if (plan->kind == 2) {
-    conv_wgrad_tc_kernel<<<plan->grid, TC_THREADS, plan->smem, as_stream(stream)>>>(plan->w);
+    if (beta != 0.f) return fail(RN_ERR_UNSUPPORTED, "convtc_run: wgrad overwrites its output (beta must be 0)");
+    conv_wgrad_tc_kernel<<<plan->wgrid, TC_THREADS, plan->wsmem, st>>>(plan->w);
     int rc = check_launch("conv_wgrad_tc_kernel");
     if (rc) return rc;
     if (plan->w.splits > 1) {
       const int64_t n4 = plan->dw_elems / 4;
-      wgrad_reduce_kernel<<<grid_for(n4, 256), 256, 0, as_stream(stream)>>>(plan->w.partial, plan->dw, n4, plan->w.splits);
+      wgrad_reduce_kernel<<<grid_for(n4, 256), 256, 0, st>>>(plan->w.partial, plan->dw, n4, plan->w.splits);
       rc = check_launch("wgrad_reduce_kernel");
     }
     return rc;
   }
-  conv_tc_kernel<<<plan->grid, TC_THREADS, plan->smem, as_stream(stream)>>>(plan->p);
-  return check_launch("conv_tc_kernel");
+  if (beta == 0.f && plan->clear_ptr) {
+    cudaError_t e = cudaMemsetAsync(plan->clear_ptr, 0, plan->clear_bytes, st);
+    if (e != cudaSuccess) return fail(RN_ERR_CUDA, "convtc_run: cudaMemsetAsync: %s", cudaGetErrorString(e));
+  }
+  for (int i = 0; i < plan->nsub; ++i) {
+    TcConvParams p = plan->p[i];
+    p.accumulate = beta != 0.f ? 1 : 0;
+    conv_tc_kernel<<<plan->grid[i], TC_THREADS, plan->smem_sub[i], st>>>(p);
+    int rc = check_launch("conv_tc_kernel");
+    if (rc) return rc;
+  }
+  return RN_OK;
 }
 
 extern "C" int rn_convtc_plan_destroy(rn_convtc_plan* plan) {

@@ -536,7 +536,7 @@ class Executor:
             kv = n.vars["kernel"]
             if x.requires_grad:
                 dxb, beta = self._target(x, done, bwd)
-                if beta == 0.0 and self._conv_impl(n, 1) == "tc":     # the tensor-core dgrad overwrites its output
+                if self._conv_impl(n, 1) == "tc":
                     run = self._tc_plan(n, d, 1, dy, dxb)
                     self._emit(bwd, "conv_dgrad_tc:" + y.name, lambda s, run=run, beta=beta: run(s, beta=beta),
                                node=n, dy=dy, dx=dxb, beta=beta)

@@ -102,6 +102,36 @@ def test_convtc_wgrad(case):
     _run_fprop_wgrad(case, fprop=False)
 
 
+@pytest.mark.parametrize("beta", [0.0, 1.0])
+@pytest.mark.parametrize("case", S2_CASES + [c + ((c[1], c[2]),) for c in (CASES[3], CASES[5], CASES[7])])
+def test_convtc_dgrad_stride2_and_accumulate(case, beta):
+    """dgrad at stride 2 (one GEMM per output parity class through strided views of dx) and
+    gradient fan-in (dx += ..., done by the TMA unit as a bf16 reduce-add)."""
+    N, H, W, Cin, Cout, k, s, pad, (Ho, Wo) = case
+    g = torch.Generator().manual_seed(sum(case[:8]) + 1)
+    w = (torch.randn(k, k, Cin, Cout, generator=g) / (k * k * Cin) ** 0.5).to(BF)
+    dy = torch.randn(N, Ho, Wo, Cout, generator=g).to(BF)
+    base = torch.randn(N, H, W, Cin, generator=g).to(BF)
+    net = ro.Net(dtype=torch.float64, params={"w": w.double().numpy()})
+    xv = ro.Var(torch.zeros(N, H, W, Cin, dtype=torch.float64))
+    yv = net.conv2d(xv, "w", k, Cin, Cout, s, pad, (Ho, Wo), None, "y")
+    yv.grad = dy.double()
+    net.backward()
+    want = xv.grad + (base.double() if beta else 0.0)
+    d = ConvDesc(N, H, W, Cin, Ho, Wo, Cout, k, s, pad, RN_BF16)
+    assert lib.rn_convtc_supported(C.byref(d), 1) == 1
+    _, wd = _weights(w)
+    DY = dev(dy)
+    DX = dev(base) if beta else torch.full((N, H, W, Cin), float("nan"), dtype=BF, device="cuda")
+    plan = C.c_void_p()
+    check(lib.rn_convtc_plan_create(C.byref(d), 1, ptr(DY), ptr(wd), ptr(DX), None, 0, C.byref(plan)), "plan")
+    check(lib.rn_convtc_run(plan, beta, stream()), "run")
+    torch.cuda.synchronize()
+    lib.rn_convtc_plan_destroy(plan)
+    assert torch.isfinite(DX.float()).all()
+    assert rel_err(DX.float(), want) < 2e-2
+
+
 def _run_fprop_wgrad(case, fprop=True):
     N, H, W, Cin, Cout, k, s, pad, (Ho, Wo) = case
     g = torch.Generator().manual_seed(sum(case[:8]))
