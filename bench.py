@@ -327,6 +327,21 @@ def run_ours(args):
     if rank == 0:
         # ---- per-kernel roofline (un-captured launch list, CUDA events per launch) ------------
         per_launch = profile_step(ex, model.graph, iters=2)
+        if args.dump_layers:
+            cf = conv_flops(model.graph)
+            with open(args.dump_layers, "w") as f:
+                for name, ms_ in per_launch.items():
+                    fam, _, key = name.partition(":")
+                    extra = ""
+                    if key in cf and fam.startswith("conv_"):
+                        n_ = [n for n in model.graph.nodes if n.op == "conv2d" and n.outputs[0].name == key][0]
+                        extra = " %8.1f TFLOP/s  in %s k%d s%d -> %s" % (cf[key][0] / ms_ / 1e9, n_.inputs[0].shape,
+                                                                         n_.attrs["k"], n_.attrs["stride"], n_.outputs[0].shape)
+                    else:
+                        b_ = hbm_bytes(name, ex, model.graph)
+                        if b_:
+                            extra = " %8.1f GB/s" % (b_ / ms_ / 1e6)
+                    f.write("%-44s %9.4f ms%s\n" % (name, ms_, extra))
         roof, table, prof_total = roofline_report(ex, model.graph, per_launch, pk)
         cpu = None
         if not args.no_cpu_baseline:
@@ -382,6 +397,7 @@ def main():
     ap.add_argument("--batch", type=int, default=0, help="per-GPU batch (default: the workload's)")
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--dump-layers", default="", help="write the per-launch timing table to this file")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":
         args.warmup = 3

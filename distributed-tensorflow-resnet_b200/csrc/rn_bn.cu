@@ -36,7 +36,10 @@ static BnLayout bn_layout(int64_t M, int C, int waves) {
   L.CW = L.CV < 32 ? L.CV : 32;
   L.RY = BN_THREADS / L.CW;
   L.gridY = (L.CV + L.CW - 1) / L.CW;
-  int64_t want = (M + (int64_t)L.RY * 4 - 1) / ((int64_t)L.RY * 4);
+  // at least ~64 KB of the tensor per CTA (per channel chunk): small tensors get few CTAs, which keeps
+  // the serial last-CTA reduction over the per-CTA partials short
+  const int64_t chunk_bytes = M * (int64_t)L.CW * V * (int64_t)sizeof(T);
+  int64_t want = (chunk_bytes + 65535) / 65536;
   int64_t cap = (int64_t)RN_NUM_SMS * waves / L.gridY;
   if (cap < 1) cap = 1;
   if (cap > BN_MAX_G) cap = BN_MAX_G;
@@ -80,6 +83,62 @@ __device__ __forceinline__ void cta_reduce_cols(float (&a)[V], float (&b)[V], in
   }
 }
 
+
+// Last-CTA finalisation: sum `nparts` per-CTA partials ([2][chunkC] floats each) in a FIXED order.
+// Thread t owns four adjacent channels (one 128-bit load per partial and statistic) and one of
+// S = 1024 / chunkC slices of the partial list (slice j sums partials j, j+S, ...).  Loads are issued in
+// batches before any arithmetic: the L2 ("strong") loads keep program order, so interleaving them
+// with the conversions would leave one load in flight and make the tail latency-bound.  The slices
+// are then combined in order through shared memory.  Results are valid for threads < chunkC.
+constexpr int BN_FIN_DOUBLES = 2 * 1024;
+__device__ __forceinline__ void final_reduce(const float* base, unsigned nparts, int chunkC, double* sh, double& out0,
+                                             double& out1) {
+  const int q4 = chunkC / 4;                         // float4 columns per statistic
+  const int slices = BN_THREADS / q4;                // >= 4 (chunkC <= 256)
+  const int c4 = threadIdx.x % q4;
+  const int slice = threadIdx.x / q4;
+  double a0[4] = {0, 0, 0, 0}, a1[4] = {0, 0, 0, 0};
+  if (slice < slices) {
+    unsigned b = slice;
+    constexpr int U = 4;
+    for (; b + (unsigned)((U - 1) * slices) < nparts; b += (unsigned)(U * slices)) {
+      float4 t0[U], t1[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const float4* q = reinterpret_cast<const float4*>(base + (size_t)(b + u * slices) * 2 * chunkC);
+        t0[u] = __ldcg(q + c4);
+        t1[u] = __ldcg(q + q4 + c4);
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        a0[0] += (double)t0[u].x; a0[1] += (double)t0[u].y; a0[2] += (double)t0[u].z; a0[3] += (double)t0[u].w;
+        a1[0] += (double)t1[u].x; a1[1] += (double)t1[u].y; a1[2] += (double)t1[u].z; a1[3] += (double)t1[u].w;
+      }
+    }
+    for (; b < nparts; b += slices) {
+      const float4* q = reinterpret_cast<const float4*>(base + (size_t)b * 2 * chunkC);
+      const float4 t0 = __ldcg(q + c4), t1 = __ldcg(q + q4 + c4);
+      a0[0] += (double)t0.x; a0[1] += (double)t0.y; a0[2] += (double)t0.z; a0[3] += (double)t0.w;
+      a1[0] += (double)t1.x; a1[1] += (double)t1.y; a1[2] += (double)t1.z; a1[3] += (double)t1.w;
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      sh[(size_t)slice * chunkC + c4 * 4 + j] = a0[j];
+      sh[1024 + (size_t)slice * chunkC + c4 * 4 + j] = a1[j];
+    }
+  }
+  __syncthreads();
+  double s0 = 0.0, s1 = 0.0;
+  if ((int)threadIdx.x < chunkC) {
+    for (int j = 0; j < slices; ++j) {
+      s0 += sh[(size_t)j * chunkC + threadIdx.x];
+      s1 += sh[1024 + (size_t)j * chunkC + threadIdx.x];
+    }
+  }
+  out0 = s0;
+  out1 = s1;
+}
+
 // ------------------------------------------------------------------------------------------
 // forward statistics (+ fused residual add)
 // ------------------------------------------------------------------------------------------
@@ -99,10 +158,39 @@ bn_stats_kernel(const T* __restrict__ x, const T* __restrict__ addend, T* __rest
   for (int i = 0; i < V; ++i) { s[i] = 0.f; q[i] = 0.f; }
   if (active) {
     const int64_t stride = (int64_t)gridDim.x * L.RY;
-    for (int64_t r = (int64_t)blockIdx.x * L.RY + ty; r < M; r += stride) {
+    const int64_t col = (int64_t)cg * V;
+    int64_t r = (int64_t)blockIdx.x * L.RY + ty;
+    constexpr int U = ADD ? 1 : 2;   // independent 128-bit loads in flight per thread and stream
+    for (; r + (U - 1) * stride < M; r += U * stride) {
+      Vec<T> v[U], w[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) v[u].load(x + (r + u * stride) * C + col);
+      if (ADD) {
+#pragma unroll
+        for (int u = 0; u < U; ++u) w[u].load(addend + (r + u * stride) * C + col);
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        float f[V];
+        v[u].unpack(f);
+        if (ADD) {
+          float g[V];
+          w[u].unpack(g);
+#pragma unroll
+          for (int i = 0; i < V; ++i) f[i] += g[i];
+          Vec<T> o;
+          o.pack(f);
+          o.store(sum_out + (r + u * stride) * C + col);
+          o.unpack(f);  // statistics of the value as stored (matters in bf16 mode)
+        }
+#pragma unroll
+        for (int i = 0; i < V; ++i) { s[i] += f[i]; q[i] = fmaf(f[i], f[i], q[i]); }
+      }
+    }
+    for (; r < M; r += stride) {
       Vec<T> v;
       float f[V];
-      const int64_t off = r * C + (int64_t)cg * V;
+      const int64_t off = r * C + col;
       v.load(x + off);
       v.unpack(f);
       if (ADD) {
@@ -115,7 +203,7 @@ bn_stats_kernel(const T* __restrict__ x, const T* __restrict__ addend, T* __rest
         Vec<T> o;
         o.pack(f);
         o.store(sum_out + off);
-        o.unpack(f);  // statistics of the value as stored (matters in bf16 mode)
+        o.unpack(f);
       }
 #pragma unroll
       for (int i = 0; i < V; ++i) { s[i] += f[i]; q[i] = fmaf(f[i], f[i], q[i]); }
@@ -128,25 +216,25 @@ bn_stats_kernel(const T* __restrict__ x, const T* __restrict__ addend, T* __rest
 #pragma unroll
     for (int i = 0; i < V; ++i) { my[tx * V + i] = s[i]; my[chunkC + tx * V + i] = q[i]; }
   }
+  // Publish the partials: barrier (CTA-scope ordering of every thread's stores), then ONE gpu-scope
+  // fence by the ticket thread (fences are cumulative).  A __threadfence() by all 256 threads costs
+  // ~20 us per resident CTA on this part (each one invalidates L1) and dominated small layers.
   __shared__ bool is_last;
-  __threadfence();
   __syncthreads();
   if (threadIdx.x == 0) {
+    __threadfence();
     unsigned t = atomicAdd(&counters[blockIdx.y], 1u);
     is_last = (t == gridDim.x - 1);
+    __threadfence();
   }
   __syncthreads();
   if (!is_last) return;
-  __threadfence();
+  __shared__ double fin[BN_FIN_DOUBLES];
+  double S, Q;
+  final_reduce(partials + (size_t)blockIdx.y * gridDim.x * 2 * chunkC, gridDim.x, chunkC, fin, S, Q);
   const int c_local = threadIdx.x;
   const int c = blockIdx.y * chunkC + c_local;
   if (c_local < chunkC && c < C) {
-    double S = 0.0, Q = 0.0;
-    const float* base = partials + (size_t)blockIdx.y * gridDim.x * 2 * chunkC;
-    for (unsigned b = 0; b < gridDim.x; ++b) {
-      S += (double)__ldcg(base + (size_t)b * 2 * chunkC + c_local);
-      Q += (double)__ldcg(base + (size_t)b * 2 * chunkC + chunkC + c_local);
-    }
     const double mean = S / (double)M;
     double var = Q / (double)M - mean * mean;
     if (var < 0.0) var = 0.0;
@@ -183,8 +271,25 @@ bn_apply_kernel(const T* __restrict__ x, T* __restrict__ y, int64_t M, int C, Bn
     b[i] = beta[c] - mean[c] * a[i];
   }
   const int64_t stride = (int64_t)gridDim.x * L.RY;
-  for (int64_t r = (int64_t)blockIdx.x * L.RY + ty; r < M; r += stride) {
-    const int64_t off = r * C + (int64_t)cg * V;
+  const int64_t col = (int64_t)cg * V;
+  int64_t r = (int64_t)blockIdx.x * L.RY + ty;
+  constexpr int U = 4;
+  for (; r + (U - 1) * stride < M; r += U * stride) {
+    Vec<T> v[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) v[u].load_stream(x + (r + u * stride) * C + col);
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      float f[V];
+      v[u].unpack(f);
+#pragma unroll
+      for (int i = 0; i < V; ++i) f[i] = act_fn(fmaf(f[i], a[i], b[i]), leak);
+      v[u].pack(f);
+      v[u].store(y + (r + u * stride) * C + col);
+    }
+  }
+  for (; r < M; r += stride) {
+    const int64_t off = r * C + col;
     Vec<T> v;
     float f[V];
     v.load_stream(x + off);
@@ -223,8 +328,32 @@ bn_bwd_reduce_kernel(const T* __restrict__ dy, const T* __restrict__ x, int64_t 
       b[i] = beta[c] - mu[i] * a[i];
     }
     const int64_t stride = (int64_t)gridDim.x * L.RY;
-    for (int64_t r = (int64_t)blockIdx.x * L.RY + ty; r < M; r += stride) {
-      const int64_t off = r * C + (int64_t)cg * V;
+    const int64_t col = (int64_t)cg * V;
+    int64_t r = (int64_t)blockIdx.x * L.RY + ty;
+    constexpr int U = 2;   // 2 x 2 independent 128-bit loads in flight per thread
+    for (; r + (U - 1) * stride < M; r += U * stride) {
+      Vec<T> vx[U], vg[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        vx[u].load(x + (r + u * stride) * C + col);
+        vg[u].load(dy + (r + u * stride) * C + col);
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        float fx[V], fg[V];
+        vx[u].unpack(fx);
+        vg[u].unpack(fg);
+#pragma unroll
+        for (int i = 0; i < V; ++i) {
+          const float pre = fmaf(fx[i], a[i], b[i]);
+          const float g = pre < 0.f ? leak * fg[i] : fg[i];
+          sb[i] += g;
+          sg[i] = fmaf(g, (fx[i] - mu[i]) * rs[i], sg[i]);
+        }
+      }
+    }
+    for (; r < M; r += stride) {
+      const int64_t off = r * C + col;
       Vec<T> vx, vg;
       float fx[V], fg[V];
       vx.load(x + off);
@@ -247,25 +376,25 @@ bn_bwd_reduce_kernel(const T* __restrict__ dy, const T* __restrict__ x, int64_t 
 #pragma unroll
     for (int i = 0; i < V; ++i) { my[tx * V + i] = sb[i]; my[chunkC + tx * V + i] = sg[i]; }
   }
+  // Publish the partials: barrier (CTA-scope ordering of every thread's stores), then ONE gpu-scope
+  // fence by the ticket thread (fences are cumulative).  A __threadfence() by all 256 threads costs
+  // ~20 us per resident CTA on this part (each one invalidates L1) and dominated small layers.
   __shared__ bool is_last;
-  __threadfence();
   __syncthreads();
   if (threadIdx.x == 0) {
+    __threadfence();
     unsigned t = atomicAdd(&counters[blockIdx.y], 1u);
     is_last = (t == gridDim.x - 1);
+    __threadfence();
   }
   __syncthreads();
   if (!is_last) return;
-  __threadfence();
+  __shared__ double fin[BN_FIN_DOUBLES];
+  double B, G;
+  final_reduce(partials + (size_t)blockIdx.y * gridDim.x * 2 * chunkC, gridDim.x, chunkC, fin, B, G);
   const int c_local = threadIdx.x;
   const int c = blockIdx.y * chunkC + c_local;
   if (c_local < chunkC && c < C) {
-    double B = 0.0, G = 0.0;
-    const float* base = partials + (size_t)blockIdx.y * gridDim.x * 2 * chunkC;
-    for (unsigned bb = 0; bb < gridDim.x; ++bb) {
-      B += (double)__ldcg(base + (size_t)bb * 2 * chunkC + c_local);
-      G += (double)__ldcg(base + (size_t)bb * 2 * chunkC + chunkC + c_local);
-    }
     dbeta[c] = (float)B;
     dgamma[c] = (float)G;
   }
@@ -298,8 +427,38 @@ bn_bwd_apply_kernel(const T* __restrict__ dy, const T* __restrict__ x, T* dx, co
     k2[i] = dgamma[c] * invM;
   }
   const int64_t stride = (int64_t)gridDim.x * L.RY;
-  for (int64_t r = (int64_t)blockIdx.x * L.RY + ty; r < M; r += stride) {
-    const int64_t off = r * C + (int64_t)cg * V;
+  const int64_t col = (int64_t)cg * V;
+  int64_t r = (int64_t)blockIdx.x * L.RY + ty;
+  constexpr int U = 2;
+  for (; r + (U - 1) * stride < M; r += U * stride) {
+    Vec<T> vx[U], vg[U], va[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      vx[u].load_stream(x + (r + u * stride) * C + col);
+      vg[u].load_stream(dy + (r + u * stride) * C + col);
+      if (ADD) va[u].load(dx_addend + (r + u * stride) * C + col);
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      float fx[V], fg[V], fo[V];
+      vx[u].unpack(fx);
+      vg[u].unpack(fg);
+      if (ADD) va[u].unpack(fo);
+#pragma unroll
+      for (int i = 0; i < V; ++i) {
+        const float pre = fmaf(fx[i], a[i], b[i]);
+        const float g = pre < 0.f ? leak * fg[i] : fg[i];
+        const float xhat = (fx[i] - mu[i]) * rs[i];
+        const float d = a[i] * (g - k1[i] - xhat * k2[i]);
+        fo[i] = ADD ? fo[i] + d : d;
+      }
+      Vec<T> vo;
+      vo.pack(fo);
+      vo.store(dx + (r + u * stride) * C + col);
+    }
+  }
+  for (; r < M; r += stride) {
+    const int64_t off = r * C + col;
     Vec<T> vx, vg;
     float fx[V], fg[V], fo[V];
     vx.load_stream(x + off);

@@ -803,3 +803,99 @@ extern "C" int rn_weights_to_bf16(const float* w_hwio, int k, int Cin, int Cout,
                                                                          (__nv_bfloat16*)w_fprop, (__nv_bfloat16*)w_dgrad);
   return check_launch("weights_to_bf16_kernel");
 }
+
+// ------------------------------------------------------------------------------------------
+// Stem (first) convolution: 3 input channels cannot feed TMA rows (16-byte granularity) or UMMA K
+// steps, so the image is unfolded once per step into bf16 rows of Kpad = roundup(k*k*Cin, 64)
+// columns ordered (r, s, ci) — the HWIO flattening — and the GEMM kernels above run it as a 1x1
+// convolution with Kpad input channels (forward and wgrad; the image needs no dgrad).
+// ------------------------------------------------------------------------------------------
+namespace rn {
+constexpr int IM2COL_MAX_K = 512;
+template <typename T>
+__global__ void __launch_bounds__(256)
+im2col_kernel(const T* __restrict__ x, __nv_bfloat16* __restrict__ cols, int N, int H, int W, int Cin, int Ho, int Wo,
+              int k, int stride, int pad, int Kpad) {
+  // per-column lookup: input offset relative to the window origin, and the (r, s) of the tap
+  __shared__ int s_off[IM2COL_MAX_K];
+  __shared__ int8_t s_r[IM2COL_MAX_K], s_s[IM2COL_MAX_K];
+  const int K = k * k * Cin;
+  for (int kk = threadIdx.x; kk < Kpad; kk += blockDim.x) {
+    if (kk < K) {
+      const int tap = kk / Cin, c = kk - tap * Cin;
+      const int r = tap / k, sft = tap - r * k;
+      s_off[kk] = (r * W + sft) * Cin + c;
+      s_r[kk] = (int8_t)r;
+      s_s[kk] = (int8_t)sft;
+    } else {
+      s_off[kk] = 0;
+      s_r[kk] = -128;          // padding column
+      s_s[kk] = 0;
+    }
+  }
+  __syncthreads();
+  const int chunks = Kpad / 8;
+  const int64_t total = (int64_t)N * Ho * Wo * chunks;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int ch = (int)(i % chunks);
+    int64_t p = i / chunks;
+    const int wo = (int)(p % Wo);
+    p /= Wo;
+    const int ho = (int)(p % Ho);
+    const int n = (int)(p / Ho);
+    const int h0 = ho * stride - pad, w0 = wo * stride - pad;
+    const int64_t base = (((int64_t)n * H + h0) * W + w0) * Cin;
+    float f[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int kk = ch * 8 + j;
+      const int r = s_r[kk];
+      const int h = h0 + r, w = w0 + s_s[kk];
+      float v = 0.f;
+      if (r >= 0 && h >= 0 && h < H && w >= 0 && w < W) v = to_f<T>(x[base + s_off[kk]]);
+      f[j] = v;
+    }
+    Vec<__nv_bfloat16> o;
+    o.pack(f);
+    o.store(cols + i * 8);
+  }
+}
+
+// fp32 HWIO [rows = k*k*Cin][Cout] -> bf16 [Cout][Kpad] (K-major B operand, zero padded)
+__global__ void stem_weights_kernel(const float* __restrict__ w, int rows, int Cout, int Kpad,
+                                    __nv_bfloat16* __restrict__ wf) {
+  const int64_t total = (int64_t)Cout * Kpad;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int kk = (int)(i % Kpad);
+    const int co = (int)(i / Kpad);
+    wf[i] = __float2bfloat16_rn(kk < rows ? w[(int64_t)kk * Cout + co] : 0.f);
+  }
+}
+}  // namespace rn
+
+extern "C" int rn_im2col(const void* x, void* cols, int32_t N, int32_t H, int32_t W, int32_t Cin, int32_t Ho, int32_t Wo,
+                         int32_t k, int32_t stride, int32_t pad, int32_t Kpad, int32_t src_dtype, void* stream) {
+  RN_REQUIRE(x && cols && N > 0 && H > 0 && W > 0 && Cin > 0 && Ho > 0 && Wo > 0 && k > 0 && stride > 0 && pad >= 0,
+             "im2col: bad arguments");
+  RN_REQUIRE(Kpad % 8 == 0 && Kpad >= k * k * Cin && Kpad <= IM2COL_MAX_K,
+             "im2col: Kpad=%d must be a multiple of 8, >= k*k*Cin and <= 512", Kpad);
+  const int64_t total = (int64_t)N * Ho * Wo * (Kpad / 8);
+  const int g = grid_for(total, 256, 16);
+  if (src_dtype == RN_BF16)
+    im2col_kernel<__nv_bfloat16><<<g, 256, 0, as_stream(stream)>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)cols, N, H,
+                                                                  W, Cin, Ho, Wo, k, stride, pad, Kpad);
+  else if (src_dtype == RN_F32)
+    im2col_kernel<float><<<g, 256, 0, as_stream(stream)>>>((const float*)x, (__nv_bfloat16*)cols, N, H, W, Cin, Ho, Wo,
+                                                          k, stride, pad, Kpad);
+  else
+    return fail(RN_ERR_INVALID, "im2col: bad src_dtype %d", src_dtype);
+  return check_launch("im2col_kernel");
+}
+
+extern "C" int rn_stem_weights(const float* w_hwio, int32_t rows, int32_t Cout, int32_t Kpad, void* w_fprop,
+                               void* stream) {
+  RN_REQUIRE(w_hwio && w_fprop && rows > 0 && Cout > 0 && Kpad >= rows, "stem_weights: bad arguments");
+  stem_weights_kernel<<<grid_for((int64_t)Cout * Kpad, 256), 256, 0, as_stream(stream)>>>(w_hwio, rows, Cout, Kpad,
+                                                                                         (__nv_bfloat16*)w_fprop);
+  return check_launch("stem_weights_kernel");
+}

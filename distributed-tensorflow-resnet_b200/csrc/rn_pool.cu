@@ -70,6 +70,105 @@ __global__ void maxpool_bwd_kernel(const T* __restrict__ dy, const uint8_t* __re
   }
 }
 
+// 128-bit vector versions (C % Vec<T>::N == 0): one thread per pixel x channel group.
+template <typename T>
+__global__ void maxpool_fwd_vec_kernel(const T* __restrict__ x, T* __restrict__ y, uint8_t* __restrict__ argmax, int N,
+                                       int H, int W, int C, int Ho, int Wo, int pad) {
+  constexpr int V = Vec<T>::N;
+  const int CV = C / V;
+  const int64_t total = (int64_t)N * Ho * Wo * CV;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int cg = (int)(i % CV);
+    int64_t p = i / CV;
+    const int wo = (int)(p % Wo);
+    p /= Wo;
+    const int ho = (int)(p % Ho);
+    const int n = (int)(p / Ho);
+    float best[V];
+    int bi[V];
+    bool any = false;
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+      const int h = ho * 2 - pad + r;
+      if (h < 0 || h >= H) continue;
+#pragma unroll
+      for (int s = 0; s < 3; ++s) {
+        const int w = wo * 2 - pad + s;
+        if (w < 0 || w >= W) continue;
+        Vec<T> v;
+        float f[V];
+        v.load(x + (((int64_t)n * H + h) * W + w) * C + (int64_t)cg * V);
+        v.unpack(f);
+#pragma unroll
+        for (int j = 0; j < V; ++j)
+          if (!any || f[j] > best[j]) { best[j] = f[j]; bi[j] = r * 3 + s; }
+        any = true;
+      }
+    }
+    Vec<T> o;
+    o.pack(best);
+    const int64_t ob = (((int64_t)n * Ho + ho) * Wo + wo) * C + (int64_t)cg * V;
+    o.store(y + ob);
+#pragma unroll
+    for (int j = 0; j < V; ++j) argmax[ob + j] = (uint8_t)bi[j];
+  }
+}
+
+template <typename T>
+__global__ void maxpool_bwd_vec_kernel(const T* __restrict__ dy, const uint8_t* __restrict__ argmax, T* dx, int N, int H,
+                                       int W, int C, int Ho, int Wo, int pad, float beta) {
+  constexpr int V = Vec<T>::N;
+  const int CV = C / V;
+  const int64_t total = (int64_t)N * H * W * CV;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int cg = (int)(i % CV);
+    int64_t p = i / CV;
+    const int w = (int)(p % W);
+    p /= W;
+    const int h = (int)(p % H);
+    const int n = (int)(p / H);
+    float acc[V];
+#pragma unroll
+    for (int j = 0; j < V; ++j) acc[j] = 0.f;
+    for (int r = 0; r < 3; ++r) {
+      const int t = h + pad - r;
+      if (t < 0 || (t & 1)) continue;
+      const int ho = t >> 1;
+      if (ho >= Ho) continue;
+      for (int s = 0; s < 3; ++s) {
+        const int u = w + pad - s;
+        if (u < 0 || (u & 1)) continue;
+        const int wo = u >> 1;
+        if (wo >= Wo) continue;
+        const int64_t ob = (((int64_t)n * Ho + ho) * Wo + wo) * C + (int64_t)cg * V;
+        Vec<T> g;
+        float f[V];
+        g.load(dy + ob);
+        g.unpack(f);
+        uint8_t am[V];
+        if (V == 8) *reinterpret_cast<uint2*>(am) = *reinterpret_cast<const uint2*>(argmax + ob);
+        else        *reinterpret_cast<uint32_t*>(am) = *reinterpret_cast<const uint32_t*>(argmax + ob);
+        const uint8_t me = (uint8_t)(r * 3 + s);
+#pragma unroll
+        for (int j = 0; j < V; ++j)
+          if (am[j] == me) acc[j] += f[j];
+      }
+    }
+    const int64_t xb = (((int64_t)n * H + h) * W + w) * C + (int64_t)cg * V;
+    if (beta != 0.f) {
+      Vec<T> o;
+      float f[V];
+      o.load(dx + xb);
+      o.unpack(f);
+#pragma unroll
+      for (int j = 0; j < V; ++j) acc[j] += f[j];
+    }
+    Vec<T> o;
+    o.pack(acc);
+    o.store(dx + xb);
+  }
+}
+
 template <typename TI, typename TO>
 __global__ void avgpool_fwd_kernel(const TI* __restrict__ x, TO* __restrict__ y, int N, int H, int W, int C, int k,
                                    int s, int Ho, int Wo, int Cout, int cb) {
@@ -127,7 +226,14 @@ extern "C" int rn_maxpool3x3s2_fwd(const void* x, void* y, uint8_t* argmax, int3
              "maxpool_fwd: bad arguments");
   RN_REQUIRE((Ho - 1) * 2 - pad < H && (Wo - 1) * 2 - pad < W, "maxpool_fwd: empty window");
   const int g = grid_for((int64_t)N * Ho * Wo * C, 256);
-  if (dtype == RN_F32)
+  const bool al = (((uintptr_t)x | (uintptr_t)y) & 15) == 0 && ((uintptr_t)argmax & 7) == 0;
+  if (dtype == RN_F32 && C % 4 == 0 && al)
+    maxpool_fwd_vec_kernel<float><<<grid_for((int64_t)N * Ho * Wo * C / 4, 256, 16), 256, 0, as_stream(stream)>>>(
+        (const float*)x, (float*)y, argmax, N, H, W, C, Ho, Wo, pad);
+  else if (dtype == RN_BF16 && C % 8 == 0 && al)
+    maxpool_fwd_vec_kernel<__nv_bfloat16><<<grid_for((int64_t)N * Ho * Wo * C / 8, 256, 16), 256, 0, as_stream(stream)>>>(
+        (const __nv_bfloat16*)x, (__nv_bfloat16*)y, argmax, N, H, W, C, Ho, Wo, pad);
+  else if (dtype == RN_F32)
     maxpool_fwd_kernel<float><<<g, 256, 0, as_stream(stream)>>>((const float*)x, (float*)y, argmax, N, H, W, C, Ho, Wo, pad);
   else if (dtype == RN_BF16)
     maxpool_fwd_kernel<__nv_bfloat16><<<g, 256, 0, as_stream(stream)>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)y,
@@ -142,7 +248,14 @@ extern "C" int rn_maxpool3x3s2_bwd(const void* dy, const uint8_t* argmax, void* 
                                    void* stream) {
   RN_REQUIRE(dy && dx && argmax && N > 0 && H > 0 && W > 0 && C > 0 && Ho > 0 && Wo > 0, "maxpool_bwd: bad arguments");
   const int g = grid_for((int64_t)N * H * W * C, 256);
-  if (dtype == RN_F32)
+  const bool al = (((uintptr_t)dy | (uintptr_t)dx) & 15) == 0 && ((uintptr_t)argmax & 7) == 0;
+  if (dtype == RN_F32 && C % 4 == 0 && al)
+    maxpool_bwd_vec_kernel<float><<<grid_for((int64_t)N * H * W * C / 4, 256, 16), 256, 0, as_stream(stream)>>>(
+        (const float*)dy, argmax, (float*)dx, N, H, W, C, Ho, Wo, pad, beta);
+  else if (dtype == RN_BF16 && C % 8 == 0 && al)
+    maxpool_bwd_vec_kernel<__nv_bfloat16><<<grid_for((int64_t)N * H * W * C / 8, 256, 16), 256, 0, as_stream(stream)>>>(
+        (const __nv_bfloat16*)dy, argmax, (__nv_bfloat16*)dx, N, H, W, C, Ho, Wo, pad, beta);
+  else if (dtype == RN_F32)
     maxpool_bwd_kernel<float><<<g, 256, 0, as_stream(stream)>>>((const float*)dy, argmax, (float*)dx, N, H, W, C, Ho, Wo,
                                                                 pad, beta);
   else if (dtype == RN_BF16)

@@ -307,11 +307,58 @@ class Executor:
             return "tc"
         return "simt"
 
+    def _is_stem(self, n):
+        """Convolutions over fewer than 16 channels (the image): unfolded once, then 1x1 tensor-core GEMMs."""
+        d = self._desc(n)
+        if not (self.use_tc and d.Cin < 16):
+            return False
+        kpad = _align(d.k * d.k * d.Cin, 64)
+        d1 = ConvDesc(d.N, d.Ho, d.Wo, kpad, d.Ho, d.Wo, d.Cout, 1, 1, 0, self.rn_dt)
+        return bool(lib.rn_convtc_supported(C.byref(d1), 0))
+
+    def _stem_setup(self, n):
+        if hasattr(n, "_stem"):
+            return n._stem
+        d = self._desc(n)
+        kv = n.vars["kernel"]
+        rows = d.k * d.k * d.Cin
+        kpad = _align(rows, 64)
+        d1 = ConvDesc(d.N, d.Ho, d.Wo, kpad, d.Ho, d.Wo, d.Cout, 1, 1, 0, self.rn_dt)
+        cols = torch.zeros(d.N * d.Ho * d.Wo, kpad, dtype=torch.bfloat16, device=self.dev)
+        wf = torch.zeros(d.Cout, kpad, dtype=torch.bfloat16, device=self.dev)
+        fn = (lambda s, pw=self._wptr(kv), r=rows, co=d.Cout, kp=kpad, a=ptr(wf):
+              check(lib.rn_stem_weights(pw, r, co, kp, a, s), "rn_stem_weights"))
+        if not hasattr(self, "_relayout"):
+            self._relayout = []
+        self._relayout.append(fn)
+        fn(torch.cuda.current_stream().cuda_stream)
+        self._keep += [d, d1, cols, wf]
+        n._stem = dict(d=d, d1=d1, cols=cols, wf=wf, rows=rows, kpad=kpad)
+        return n._stem
+
+    def _plan_raw(self, d, kind, a_buf, b_buf, out):
+        nbytes = lib.rn_convtc_scratch_bytes(C.byref(d), kind)
+        scratch = torch.zeros(max(nbytes, 16), dtype=torch.uint8, device=self.dev)
+        self._keep.append(scratch)
+        plan = C.c_void_p()
+        outp = out if isinstance(out, int) else ptr(out)
+        check(lib.rn_convtc_plan_create(C.byref(d), kind, ptr(a_buf), ptr(b_buf), outp, ptr(scratch), nbytes,
+                                        C.byref(plan)), "rn_convtc_plan_create")
+        self._plans.append(plan)
+        return lambda s, p=plan, beta=0.0: check(lib.rn_convtc_run(p, beta, s), "rn_convtc_run")
+
     def _conv_fprop(self, n):
         x, y = n.inputs[0], n.outputs[0]
         d = self._desc(n)
         self._keep.append(d)
         kv = n.vars["kernel"]
+        if self._is_stem(n):
+            st = self._stem_setup(n)
+            sdt = RN_BF16 if x.buf.dtype == torch.bfloat16 else RN_F32
+            im2col = (lambda s, a=(ptr(x.buf), ptr(st["cols"]), d.N, d.H, d.W, d.Cin, d.Ho, d.Wo, d.k, d.stride, d.pad, st["kpad"], sdt):
+                      check(lib.rn_im2col(*a, s), "rn_im2col"))
+            run = self._plan_raw(st["d1"], 0, st["cols"], st["wf"], y.buf)
+            return ("conv_fprop_tc:" + y.name, lambda s, im2col=im2col, run=run: (im2col(s), run(s)))
         if self._conv_impl(n, 0) == "tc":
             return ("conv_fprop_tc:" + y.name, self._tc_plan(n, d, 0, x.buf, y.buf))
         w = self._wptr(kv, "Wb" if self.bf16 else "W")
@@ -545,7 +592,15 @@ class Executor:
                     self._emit(bwd, "conv_dgrad:" + y.name, lambda s, d=d, pdy=ptr(dy), w=w, pdx=ptr(dxb), beta=beta:
                                check(lib.rn_conv2d_dgrad(C.byref(d), pdy, w, pdx, beta, s), "rn_conv2d_dgrad"),
                                node=n, dy=dy, dx=dxb, beta=beta)
-            if self._conv_impl(n, 2) == "tc":
+            if self._is_stem(n) and lib.rn_convtc_supported(C.byref(self._stem_setup(n)["d1"]), 2):
+                st = self._stem_setup(n)
+                tmp = torch.zeros(st["kpad"], d.Cout, dtype=torch.float32, device=self.dev)
+                self._keep.append(tmp)
+                run = self._plan_raw(st["d1"], 2, st["cols"], dy, tmp)
+                cp = (lambda s, a=ptr(tmp), b=self._wptr(kv, "G"), k=st["rows"] * d.Cout:
+                      check(lib.rn_cast(a, b, k, RN_F32, RN_F32, s), "rn_cast"))
+                self._emit(bwd, "conv_wgrad_tc:" + y.name, lambda s, run=run, cp=cp: (run(s), cp(s)), node=n, dy=dy)
+            elif self._conv_impl(n, 2) == "tc":
                 run = self._tc_plan(n, d, 2, x.buf, self._wptr(kv, "G"), b_buf=dy)
                 self._emit(bwd, "conv_wgrad_tc:" + y.name, run, node=n, dy=dy)
             else:

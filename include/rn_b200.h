@@ -90,6 +90,15 @@ int rn_convtc_plan_destroy(rn_convtc_plan* plan);
  * ([k*k][Cout][Cin] for fprop, [k*k][Cin][Cout] for dgrad). Either output may be NULL. */
 int rn_weights_to_bf16(const float* w_hwio, int k, int Cin, int Cout, void* w_fprop, void* w_dgrad, void* stream);
 
+/* Stem convolution (the 3-channel image, resnet_model_official.py:250 / :310): TMA rows and UMMA K
+ * steps need >= 16 bytes of channels, so the image is unfolded into bf16 rows of
+ * Kpad = roundup(k*k*Cin, 64) columns ordered (r, s, ci) and the tensor-core kernels run the layer as
+ * a 1x1 convolution over Kpad channels (rn_convtc_* with k=1).  rn_stem_weights builds the matching
+ * bf16 [Cout][Kpad] operand from the fp32 HWIO master. */
+int rn_im2col(const void* x, void* cols, int32_t N, int32_t H, int32_t W, int32_t Cin, int32_t Ho, int32_t Wo,
+              int32_t k, int32_t stride, int32_t pad, int32_t Kpad, int32_t src_dtype, void* stream);
+int rn_stem_weights(const float* w_hwio, int32_t rows, int32_t Cout, int32_t Kpad, void* w_fprop, void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * Batch normalisation + (leaky) ReLU (+ residual add)
  *   replaces tf.layers.batch_normalization(fused=True) + tf.nn.relu, resnet_model_official.py:41-50
