@@ -721,8 +721,32 @@ class Executor:
             self.refresh_shadow_weights()
         return self.launches_per_step
 
+    def _segments(self):
+        """Launch list of one step cut where gradient buckets become complete:
+        [(launches, [bucket indices to all-reduce afterwards])...], then the update list."""
+        segs = []
+        if self.world > 1 and self.buckets:
+            start = 0
+            bi = 0
+            # buckets are ordered by readiness (monotone `ready`)
+            cuts = sorted(set(b[2] for b in self.buckets))
+            prev = 0
+            for c in cuts:
+                lst = (self.fwd if prev == 0 else []) + self.bwd[prev:c]
+                ready = [i for i, b in enumerate(self.buckets) if b[2] == c]
+                segs.append((lst, ready))
+                prev = c
+            if prev < len(self.bwd):
+                segs.append((self.bwd[prev:], []))
+        else:
+            segs.append((self.fwd + (self.bwd if self.train else []), []))
+        return segs
+
     def capture(self):
-        """Capture one full step (forward, backward, all-reduce, update) in a CUDA graph."""
+        """Capture the step in CUDA graphs.  Single GPU: one graph for the whole step.  Multi-GPU: one
+        graph per backward segment between gradient-bucket boundaries plus one for the update; the NCCL
+        all-reduces are issued eagerly on the side stream between the segment launches (ordering by
+        stream events), so communication still overlaps the remaining backward segments."""
         if self._graph_exec is not None:
             return
         torch.cuda.synchronize(self.dev)
@@ -742,27 +766,45 @@ class Executor:
                 self.forward()
         torch.cuda.current_stream().wait_stream(side)
         torch.cuda.synchronize(self.dev)
-        gexec = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(gexec):
-            if self.train:
-                self._step_launches()
-            else:
-                self.forward()
-        self._graph_exec = gexec
+        graphs = []
+        pool = None
+        lists = [(lst, ready) for lst, ready in self._segments()] if self.train else [(self.fwd, [])]
+        if self.train:
+            lists.append((self.update, None))
+        for lst, ready in lists:
+            gexec = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(gexec, pool=pool):
+                self._run_list(lst, torch.cuda.current_stream().cuda_stream)
+            pool = gexec.pool()
+            graphs.append((gexec, ready))
+        self._graph_exec = graphs
+
+    def _replay(self):
+        import torch.distributed as dist
+        cur = torch.cuda.current_stream()
+        for gexec, ready in self._graph_exec:
+            if ready is None:                      # the update graph waits for every all-reduce
+                if self.world > 1:
+                    cur.wait_stream(self.comm_stream)
+                gexec.replay()
+                continue
+            gexec.replay()
+            for bi in ready:
+                self._reduce_bucket(bi, cur, dist)
 
     def step(self):
         """One synchronous training step (== sess.run(train_op), resnet_cifar_train.py:343-344)."""
         if not self.train:
             raise RuntimeError("executor was built with train=False")
         if self._graph_exec is not None:
-            self._graph_exec.replay()
+            self._replay()
         else:
             self._step_launches()
         self.global_step += 1
 
     def run_forward(self):
         if self._graph_exec is not None and not self.train:
-            self._graph_exec.replay()
+            self._replay()
         else:
             self.forward()
 
