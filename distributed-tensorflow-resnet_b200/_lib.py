@@ -55,6 +55,8 @@ SIGNATURES = {
     "rn_convtc_run": (C.c_int, [vp, f32, vp]),
     "rn_convtc_plan_destroy": (C.c_int, [vp]),
     "rn_weights_to_bf16": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, vp, vp, vp]),
+    "rn_relayout_job_bytes": (sz, []),
+    "rn_weights_to_bf16_batched": (C.c_int, [vp, i32, vp]),
     "rn_im2col": (C.c_int, [vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, i32, i32, i32, vp]),
     "rn_stem_weights": (C.c_int, [vp, i32, i32, i32, vp, vp]),
     "rn_bn_scratch_bytes": (sz, [i64, i32]),

@@ -399,6 +399,37 @@ __global__ void weights_to_bf16_kernel(const float* __restrict__ w, int taps, in
   }
 }
 
+// All conv kernels of the net in ONE launch: a device table of jobs, blockIdx.y = job.
+struct RelayoutJob {
+  const float* w;
+  __nv_bfloat16* wf;
+  __nv_bfloat16* wd;
+  int taps, Cin, Cout, kpad;      // kpad > 0: stem layout bf16 [Cout][kpad] from [taps*Cin][Cout]
+};
+__global__ void weights_to_bf16_batched_kernel(const RelayoutJob* __restrict__ jobs) {
+  const RelayoutJob j = jobs[blockIdx.y];
+  if (j.kpad > 0) {
+    const int rows = j.taps * j.Cin;
+    const int64_t total = (int64_t)j.Cout * j.kpad;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+      const int kk = (int)(i % j.kpad);
+      const int co = (int)(i / j.kpad);
+      j.wf[i] = __float2bfloat16_rn(kk < rows ? j.w[(int64_t)kk * j.Cout + co] : 0.f);
+    }
+    return;
+  }
+  const int64_t n = (int64_t)j.taps * j.Cin * j.Cout;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const int co = (int)(i % j.Cout);
+    const int64_t r = i / j.Cout;
+    const int ci = (int)(r % j.Cin);
+    const int tap = (int)(r / j.Cin);
+    const __nv_bfloat16 v = __float2bfloat16_rn(j.w[i]);
+    if (j.wd) j.wd[i] = v;
+    if (j.wf) j.wf[((int64_t)tap * j.Cout + co) * j.Cin + ci] = v;
+  }
+}
+
 // ------------------------------------------------------------------------------------------
 // host side: tensor maps and plans
 // ------------------------------------------------------------------------------------------
@@ -898,4 +929,12 @@ extern "C" int rn_stem_weights(const float* w_hwio, int32_t rows, int32_t Cout, 
   stem_weights_kernel<<<grid_for((int64_t)Cout * Kpad, 256), 256, 0, as_stream(stream)>>>(w_hwio, rows, Cout, Kpad,
                                                                                          (__nv_bfloat16*)w_fprop);
   return check_launch("stem_weights_kernel");
+}
+
+extern "C" size_t rn_relayout_job_bytes(void) { return sizeof(rn::RelayoutJob); }
+
+extern "C" int rn_weights_to_bf16_batched(const void* jobs_device, int32_t njobs, void* stream) {
+  RN_REQUIRE(jobs_device && njobs > 0 && njobs <= 65535, "weights_to_bf16_batched: bad arguments");
+  weights_to_bf16_batched_kernel<<<dim3(16, njobs), 256, 0, as_stream(stream)>>>((const rn::RelayoutJob*)jobs_device);
+  return check_launch("weights_to_bf16_batched_kernel");
 }

@@ -85,6 +85,9 @@ class Executor:
         self.world = int(world_size)
         self.rank = int(rank)
         self.use_tc = bool(use_tensor_cores) and self.bf16
+        import os as _os
+        self.overlap_wgrad = train and not _os.environ.get("RN_NO_OVERLAP")
+        self.wg_stream = torch.cuda.Stream(device=self.dev) if self.overlap_wgrad else None
         self.loss = loss   # (probs, scalars) tensors from graph.softmax_xent
         self.global_step = 0
         self.launches_per_step = 0
@@ -330,7 +333,9 @@ class Executor:
               check(lib.rn_stem_weights(pw, r, co, kp, a, s), "rn_stem_weights"))
         if not hasattr(self, "_relayout"):
             self._relayout = []
+            self._relayout_jobs = []
         self._relayout.append(fn)
+        self._relayout_jobs.append((self._wptr(kv), ptr(wf), 0, d.k * d.k, d.Cin, d.Cout, kpad))
         fn(torch.cuda.current_stream().cuda_stream)
         self._keep += [d, d1, cols, wf]
         n._stem = dict(d=d, d1=d1, cols=cols, wf=wf, rows=rows, kpad=kpad)
@@ -379,7 +384,9 @@ class Executor:
                   check(lib.rn_weights_to_bf16(pw, k, ci, co, a, b, s), "rn_weights_to_bf16"))
             if not hasattr(self, "_relayout"):
                 self._relayout = []
+                self._relayout_jobs = []
             self._relayout.append(fn)
+            self._relayout_jobs.append((self._wptr(kv), ptr(wf), ptr(wd), k * k, Cin, Cout, 0))
             fn(torch.cuda.current_stream().cuda_stream)
         return n._tcw
 
@@ -646,8 +653,14 @@ class Executor:
                             ptr(self.W), ptr(self.Gd), ptr(self.Mom), ptr(self.Wb), self.n_flat, ptr(self.mask),
                             ptr(self.hyper), inv_R, self.wd, self.momentum, use_mom, ptr(self.sumsq),
                             ptr(self.scratch), self.scratch_bytes, s), "rn_sgd_momentum_fused"))]
-        for i, fn in enumerate(getattr(self, "_relayout", [])):
-            self.update.append(("weights_to_bf16:%d" % i, fn))
+        jobs = getattr(self, "_relayout_jobs", [])
+        if jobs:     # one launch re-lays out every conv kernel for the tensor-core path
+            import struct
+            assert lib.rn_relayout_job_bytes() == 40
+            blob = b"".join(struct.pack("<QQQiiii", *j) for j in jobs)
+            self._jobs_dev = torch.frombuffer(bytearray(blob), dtype=torch.uint8).to(self.dev)
+            self.update.append(("weights_to_bf16", lambda s, p=ptr(self._jobs_dev), n=len(jobs):
+                                check(lib.rn_weights_to_bf16_batched(p, n, s), "rn_weights_to_bf16_batched")))
 
     def set_lr(self, lr):
         """The reference feeds the learning rate every step (resnet_cifar_train.py:297-299); here
@@ -673,6 +686,46 @@ class Executor:
         for _, fn in lst:
             fn(st)
 
+    def _run_overlapped(self, lst, cur):
+        """Run a launch list on stream `cur`, with every weight-gradient kernel forked onto a side stream:
+        a conv layer's wgrad and dgrad are independent, so the wgrad GEMMs (tensor-bound, one CTA per SM)
+        run concurrently with the batch-norm backward kernels (HBM-bound) that follow the dgrad.  A wgrad
+        reads dy; the main stream therefore waits for it before any kernel that overwrites that buffer
+        (the in-place residual-stream accumulation) and at the end of the list."""
+        if not self.overlap_wgrad:
+            return self._run_list(lst, cur.cuda_stream)
+        side = self.wg_stream
+        pending = []
+        for name, fn in lst:
+            m = self.meta.get(name)
+            if name.startswith("conv_wgrad"):
+                ev = torch.cuda.Event()
+                ev.record(cur)
+                side.wait_event(ev)
+                fn(side.cuda_stream)
+                done = torch.cuda.Event()
+                done.record(side)
+                pending.append((m["dy"].data_ptr(), done))
+                continue
+            if pending:
+                dx = m.get("dx") if m else None
+                if m is None or name.startswith("grad_"):
+                    for _, e in pending:
+                        cur.wait_event(e)
+                    pending = []
+                elif dx is not None:
+                    p = dx.data_ptr()
+                    keep = []
+                    for q, e in pending:
+                        if q == p:
+                            cur.wait_event(e)
+                        else:
+                            keep.append((q, e))
+                    pending = keep
+            fn(cur.cuda_stream)
+        for _, e in pending:
+            cur.wait_event(e)
+
     def forward(self):
         st = torch.cuda.current_stream().cuda_stream
         self._run_list(self.fwd, st)
@@ -681,20 +734,12 @@ class Executor:
         import torch.distributed as dist
         cur = torch.cuda.current_stream()
         st = cur.cuda_stream
-        self._run_list(self.fwd, st)
-        if self.world > 1:
-            bi = 0
-            for i, (_, fn) in enumerate(self.bwd):
-                fn(st)
-                while bi < len(self.buckets) and self.buckets[bi][2] <= i + 1:
-                    self._reduce_bucket(bi, cur, dist)
-                    bi += 1
-            while bi < len(self.buckets):
+        for lst, ready in self._segments():
+            self._run_overlapped(lst, cur)
+            for bi in ready:
                 self._reduce_bucket(bi, cur, dist)
-                bi += 1
+        if self.world > 1:
             cur.wait_stream(self.comm_stream)
-        else:
-            self._run_list(self.bwd, st)
         self._run_list(self.update, st)
 
     def _reduce_bucket(self, bi, cur, dist):
@@ -774,7 +819,10 @@ class Executor:
         for lst, ready in lists:
             gexec = torch.cuda.CUDAGraph()
             with torch.cuda.graph(gexec, pool=pool):
-                self._run_list(lst, torch.cuda.current_stream().cuda_stream)
+                if ready is None:
+                    self._run_list(lst, torch.cuda.current_stream().cuda_stream)
+                else:
+                    self._run_overlapped(lst, torch.cuda.current_stream())
             pool = gexec.pool()
             graphs.append((gexec, ready))
         self._graph_exec = graphs

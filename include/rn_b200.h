@@ -90,6 +90,12 @@ int rn_convtc_plan_destroy(rn_convtc_plan* plan);
  * ([k*k][Cout][Cin] for fprop, [k*k][Cin][Cout] for dgrad). Either output may be NULL. */
 int rn_weights_to_bf16(const float* w_hwio, int k, int Cin, int Cout, void* w_fprop, void* w_dgrad, void* stream);
 
+/* The same re-layouts for every conv kernel of a net in ONE launch.  `jobs_device` is a device array
+ * of njobs records { const float* w; bf16* w_fprop; bf16* w_dgrad; int32 taps, Cin, Cout, kpad; }
+ * (rn_relayout_job_bytes() each); kpad > 0 selects the stem layout of rn_stem_weights. */
+size_t rn_relayout_job_bytes(void);
+int rn_weights_to_bf16_batched(const void* jobs_device, int32_t njobs, void* stream);
+
 /* Stem convolution (the 3-channel image, resnet_model_official.py:250 / :310): TMA rows and UMMA K
  * steps need >= 16 bytes of channels, so the image is unfolded into bf16 rows of
  * Kpad = roundup(k*k*Cin, 64) columns ordered (r, s, ci) and the tensor-core kernels run the layer as
