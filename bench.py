@@ -163,10 +163,14 @@ def roofline_report(ex, graph, per_launch_ms, pk):
         table.append(row)
     top = next((r for r in table if "bound" in r), None)
     roof = None
+    traffic = None
+    tp = os.path.join(ROOT, "profiles", "traffic.json")     # dram bytes per launch from the last ncu --set full capture
+    if top and os.path.exists(tp):
+        traffic = json.load(open(tp)).get(top["kernel"])
     if top:
         roof = dict(kernel=top["kernel"], bound=top["bound"], achieved=top["achieved"],
                     peak=pk["tf_sust"] if top["bound"] == "tensor" else pk["hbm"], unit=top["unit"], frac=top["frac"],
-                    traffic=None, peak_source=pk["src"] + (" sustained bf16" if top["bound"] == "tensor" else " copy"),
+                    traffic=traffic, peak_source=pk["src"] + (" sustained bf16" if top["bound"] == "tensor" else " copy"),
                     share_of_step=top["share"], launches_per_step=top["launches"])
     return roof, table, total
 
@@ -323,6 +327,26 @@ def run_ours(args):
     h2d = host_img.numel() * 4 + host_lab.numel() * 4
     d2h = 8
 
+    # ---- gradient aggregation alone (C5): all-reduce of the flat fp32 fusion buffer, bus bandwidth
+    allreduce = None
+    if world > 1:
+        nbytes = ex.Gd.numel() * 4
+        for _ in range(3):
+            dist.all_reduce(ex.Gd)
+        barrier()
+        e0.record()
+        for _ in range(10):
+            dist.all_reduce(ex.Gd)
+        e1.record()
+        barrier()
+        t = torch.tensor([e0.elapsed_time(e1) / 10], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ar_ms = t.item()
+        allreduce = {"bytes": nbytes, "ms": round(ar_ms, 4), "replicas_to_aggregate": world,
+                     "bus_gbs": round(2.0 * (world - 1) / world * nbytes / ar_ms / 1e6, 1), "nvlink_nominal_gbs": 900.0,
+                     "buckets_in_step": len(ex.buckets)}
+        ex.Gd.zero_()
+
     line = None
     if rank == 0:
         # ---- per-kernel roofline (un-captured launch list, CUDA events per launch) ------------
@@ -371,6 +395,7 @@ def run_ours(args):
             "gpu_launches_outside_graph": int(launched_live),
             "clocks": clocks,
             "roofline": roof,
+            "allreduce": allreduce,
             "conv": {"tflops_all_conv_kernels": round(conv_fl / conv_ms / 1e9, 2) if conv_ms else None,
                      "frac_of_sustained_peak": round(conv_fl / conv_ms / 1e9 / pk["tf_sust"], 4) if conv_ms else None,
                      "gflop_per_step": round(conv_fl / 1e9, 2)},

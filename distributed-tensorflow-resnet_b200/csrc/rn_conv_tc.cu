@@ -222,12 +222,15 @@ struct TcWgradParams {
   CUtensorMap dy_map;
   float* partial;                 // [splits][taps*Cin][Cout]
   int Cin, Cout, taps, cin_blocks, RB;
-  int acc;                        // accumulators per CTA; row blocks per CTA = 2 * acc
+  int bwA, bwB;                   // channels per A / B box (64, 32 or 16 -> 128 / 64 / 32-byte swizzled rows)
+  int blocksA;                    // A boxes per 128-row accumulator (128 / bwA)
+  uint32_t a_box_bytes, b_box_bytes;
+  int acc;                        // accumulators per CTA; row blocks per CTA = blocksA * acc
   int row_groups, block_n, n_tiles;
   int PW, PH, PN, tiles_w, tiles_h, tiles_n, k_tiles;
   int splits, tiles_per_split;
   int kp, stages;
-  uint32_t box_bytes, stage_bytes, tmem_cols;
+  uint32_t stage_bytes, tmem_cols;
   int8_t tap_map[TC_MAX_TAPS], tap_dw[TC_MAX_TAPS], tap_dh[TC_MAX_TAPS];
 };
 
@@ -259,8 +262,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_wgrad_tc_kernel(const __gr
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   const int total = p.row_groups * p.n_tiles * p.splits;
-  const int rb_per_cta = 2 * p.acc;
-  const int nb = p.block_n / 64;
+  const int rb_per_cta = p.blocksA * p.acc;
+  const int nb = p.block_n / p.bwB;
 
   if (warp == 0) {
     if (lane == 0) {
@@ -281,16 +284,16 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_wgrad_tc_kernel(const __gr
           const int n0 = (q / p.tiles_h) * p.PN;
           mbar_wait(&empty[stage], phase ^ 1);
           uint8_t* sa = smem + (size_t)stage * p.stage_bytes;
-          mbar_expect_tx(&full[stage], (uint32_t)(valid + nb) * p.box_bytes);
+          mbar_expect_tx(&full[stage], (uint32_t)valid * p.a_box_bytes + (uint32_t)nb * p.b_box_bytes);
           for (int j = 0; j < valid; ++j) {
             const int rb = rg * rb_per_cta + j;
             const int tap = rb / p.cin_blocks, cb = rb - tap * p.cin_blocks;
-            tma_load_4d(sa + (size_t)j * p.box_bytes, &p.x_map[p.tap_map[tap]], &full[stage], cb * 64,
+            tma_load_4d(sa + (size_t)j * p.a_box_bytes, &p.x_map[p.tap_map[tap]], &full[stage], cb * p.bwA,
                         w0 + p.tap_dw[tap], h0 + p.tap_dh[tap], n0);
           }
-          uint8_t* sbm = sa + (size_t)rb_per_cta * p.box_bytes;
+          uint8_t* sbm = sa + (size_t)rb_per_cta * p.a_box_bytes;
           for (int j = 0; j < nb; ++j)
-            tma_load_4d(sbm + (size_t)j * p.box_bytes, &p.dy_map, &full[stage], nt * p.block_n + j * 64, w0, h0, n0);
+            tma_load_4d(sbm + (size_t)j * p.b_box_bytes, &p.dy_map, &full[stage], nt * p.block_n + j * p.bwB, w0, h0, n0);
           if (++stage == p.stages) { stage = 0; phase ^= 1; }
         }
       }
@@ -306,7 +309,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_wgrad_tc_kernel(const __gr
         const int rg = it / (p.splits * p.n_tiles);
         int valid = p.RB - rg * rb_per_cta;
         if (valid > rb_per_cta) valid = rb_per_cta;
-        const int nacc = (valid + 1) / 2;
+        const int nacc = (valid + p.blocksA - 1) / p.blocksA;
+        const uint32_t rowA = (uint32_t)p.bwA * 2, rowB = (uint32_t)p.bwB * 2;
+        const uint32_t ltA = swizzle_layout_type(rowA), ltB = swizzle_layout_type(rowB);
         mbar_wait(tempty, tphase ^ 1);
         tc_fence_after();
         const int kt_begin = z * p.tiles_per_split, kt_end = min((z + 1) * p.tiles_per_split, p.k_tiles);
@@ -314,11 +319,13 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_wgrad_tc_kernel(const __gr
           mbar_wait(&full[stage], phase);
           tc_fence_after();
           const uint32_t a_addr = base_u32 + (uint32_t)stage * p.stage_bytes;
-          const uint32_t b_addr = a_addr + (uint32_t)rb_per_cta * p.box_bytes;
+          const uint32_t b_addr = a_addr + (uint32_t)rb_per_cta * p.a_box_bytes;
           for (int a = 0; a < nacc; ++a) {
             for (int ks = 0; ks < ksteps; ++ks) {
-              const uint64_t da = make_smem_desc(a_addr + (uint32_t)(2 * a) * p.box_bytes + ks * 2048, p.box_bytes, 1024, 2);
-              const uint64_t db = make_smem_desc(b_addr + ks * 2048, p.box_bytes, 1024, 2);
+              // MN-major operands: LBO = distance between consecutive channel boxes, SBO = 8 pixel rows
+              const uint64_t da = make_smem_desc(a_addr + (uint32_t)(p.blocksA * a) * p.a_box_bytes + ks * 16 * rowA,
+                                                 p.a_box_bytes, 8 * rowA, ltA);
+              const uint64_t db = make_smem_desc(b_addr + ks * 16 * rowB, p.b_box_bytes, 8 * rowB, ltB);
               umma_bf16(tmem_base + (uint32_t)(a * p.block_n), da, db, idesc, (kt > kt_begin || ks > 0) ? 1u : 0u);
             }
           }
@@ -341,12 +348,13 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_wgrad_tc_kernel(const __gr
       mbar_wait(tfull, tphase);
       tc_fence_after();
       for (int a = 0; a < p.acc; ++a) {
-        const int rb = rg * rb_per_cta + 2 * a + (row >> 6);
-        if (rb - (row >> 6) >= p.RB) break;                       // warp-uniform: this accumulator was not computed
+        const int rb0 = rg * rb_per_cta + p.blocksA * a;
+        if (rb0 >= p.RB) break;                                   // uniform: this accumulator was not computed
+        const int rb = rb0 + row / p.bwA;
         const bool ok = rb < p.RB;
         const int tap = ok ? rb / p.cin_blocks : 0;
         const int cb = rb - tap * p.cin_blocks;
-        const int64_t grow = (int64_t)tap * p.Cin + cb * 64 + (row & 63);
+        const int64_t grow = (int64_t)tap * p.Cin + cb * p.bwA + (row % p.bwA);
         float* dst = p.partial + ((int64_t)z * rows_total + grow) * p.Cout + (int64_t)nt * p.block_n;
         const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(a * p.block_n);
         for (int c0 = 0; c0 < p.block_n; c0 += 16) {
@@ -543,26 +551,37 @@ static void forward_tap(int r, int s, int pad, int stride, int8_t* map, int8_t* 
 
 struct WgradShape {
   int block_n, n_tiles, acc, cin_blocks, RB, row_groups, kp, stages, PW, PH, PN, tiles_w, tiles_h, tiles_n, k_tiles;
-  int splits, tiles_per_split;
-  uint32_t box_bytes, stage_bytes, tmem_cols;
+  int splits, tiles_per_split, bwA, bwB, blocksA;
+  uint32_t a_box_bytes, b_box_bytes, stage_bytes, tmem_cols;
   size_t smem, scratch;
 };
 
+static int box_width(int c) { return c % 64 == 0 ? 64 : (c % 32 == 0 ? 32 : (c % 16 == 0 ? 16 : 0)); }
+
 static bool wgrad_shape(const rn_conv_desc* d, WgradShape* w) {
-  if (d->Cin % 64 || d->Cout % 64) return false;
-  w->block_n = d->Cout % 256 == 0 ? 256 : (d->Cout % 128 == 0 ? 128 : 64);
+  w->bwA = box_width(d->Cin);
+  w->bwB = box_width(d->Cout);
+  if (!w->bwA || !w->bwB) return false;
+  w->block_n = choose_block_n(d->Cout);
+  if (w->block_n == 0 || w->block_n % w->bwB) return false;
   w->n_tiles = d->Cout / w->block_n;
+  w->blocksA = 128 / w->bwA;
+  w->cin_blocks = d->Cin / w->bwA;
+  w->RB = d->k * d->k * w->cin_blocks;
   w->acc = 512 / w->block_n;
   if (w->acc > 4) w->acc = 4;
-  w->cin_blocks = d->Cin / 64;
-  w->RB = d->k * d->k * w->cin_blocks;
-  if (w->acc > (w->RB + 1) / 2) w->acc = (w->RB + 1) / 2;
-  w->row_groups = (w->RB + 2 * w->acc - 1) / (2 * w->acc);
-  const int boxes = 2 * w->acc + w->block_n / 64;
-  w->kp = 64;
-  if ((size_t)boxes * 64 * 128 * 3 > 200 * 1024) w->kp = 32;
-  w->box_bytes = (uint32_t)w->kp * 128;
-  w->stage_bytes = (uint32_t)boxes * w->box_bytes;
+  const int need_acc = (w->RB + w->blocksA - 1) / w->blocksA;
+  if (w->acc > need_acc) w->acc = need_acc;
+  w->row_groups = (w->RB + w->blocksA * w->acc - 1) / (w->blocksA * w->acc);
+  const int nb = w->block_n / w->bwB;
+  for (w->kp = 64; w->kp >= 32; w->kp /= 2) {
+    w->a_box_bytes = (uint32_t)w->kp * w->bwA * 2;
+    w->b_box_bytes = (uint32_t)w->kp * w->bwB * 2;
+    w->stage_bytes = (uint32_t)(w->blocksA * w->acc) * w->a_box_bytes + (uint32_t)nb * w->b_box_bytes;
+    if ((size_t)w->stage_bytes * 3 <= 200 * 1024) break;
+  }
+  if (w->kp < 32) return false;
+  if (w->a_box_bytes % 1024 || w->b_box_bytes % 1024) return false;   // swizzle atoms must stay 1024-byte aligned
   w->stages = (int)((220 * 1024) / w->stage_bytes);
   if (w->stages > 8) w->stages = 8;
   if (w->stages < 2) return false;
@@ -752,18 +771,20 @@ static int create_wgrad_plan(const rn_conv_desc* d, const void* x, const void* d
   w.acc = ws.acc; w.row_groups = ws.row_groups; w.block_n = ws.block_n; w.n_tiles = ws.n_tiles;
   w.PW = ws.PW; w.PH = ws.PH; w.PN = ws.PN; w.tiles_w = ws.tiles_w; w.tiles_h = ws.tiles_h; w.tiles_n = ws.tiles_n;
   w.k_tiles = ws.k_tiles; w.splits = ws.splits; w.tiles_per_split = ws.tiles_per_split; w.kp = ws.kp;
-  w.stages = ws.stages; w.box_bytes = ws.box_bytes; w.stage_bytes = ws.stage_bytes; w.tmem_cols = ws.tmem_cols;
+  w.stages = ws.stages; w.stage_bytes = ws.stage_bytes; w.tmem_cols = ws.tmem_cols;
+  w.bwA = ws.bwA; w.bwB = ws.bwB; w.blocksA = ws.blocksA; w.a_box_bytes = ws.a_box_bytes; w.b_box_bytes = ws.b_box_bytes;
   w.partial = ws.splits > 1 ? (float*)scratch : (float*)dw;
   for (int r = 0; r < d->k; ++r)
     for (int s = 0; s < d->k; ++s)
       forward_tap(r, s, d->pad, d->stride, &w.tap_map[r * d->k + s], &w.tap_dw[r * d->k + s], &w.tap_dh[r * d->k + s]);
-  const uint32_t box[4] = {64u, (uint32_t)ws.PW, (uint32_t)ws.PH, (uint32_t)ws.PN};
-  int rc = encode_activation_maps(w.x_map, x, d->Cin, d->W, d->H, d->N, d->stride, box, 128);
+  const uint32_t box[4] = {(uint32_t)ws.bwA, (uint32_t)ws.PW, (uint32_t)ws.PH, (uint32_t)ws.PN};
+  int rc = encode_activation_maps(w.x_map, x, d->Cin, d->W, d->H, d->N, d->stride, box, ws.bwA * 2);
   if (rc) return rc;
   {
     const uint64_t dims[4] = {(uint64_t)d->Cout, (uint64_t)d->Wo, (uint64_t)d->Ho, (uint64_t)d->N};
     const uint64_t str[3] = {(uint64_t)d->Cout * 2, (uint64_t)d->Wo * d->Cout * 2, (uint64_t)d->Ho * d->Wo * d->Cout * 2};
-    rc = encode_map(&w.dy_map, dy, 4, dims, str, box, 128, "dy");
+    const uint32_t boxb[4] = {(uint32_t)ws.bwB, (uint32_t)ws.PW, (uint32_t)ws.PH, (uint32_t)ws.PN};
+    rc = encode_map(&w.dy_map, dy, 4, dims, str, boxb, ws.bwB * 2, "dy");
     if (rc) return rc;
   }
   const long total = (long)ws.row_groups * ws.n_tiles * ws.splits;

@@ -84,11 +84,18 @@ S2_CASES = [
     (2, 56, 56, 256, 512, 1, 2, 0, (28, 28)),    # C3 stage-2 projection
     (2, 28, 28, 128, 128, 3, 2, 1, (14, 14)),    # C3 3x3 s2 (stride on the 3x3 of the bottleneck)
     (3, 15, 13, 64, 64, 3, 2, 1, (8, 7)),        # odd sizes: parity views of different extents
+    (8, 32, 32, 16, 32, 3, 2, 1, (16, 16)),      # CIFAR stage transition
+    (8, 32, 32, 16, 32, 1, 2, 0, (16, 16)),
 ]
 
 WGRAD_CASES = CASES[0:3] + CASES[3:7] + [CASES[11]] + [
     (16, 14, 14, 128, 128, 3, 1, 1),             # BLOCK_N = 128, four accumulators
     (4, 28, 28, 192, 64, 1, 1, 0),               # three 64-channel row blocks
+    (8, 32, 32, 16, 16, 3, 1, 1),                # CIFAR widths: 16-channel boxes (32-byte MN-major rows), 8 taps per M tile
+    (8, 16, 16, 32, 32, 3, 1, 1),                # 32-channel boxes (64-byte rows)
+    (8, 16, 16, 16, 32, 1, 1, 0),                # mixed box widths A=16, B=32
+    (4, 32, 32, 160, 160, 3, 1, 1),              # WRN-28-10 width: 32-channel boxes, N = 160
+    (4, 16, 16, 32, 64, 3, 1, 1),
 ]
 
 
