@@ -69,7 +69,8 @@ SIGNATURES = {
     "rn_maxpool3x3s2_bwd": (C.c_int, [vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, f32, vp]),
     "rn_avgpool_fwd": (C.c_int, [vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, i32, i32, vp]),
     "rn_avgpool_bwd": (C.c_int, [vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, i32, i32, f32, vp]),
-    "rn_dense_fwd": (C.c_int, [vp, vp, vp, vp, i32, i32, i32, vp]),
+    "rn_dense_scratch_bytes": (sz, [i32, i32, i32]),
+    "rn_dense_fwd": (C.c_int, [vp, vp, vp, vp, i32, i32, i32, vp, sz, vp]),
     "rn_dense_bwd": (C.c_int, [vp, vp, vp, vp, vp, vp, i32, i32, i32, vp]),
     "rn_softmax_xent": (C.c_int, [vp, vp, i32, i32, vp, vp, vp, vp]),
     "rn_optimizer_scratch_bytes": (sz, [i64]),

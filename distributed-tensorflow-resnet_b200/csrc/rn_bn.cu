@@ -157,11 +157,13 @@ bn_stats_kernel(const T* __restrict__ x, const T* __restrict__ addend, T* __rest
 #pragma unroll
   for (int i = 0; i < V; ++i) { s[i] = 0.f; q[i] = 0.f; }
   if (active) {
-    const int64_t stride = (int64_t)gridDim.x * L.RY;
+    const int64_t stride = L.RY;
     const int64_t col = (int64_t)cg * V;
-    int64_t r = (int64_t)blockIdx.x * L.RY + ty;
+    const int64_t rows_per_cta = ((M + gridDim.x - 1) / gridDim.x + L.RY - 1) / L.RY * L.RY;
+    const int64_t M_end = min(M, (int64_t)(blockIdx.x + 1) * rows_per_cta);
+    int64_t r = (int64_t)blockIdx.x * rows_per_cta + ty;
     constexpr int U = ADD ? 1 : 2;   // independent 128-bit loads in flight per thread and stream
-    for (; r + (U - 1) * stride < M; r += U * stride) {
+    for (; r + (U - 1) * stride < M_end; r += U * stride) {
       Vec<T> v[U], w[U];
 #pragma unroll
       for (int u = 0; u < U; ++u) v[u].load(x + (r + u * stride) * C + col);
@@ -187,7 +189,7 @@ bn_stats_kernel(const T* __restrict__ x, const T* __restrict__ addend, T* __rest
         for (int i = 0; i < V; ++i) { s[i] += f[i]; q[i] = fmaf(f[i], f[i], q[i]); }
       }
     }
-    for (; r < M; r += stride) {
+    for (; r < M_end; r += stride) {
       Vec<T> v;
       float f[V];
       const int64_t off = r * C + col;
@@ -270,11 +272,13 @@ bn_apply_kernel(const T* __restrict__ x, T* __restrict__ y, int64_t M, int C, Bn
     a[i] = gamma[c] * rs;
     b[i] = beta[c] - mean[c] * a[i];
   }
-  const int64_t stride = (int64_t)gridDim.x * L.RY;
+  const int64_t stride = L.RY;
   const int64_t col = (int64_t)cg * V;
-  int64_t r = (int64_t)blockIdx.x * L.RY + ty;
+  const int64_t rows_per_cta = ((M + gridDim.x - 1) / gridDim.x + L.RY - 1) / L.RY * L.RY;
+  const int64_t M_end = min(M, (int64_t)(blockIdx.x + 1) * rows_per_cta);
+  int64_t r = (int64_t)blockIdx.x * rows_per_cta + ty;
   constexpr int U = 4;
-  for (; r + (U - 1) * stride < M; r += U * stride) {
+  for (; r + (U - 1) * stride < M_end; r += U * stride) {
     Vec<T> v[U];
 #pragma unroll
     for (int u = 0; u < U; ++u) v[u].load_stream(x + (r + u * stride) * C + col);
@@ -288,7 +292,7 @@ bn_apply_kernel(const T* __restrict__ x, T* __restrict__ y, int64_t M, int C, Bn
       v[u].store(y + (r + u * stride) * C + col);
     }
   }
-  for (; r < M; r += stride) {
+  for (; r < M_end; r += stride) {
     const int64_t off = r * C + col;
     Vec<T> v;
     float f[V];
@@ -327,11 +331,13 @@ bn_bwd_reduce_kernel(const T* __restrict__ dy, const T* __restrict__ x, int64_t 
       a[i] = gamma[c] * rs[i];
       b[i] = beta[c] - mu[i] * a[i];
     }
-    const int64_t stride = (int64_t)gridDim.x * L.RY;
+    const int64_t stride = L.RY;
     const int64_t col = (int64_t)cg * V;
-    int64_t r = (int64_t)blockIdx.x * L.RY + ty;
+    const int64_t rows_per_cta = ((M + gridDim.x - 1) / gridDim.x + L.RY - 1) / L.RY * L.RY;
+    const int64_t M_end = min(M, (int64_t)(blockIdx.x + 1) * rows_per_cta);
+    int64_t r = (int64_t)blockIdx.x * rows_per_cta + ty;
     constexpr int U = 2;   // 2 x 2 independent 128-bit loads in flight per thread
-    for (; r + (U - 1) * stride < M; r += U * stride) {
+    for (; r + (U - 1) * stride < M_end; r += U * stride) {
       Vec<T> vx[U], vg[U];
 #pragma unroll
       for (int u = 0; u < U; ++u) {
@@ -352,7 +358,7 @@ bn_bwd_reduce_kernel(const T* __restrict__ dy, const T* __restrict__ x, int64_t 
         }
       }
     }
-    for (; r < M; r += stride) {
+    for (; r < M_end; r += stride) {
       const int64_t off = r * C + col;
       Vec<T> vx, vg;
       float fx[V], fg[V];
@@ -426,11 +432,13 @@ bn_bwd_apply_kernel(const T* __restrict__ dy, const T* __restrict__ x, T* dx, co
     k1[i] = dbeta[c] * invM;
     k2[i] = dgamma[c] * invM;
   }
-  const int64_t stride = (int64_t)gridDim.x * L.RY;
+  const int64_t stride = L.RY;
   const int64_t col = (int64_t)cg * V;
-  int64_t r = (int64_t)blockIdx.x * L.RY + ty;
+  const int64_t rows_per_cta = ((M + gridDim.x - 1) / gridDim.x + L.RY - 1) / L.RY * L.RY;
+  const int64_t M_end = min(M, (int64_t)(blockIdx.x + 1) * rows_per_cta);
+  int64_t r = (int64_t)blockIdx.x * rows_per_cta + ty;
   constexpr int U = 2;
-  for (; r + (U - 1) * stride < M; r += U * stride) {
+  for (; r + (U - 1) * stride < M_end; r += U * stride) {
     Vec<T> vx[U], vg[U], va[U];
 #pragma unroll
     for (int u = 0; u < U; ++u) {
@@ -457,7 +465,7 @@ bn_bwd_apply_kernel(const T* __restrict__ dy, const T* __restrict__ x, T* dx, co
       vo.store(dx + (r + u * stride) * C + col);
     }
   }
-  for (; r < M; r += stride) {
+  for (; r < M_end; r += stride) {
     const int64_t off = r * C + col;
     Vec<T> vx, vg;
     float fx[V], fg[V], fo[V];

@@ -45,6 +45,9 @@ struct TcConvParams {
   uint32_t tx_bytes;              // bytes TMA delivers per stage
   uint32_t tmem_cols;
   int accumulate;                 // 1: OUT += result (TMA reduce-add), 0: OUT = result
+  int b_mn;                       // 1: B operand is MN-major (fprop reads the HWIO weights as they are)
+  int b_boxes;                    // MN-major: TMA boxes per stage (block_n / gw), each kc rows of gw channels
+  uint32_t b_box_bytes;
   int8_t tap_map[TC_MAX_TAPS], tap_dw[TC_MAX_TAPS], tap_dh[TC_MAX_TAPS], tap_b[TC_MAX_TAPS];
 };
 
@@ -105,7 +108,13 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const __grid_con
             uint8_t* sa = smem + (size_t)stage * stage_bytes;
             mbar_expect_tx(&full[stage], p.tx_bytes);
             tma_load_4d(sa, am, &full[stage], kk * p.kc, cw, ch, n0);
-            tma_load_3d(sa + p.a_bytes, &p.b_map, &full[stage], kk * p.kc, nt * p.block_n, tb);
+            if (p.b_mn) {
+              for (int j = 0; j < p.b_boxes; ++j)
+                tma_load_3d(sa + p.a_bytes + (size_t)j * p.b_box_bytes, &p.b_map, &full[stage],
+                            nt * p.block_n + j * p.gw, kk * p.kc, tb);
+            } else {
+              tma_load_3d(sa + p.a_bytes, &p.b_map, &full[stage], kk * p.kc, nt * p.block_n, tb);
+            }
             if (++stage == p.stages) { stage = 0; phase ^= 1; }
           }
         }
@@ -114,7 +123,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const __grid_con
   } else if (warp == 1) {
     if (lane == 0) {
       // ===================== MMA issuer =====================
-      const uint32_t idesc = make_idesc_bf16(TC_BLOCK_M, p.block_n, 0, 0);
+      const uint32_t idesc = make_idesc_bf16(TC_BLOCK_M, p.block_n, 0, p.b_mn);
+      const uint32_t rowB = (uint32_t)p.gw * 2, ltB = swizzle_layout_type(p.gw * 2);
       const int row_bytes = p.kc * 2;
       const uint32_t lt = swizzle_layout_type(row_bytes);
       const uint32_t sbo = 8u * row_bytes;
@@ -134,7 +144,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const __grid_con
           const uint32_t b_addr = a_addr + p.a_bytes;
           for (int k = 0; k < ksteps; ++k) {
             const uint64_t da = make_smem_desc(a_addr + k * 32, 16, sbo, lt);
-            const uint64_t db = make_smem_desc(b_addr + k * 32, 16, sbo, lt);
+            // K-major B: +32 bytes per K step inside the swizzled row.  MN-major B (rows = input channels):
+            // +16 rows per K step, LBO = next 64-column box, SBO = 8 rows.
+            const uint64_t db = p.b_mn ? make_smem_desc(b_addr + k * 16 * rowB, p.b_box_bytes, 8 * rowB, ltB)
+                                       : make_smem_desc(b_addr + k * 32, 16, sbo, lt);
             umma_bf16(d_tmem, da, db, idesc, (it > 0 || k > 0) ? 1u : 0u);
           }
           umma_commit(&empty[stage]);      // frees the smem slot once these MMAs have read it
@@ -691,7 +704,18 @@ static int create_sub(const rn_conv_desc* d, int kind, const void* a, const void
   const uint32_t abox[4] = {(uint32_t)p.kc, (uint32_t)p.BW, (uint32_t)p.BH, (uint32_t)p.BN};
   rc = encode_activation_maps(p.a_map, a, cred, aW, aH, d->N, kind == 0 ? d->stride : 1, abox, row_bytes);
   if (rc) return rc;
-  {  // weights: dims (cred, ncols, taps)
+  if (kind == 0) {
+    // fprop: bf16 HWIO [tap][Cin][Cout] read as an MN-major B operand: dims (Cout, Cin, taps)
+    p.b_mn = 1;
+    p.b_boxes = p.block_n / p.gw;
+    p.b_box_bytes = (uint32_t)p.kc * p.gw * 2;
+    const uint64_t dims[3] = {(uint64_t)ncols, (uint64_t)cred, (uint64_t)(d->k * d->k)};
+    const uint64_t str[2] = {(uint64_t)ncols * 2, (uint64_t)ncols * cred * 2};
+    const uint32_t box[3] = {(uint32_t)p.gw, (uint32_t)p.kc, 1u};
+    rc = encode_map(&p.b_map, b, 3, dims, str, box, p.gw * 2, "weights (MN-major)");
+    if (rc) return rc;
+  } else {
+    // dgrad: the same bf16 HWIO tensor is K-major for this GEMM (K = Cout contiguous): dims (cred, ncols, taps)
     const uint64_t dims[3] = {(uint64_t)cred, (uint64_t)ncols, (uint64_t)(d->k * d->k)};
     const uint64_t str[2] = {(uint64_t)cred * 2, (uint64_t)ncols * cred * 2};
     const uint32_t box[3] = {(uint32_t)p.kc, (uint32_t)p.block_n, 1u};

@@ -48,6 +48,62 @@ sgemm_strided_kernel(const float* __restrict__ A, int64_t a_rs, int64_t a_cs, co
     }
 }
 
+// Split-K flavour for GEMMs with few output tiles and a long reduction (the ImageNet classifier:
+// 128 x 1000 outputs, K = 2048): blockIdx.z takes a K slice and writes a partial tile; a second pass sums the
+// slices in a fixed order and adds the bias (deterministic).
+__global__ void __launch_bounds__(256)
+sgemm_splitk_kernel(const float* __restrict__ A, int64_t a_rs, int64_t a_cs, const float* __restrict__ Bm, int64_t b_rs,
+                    int64_t b_cs, float* __restrict__ part, int M, int N, int K, int kslice) {
+  __shared__ float As[16][64 + 4];
+  __shared__ float Bs[16][64 + 4];
+  const int tid = threadIdx.x;
+  const int tr = tid / 16, tc = tid % 16;
+  const int m0 = blockIdx.y * 64, n0 = blockIdx.x * 64;
+  const int kb = blockIdx.z * kslice;
+  const int ke = min(K, kb + kslice);
+  float acc[4][4] = {};
+  for (int k0 = kb; k0 < ke; k0 += 16) {
+    for (int e = tid; e < 64 * 16; e += 256) {
+      const int kk = e % 16, mm = e / 16;
+      const int gm = m0 + mm, gk = k0 + kk;
+      As[kk][mm] = (gm < M && gk < ke) ? A[gm * a_rs + gk * a_cs] : 0.f;
+      const int nn = e % 64, k2 = e / 64;
+      const int gn = n0 + nn, gk2 = k0 + k2;
+      Bs[k2][nn] = (gn < N && gk2 < ke) ? Bm[gk2 * b_rs + gn * b_cs] : 0.f;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int kk = 0; kk < 16; ++kk) {
+      float a[4], b[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) { a[i] = As[kk][tr * 4 + i]; b[i] = Bs[kk][tc * 4 + i]; }
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+    }
+    __syncthreads();
+  }
+  float* o = part + (int64_t)blockIdx.z * M * N;
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int gm = m0 + tr * 4 + i, gn = n0 + tc * 4 + j;
+      if (gm < M && gn < N) o[(int64_t)gm * N + gn] = acc[i][j];
+    }
+}
+
+__global__ void splitk_bias_reduce_kernel(const float* __restrict__ part, const float* __restrict__ bias,
+                                          float* __restrict__ out, int M, int N, int splits) {
+  const int64_t n = (int64_t)M * N;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    float s = bias ? bias[i % N] : 0.f;
+    for (int z = 0; z < splits; ++z) s += part[(int64_t)z * n + i];
+    out[i] = s;
+  }
+}
+
 __global__ void colsum_kernel(const float* __restrict__ dy, float* __restrict__ db, int B, int K) {
   const int j = blockIdx.x * blockDim.x + threadIdx.x;
   if (j >= K) return;
@@ -191,10 +247,30 @@ sgd_momentum_kernel(float* __restrict__ w, const float* __restrict__ g, float* _
 }  // namespace rn
 using namespace rn;
 
+extern "C" size_t rn_dense_scratch_bytes(int32_t B, int32_t D, int32_t K) {
+  const int tiles = ((K + 63) / 64) * ((B + 63) / 64);
+  int splits = (2 * RN_NUM_SMS + tiles - 1) / tiles;
+  if (splits > D / 64) splits = D / 64;
+  if (splits < 2) return 0;
+  return (size_t)splits * B * K * sizeof(float);
+}
+
 extern "C" int rn_dense_fwd(const float* x, const float* w, const float* b, float* y, int32_t B, int32_t D, int32_t K,
-                            void* stream) {
+                            void* scratch, size_t scratch_bytes, void* stream) {
   RN_REQUIRE(x && w && y && B > 0 && D > 0 && K > 0, "dense_fwd: bad arguments");
-  return sgemm(x, D, 1, w, K, 1, b, y, B, K, D, as_stream(stream));
+  const size_t need = rn_dense_scratch_bytes(B, D, K);
+  if (need == 0 || scratch == nullptr || scratch_bytes < need)      // small problem (or no scratch): one pass
+    return sgemm(x, D, 1, w, K, 1, b, y, B, K, D, as_stream(stream));
+  const int splits = (int)(need / ((size_t)B * K * sizeof(float)));
+  int kslice = (D + splits - 1) / splits;
+  kslice = (kslice + 15) / 16 * 16;
+  dim3 grid((K + 63) / 64, (B + 63) / 64, splits);
+  sgemm_splitk_kernel<<<grid, 256, 0, as_stream(stream)>>>(x, D, 1, w, K, 1, (float*)scratch, B, K, D, kslice);
+  int rc = check_launch("sgemm_splitk_kernel");
+  if (rc) return rc;
+  splitk_bias_reduce_kernel<<<grid_for((int64_t)B * K, 256), 256, 0, as_stream(stream)>>>((const float*)scratch, b, y,
+                                                                                         B, K, splits);
+  return check_launch("splitk_bias_reduce_kernel");
 }
 
 extern "C" int rn_dense_bwd(const float* x, const float* w, const float* dy, float* dw, float* db, float* dx, int32_t B,

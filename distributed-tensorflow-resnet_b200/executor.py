@@ -283,9 +283,11 @@ class Executor:
                 B = x.shape[0]
                 D = x.numel // B
                 K = y.shape[1]
+                nb = lib.rn_dense_scratch_bytes(B, D, K)
+                n.scratch = torch.zeros(max(nb, 16), dtype=torch.uint8, device=self.dev)
                 fwd.append(("dense:" + y.name,
-                            lambda s, px=ptr(x.buf), pw=self._wptr(n.vars["kernel"]), pb=self._wptr(n.vars["bias"]), py=ptr(y.buf), d=(B, D, K):
-                            check(lib.rn_dense_fwd(px, pw, pb, py, *d, s), "rn_dense_fwd")))
+                            lambda s, px=ptr(x.buf), pw=self._wptr(n.vars["kernel"]), pb=self._wptr(n.vars["bias"]), py=ptr(y.buf), d=(B, D, K), sc=(ptr(n.scratch), nb):
+                            check(lib.rn_dense_fwd(px, pw, pb, py, *d, sc[0], sc[1], s), "rn_dense_fwd")))
             elif n.op == "softmax_xent":
                 logits, labels = n.inputs
                 probs, scal = n.outputs
@@ -315,7 +317,7 @@ class Executor:
         d = self._desc(n)
         if not (self.use_tc and d.Cin < 16):
             return False
-        kpad = _align(d.k * d.k * d.Cin, 64)
+        kpad = _align(d.k * d.k * d.Cin, 32)
         d1 = ConvDesc(d.N, d.Ho, d.Wo, kpad, d.Ho, d.Wo, d.Cout, 1, 1, 0, self.rn_dt)
         return bool(lib.rn_convtc_supported(C.byref(d1), 0))
 
@@ -325,17 +327,16 @@ class Executor:
         d = self._desc(n)
         kv = n.vars["kernel"]
         rows = d.k * d.k * d.Cin
-        kpad = _align(rows, 64)
+        kpad = _align(rows, 32)
         d1 = ConvDesc(d.N, d.Ho, d.Wo, kpad, d.Ho, d.Wo, d.Cout, 1, 1, 0, self.rn_dt)
         cols = torch.zeros(d.N * d.Ho * d.Wo, kpad, dtype=torch.bfloat16, device=self.dev)
-        wf = torch.zeros(d.Cout, kpad, dtype=torch.bfloat16, device=self.dev)
-        fn = (lambda s, pw=self._wptr(kv), r=rows, co=d.Cout, kp=kpad, a=ptr(wf):
-              check(lib.rn_stem_weights(pw, r, co, kp, a, s), "rn_stem_weights"))
+        # [Kpad][Cout] bf16: the first k*k*Cin rows are the HWIO kernel (refreshed each step), the rest stay 0
+        wf = torch.zeros(kpad, d.Cout, dtype=torch.bfloat16, device=self.dev)
+        fn = (lambda s, a=self._wptr(kv, "Wb"), b=ptr(wf), k=rows * d.Cout:
+              check(lib.rn_cast(a, b, k, RN_BF16, RN_BF16, s), "rn_cast"))
         if not hasattr(self, "_relayout"):
             self._relayout = []
-            self._relayout_jobs = []
         self._relayout.append(fn)
-        self._relayout_jobs.append((self._wptr(kv), ptr(wf), 0, d.k * d.k, d.Cin, d.Cout, kpad))
         fn(torch.cuda.current_stream().cuda_stream)
         self._keep += [d, d1, cols, wf]
         n._stem = dict(d=d, d1=d1, cols=cols, wf=wf, rows=rows, kpad=kpad)
@@ -371,39 +372,20 @@ class Executor:
                 check(lib.rn_conv2d_fprop(C.byref(d), px, w, py, s), "rn_conv2d_fprop"))
 
     # tensor-core plans -------------------------------------------------------------------
-    def _tc_weights(self, n):
-        """bf16 operand layouts of one conv kernel for the tcgen05 path, refreshed after every
-        optimizer step by rn_weights_to_bf16."""
-        if not hasattr(n, "_tcw"):
-            kv = n.vars["kernel"]
-            k, _, Cin, Cout = kv.shape
-            wf = torch.zeros(k * k * Cout * Cin, dtype=torch.bfloat16, device=self.dev)
-            wd = torch.zeros(k * k * Cin * Cout, dtype=torch.bfloat16, device=self.dev)
-            n._tcw = (wf, wd)
-            fn = (lambda s, pw=self._wptr(kv), k=k, ci=Cin, co=Cout, a=ptr(wf), b=ptr(wd):
-                  check(lib.rn_weights_to_bf16(pw, k, ci, co, a, b, s), "rn_weights_to_bf16"))
-            if not hasattr(self, "_relayout"):
-                self._relayout = []
-                self._relayout_jobs = []
-            self._relayout.append(fn)
-            self._relayout_jobs.append((self._wptr(kv), ptr(wf), ptr(wd), k * k, Cin, Cout, 0))
-            fn(torch.cuda.current_stream().cuda_stream)
-        return n._tcw
-
     def _tc_plan(self, n, d, kind, a_buf, out_ptr_or_buf, b_buf=None):
-        wf, wd = self._tc_weights(n)
-        if kind == 0:
-            b = wf
-        elif kind == 1:
-            b = wd
+        """Tensor-core plan for one conv GEMM.  fprop and dgrad both read the conv kernel from `Wb`, the
+        flat bf16 copy of the HWIO weights that the fused optimizer kernel refreshes every step (fprop takes
+        it as an MN-major operand, dgrad as a K-major one): no per-layer re-layout."""
+        if kind in (0, 1):
+            b = self._wptr(n.vars["kernel"], "Wb")
         else:
-            b = b_buf
+            b = ptr(b_buf)
         nbytes = lib.rn_convtc_scratch_bytes(C.byref(d), kind)
         scratch = torch.zeros(max(nbytes, 16), dtype=torch.uint8, device=self.dev)
         self._keep.append(scratch)
         plan = C.c_void_p()
         outp = out_ptr_or_buf if isinstance(out_ptr_or_buf, int) else ptr(out_ptr_or_buf)
-        check(lib.rn_convtc_plan_create(C.byref(d), kind, ptr(a_buf), ptr(b), outp, ptr(scratch), nbytes,
+        check(lib.rn_convtc_plan_create(C.byref(d), kind, ptr(a_buf), b, outp, ptr(scratch), nbytes,
                                         C.byref(plan)), "rn_convtc_plan_create")
         self._plans.append(plan)
         return lambda s, p=plan, beta=0.0: check(lib.rn_convtc_run(p, beta, s), "rn_convtc_run")
@@ -653,14 +635,8 @@ class Executor:
                             ptr(self.W), ptr(self.Gd), ptr(self.Mom), ptr(self.Wb), self.n_flat, ptr(self.mask),
                             ptr(self.hyper), inv_R, self.wd, self.momentum, use_mom, ptr(self.sumsq),
                             ptr(self.scratch), self.scratch_bytes, s), "rn_sgd_momentum_fused"))]
-        jobs = getattr(self, "_relayout_jobs", [])
-        if jobs:     # one launch re-lays out every conv kernel for the tensor-core path
-            import struct
-            assert lib.rn_relayout_job_bytes() == 40
-            blob = b"".join(struct.pack("<QQQiiii", *j) for j in jobs)
-            self._jobs_dev = torch.frombuffer(bytearray(blob), dtype=torch.uint8).to(self.dev)
-            self.update.append(("weights_to_bf16", lambda s, p=ptr(self._jobs_dev), n=len(jobs):
-                                check(lib.rn_weights_to_bf16_batched(p, n, s), "rn_weights_to_bf16_batched")))
+        for i, fn in enumerate(getattr(self, "_relayout", [])):     # stem only: copy of the kernel into its K-padded operand
+            self.update.append(("stem_weights:%d" % i, fn))
 
     def set_lr(self, lr):
         """The reference feeds the learning rate every step (resnet_cifar_train.py:297-299); here

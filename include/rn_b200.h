@@ -74,8 +74,10 @@ int rn_conv2d_wgrad(const rn_conv_desc* d, const void* x, const void* dy, float*
 /* tcgen05 / TMA / TMEM implicit-GEMM path (bf16 operands, fp32 accumulation in tensor memory).
  * A plan owns the CUtensorMap descriptors (which embed the buffer addresses) for one conv layer
  * and one of its three GEMMs; it is created once at graph-build time and run every step.
- *   kind 0: fprop  a = x  [N,H,W,Cin] bf16,  b = w as [k*k][Cout][Cin] bf16,   out = y  bf16
- *   kind 1: dgrad  a = dy [N,Ho,Wo,Cout] bf16, b = w as [k*k][Cin][Cout] bf16, out = dx bf16
+ *   kind 0: fprop  a = x  [N,H,W,Cin] bf16,    b = w bf16 HWIO [k*k][Cin][Cout], out = y  bf16
+ *   kind 1: dgrad  a = dy [N,Ho,Wo,Cout] bf16, b = w bf16 HWIO [k*k][Cin][Cout], out = dx bf16
+ *           (the same bf16 copy of the HWIO kernel serves both: an MN-major UMMA operand for fprop,
+ *            a K-major one for dgrad — no transposed copy is ever made)
  *   kind 2: wgrad  a = x, b = dy, out = dw fp32 HWIO (split-K partials in caller scratch)
  * rn_convtc_supported() says whether the shape is handled (else use the CUDA-core path). */
 typedef struct rn_convtc_plan rn_convtc_plan;
@@ -177,7 +179,10 @@ int rn_avgpool_bwd(const void* dy, void* dx, int32_t N, int32_t H, int32_t W, in
  *           trainers' precision metric mean(argmax(pred) == argmax(label)),
  *           resnet_cifar_train.py:271-273.  All fp32.
  * ------------------------------------------------------------------------------------------ */
-int rn_dense_fwd(const float* x, const float* w, const float* b, float* y, int32_t B, int32_t D, int32_t K, void* stream);
+/* `scratch` (optional, rn_dense_scratch_bytes) enables a deterministic split-K pass for long reductions. */
+size_t rn_dense_scratch_bytes(int32_t B, int32_t D, int32_t K);
+int rn_dense_fwd(const float* x, const float* w, const float* b, float* y, int32_t B, int32_t D, int32_t K,
+                 void* scratch, size_t scratch_bytes, void* stream);
 int rn_dense_bwd(const float* x, const float* w, const float* dy, float* dw, float* db, float* dx,
                  int32_t B, int32_t D, int32_t K, void* stream);
 /* out_scalars[0] = mean xent, out_scalars[1] = precision. probs / dlogits may be NULL. */

@@ -63,7 +63,7 @@ def test_convtc_fprop_and_dgrad(case):
     X, DY = dev(x), dev(dy)
     Y = torch.full((N, Ho, Wo, Cout), float("nan"), dtype=BF, device="cuda")
     DX = torch.full((N, H, W, Cin), float("nan"), dtype=BF, device="cuda")
-    for kind, a, b, out, want in ((0, X, wf, Y, yv.val), (1, DY, wd, DX, xv.grad)):
+    for kind, a, b, out, want in ((0, X, wd, Y, yv.val), (1, DY, wd, DX, xv.grad)):
         if kind not in kinds:
             continue
         plan = C.c_void_p()
@@ -154,10 +154,10 @@ def _run_fprop_wgrad(case, fprop=True):
     X, DY = dev(x), dev(dy)
     if fprop:
         assert lib.rn_convtc_supported(C.byref(d), 0) == 1
-        wf, _ = _weights(w)
+        _, wd = _weights(w)
         Y = torch.full((N, Ho, Wo, Cout), float("nan"), dtype=BF, device="cuda")
         plan = C.c_void_p()
-        check(lib.rn_convtc_plan_create(C.byref(d), 0, ptr(X), ptr(wf), ptr(Y), None, 0, C.byref(plan)), "plan")
+        check(lib.rn_convtc_plan_create(C.byref(d), 0, ptr(X), ptr(wd), ptr(Y), None, 0, C.byref(plan)), "plan")
         check(lib.rn_convtc_run(plan, 0.0, stream()), "run")
         torch.cuda.synchronize()
         lib.rn_convtc_plan_destroy(plan)

@@ -271,8 +271,14 @@ def test_dense_and_softmax_xent(cfg):
     net.backward()
     X, Wd, Bd, OH = dev(x), dev(w), dev(b), dev(onehot)
     L = torch.empty(B, K, device="cuda")
-    check(lib.rn_dense_fwd(ptr(X), ptr(Wd), ptr(Bd), ptr(L), B, D, K, stream()), "dense")
+    check(lib.rn_dense_fwd(ptr(X), ptr(Wd), ptr(Bd), ptr(L), B, D, K, None, 0, stream()), "dense")
     assert rel_err(L, lg.val) < 1e-4
+    nbs = lib.rn_dense_scratch_bytes(B, D, K)
+    if nbs:      # deterministic split-K path (long reductions)
+        sc = torch.empty(nbs, dtype=torch.uint8, device="cuda")
+        L2 = torch.empty(B, K, device="cuda")
+        check(lib.rn_dense_fwd(ptr(X), ptr(Wd), ptr(Bd), ptr(L2), B, D, K, ptr(sc), nbs, stream()), "dense split-K")
+        assert rel_err(L2, lg.val) < 1e-4
     P, DL, S = torch.empty(B, K, device="cuda"), torch.empty(B, K, device="cuda"), torch.empty(2, device="cuda")
     check(lib.rn_softmax_xent(ptr(L), ptr(OH), B, K, ptr(P), ptr(DL), ptr(S), stream()), "xent")
     assert rel_err(P, probs) < 1e-4 and rel_err(DL, lg.grad) < 1e-4
