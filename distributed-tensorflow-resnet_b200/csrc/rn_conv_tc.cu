@@ -19,6 +19,7 @@
 #include "rn_tc_common.cuh"
 
 #include <string.h>
+#include <stdlib.h>
 #include <vector>
 
 namespace rn {
@@ -45,6 +46,8 @@ struct TcConvParams {
   uint32_t tx_bytes;              // bytes TMA delivers per stage
   uint32_t tmem_cols;
   int accumulate;                 // 1: OUT += result (TMA reduce-add), 0: OUT = result
+  int acc_m;                      // pixel tiles per CTA iteration (they share every B tile): 1, 2 or 4
+  int tstages;                    // TMEM accumulator sets (2 = epilogue overlaps the next tile's MMAs)
   int b_mn;                       // 1: B operand is MN-major (fprop reads the HWIO weights as they are)
   int b_boxes;                    // MN-major: TMA boxes per stage (block_n / gw), each kc rows of gw channels
   uint32_t b_box_bytes;
@@ -55,7 +58,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const __grid_con
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base_u32 = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* smem = smem_raw + (base_u32 - smem_u32(smem_raw));
-  const uint32_t stage_bytes = p.a_bytes + p.b_bytes;
+  const uint32_t stage_bytes = (uint32_t)p.acc_m * p.a_bytes + p.b_bytes;
   const int row_bytes_out = p.gw * 2;
   uint8_t* epi_buf = smem + (size_t)p.stages * stage_bytes;                  // 2 x 16 KB
   uint64_t* bars = reinterpret_cast<uint64_t*>(epi_buf + 2 * 16384);
@@ -83,9 +86,13 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const __grid_con
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
+  // work item = (group of acc_m consecutive pixel tiles, column tile); the acc_m tiles share each B tile
   const int m_tiles = p.tiles_w * p.tiles_h * p.tiles_n;
-  const int total = m_tiles * p.n_tiles;
+  const int m_groups = (m_tiles + p.acc_m - 1) / p.acc_m;
+  const int total = m_groups * p.n_tiles;
   const int k_iters = p.taps * p.k_chunks;
+  const uint32_t a_tx = (uint32_t)(p.BW * p.BH * p.BN) * (uint32_t)(p.kc * 2);
+  const uint32_t b_tx = (uint32_t)p.block_n * (uint32_t)(p.kc * 2);
 
   if (warp == 0) {
     if (lane == 0) {
@@ -94,26 +101,34 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const __grid_con
       uint32_t phase = 0;
       for (int t = blockIdx.x; t < total; t += gridDim.x) {
         const int nt = t % p.n_tiles;
-        int mt = t / p.n_tiles;
-        const int w0 = (mt % p.tiles_w) * p.BW;
-        mt /= p.tiles_w;
-        const int h0 = (mt % p.tiles_h) * p.BH;
-        const int n0 = (mt / p.tiles_h) * p.BN;
+        const int mg = t / p.n_tiles;
+        int nvalid = m_tiles - mg * p.acc_m;
+        if (nvalid > p.acc_m) nvalid = p.acc_m;
+        int w0[4], h0[4], n0[4];
+        for (int j = 0; j < nvalid; ++j) {
+          int mt = mg * p.acc_m + j;
+          w0[j] = (mt % p.tiles_w) * p.BW;
+          mt /= p.tiles_w;
+          h0[j] = (mt % p.tiles_h) * p.BH;
+          n0[j] = (mt / p.tiles_h) * p.BN;
+        }
         for (int tap = 0; tap < p.taps; ++tap) {
           const CUtensorMap* am = &p.a_map[p.tap_map[tap]];
-          const int cw = w0 + p.tap_dw[tap], ch = h0 + p.tap_dh[tap];
+          const int dw = p.tap_dw[tap], dh = p.tap_dh[tap];
           const int tb = p.tap_b[tap];
           for (int kk = 0; kk < p.k_chunks; ++kk) {
             mbar_wait(&empty[stage], phase ^ 1);
             uint8_t* sa = smem + (size_t)stage * stage_bytes;
-            mbar_expect_tx(&full[stage], p.tx_bytes);
-            tma_load_4d(sa, am, &full[stage], kk * p.kc, cw, ch, n0);
+            mbar_expect_tx(&full[stage], (uint32_t)nvalid * a_tx + b_tx);
+            for (int j = 0; j < nvalid; ++j)
+              tma_load_4d(sa + (size_t)j * p.a_bytes, am, &full[stage], kk * p.kc, w0[j] + dw, h0[j] + dh, n0[j]);
+            uint8_t* sb = sa + (size_t)p.acc_m * p.a_bytes;
             if (p.b_mn) {
               for (int j = 0; j < p.b_boxes; ++j)
-                tma_load_3d(sa + p.a_bytes + (size_t)j * p.b_box_bytes, &p.b_map, &full[stage],
-                            nt * p.block_n + j * p.gw, kk * p.kc, tb);
+                tma_load_3d(sb + (size_t)j * p.b_box_bytes, &p.b_map, &full[stage], nt * p.block_n + j * p.gw,
+                            kk * p.kc, tb);
             } else {
-              tma_load_3d(sa + p.a_bytes, &p.b_map, &full[stage], kk * p.kc, nt * p.block_n, tb);
+              tma_load_3d(sb, &p.b_map, &full[stage], kk * p.kc, nt * p.block_n, tb);
             }
             if (++stage == p.stages) { stage = 0; phase ^= 1; }
           }
@@ -134,27 +149,32 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const __grid_con
       int acc = 0;
       uint32_t acc_phase = 0;
       for (int t = blockIdx.x; t < total; t += gridDim.x) {
+        const int mg = t / p.n_tiles;
+        int nvalid = m_tiles - mg * p.acc_m;
+        if (nvalid > p.acc_m) nvalid = p.acc_m;
         mbar_wait(&tempty[acc], acc_phase ^ 1);
         tc_fence_after();
-        const uint32_t d_tmem = tmem_base + (uint32_t)(acc * p.block_n);
+        const uint32_t d_tmem = tmem_base + (uint32_t)(acc * p.acc_m * p.block_n);
         for (int it = 0; it < k_iters; ++it) {
           mbar_wait(&full[stage], phase);
           tc_fence_after();
           const uint32_t a_addr = base_u32 + (uint32_t)stage * stage_bytes;
-          const uint32_t b_addr = a_addr + p.a_bytes;
-          for (int k = 0; k < ksteps; ++k) {
-            const uint64_t da = make_smem_desc(a_addr + k * 32, 16, sbo, lt);
-            // K-major B: +32 bytes per K step inside the swizzled row.  MN-major B (rows = input channels):
-            // +16 rows per K step, LBO = next 64-column box, SBO = 8 rows.
-            const uint64_t db = p.b_mn ? make_smem_desc(b_addr + k * 16 * rowB, p.b_box_bytes, 8 * rowB, ltB)
-                                       : make_smem_desc(b_addr + k * 32, 16, sbo, lt);
-            umma_bf16(d_tmem, da, db, idesc, (it > 0 || k > 0) ? 1u : 0u);
+          const uint32_t b_addr = a_addr + (uint32_t)p.acc_m * p.a_bytes;
+          for (int j = 0; j < nvalid; ++j) {
+            for (int k = 0; k < ksteps; ++k) {
+              const uint64_t da = make_smem_desc(a_addr + (uint32_t)j * p.a_bytes + k * 32, 16, sbo, lt);
+              // K-major B: +32 bytes per K step inside the swizzled row.  MN-major B (rows = input channels):
+              // +16 rows per K step, LBO = next 64-column box, SBO = 8 rows.
+              const uint64_t db = p.b_mn ? make_smem_desc(b_addr + k * 16 * rowB, p.b_box_bytes, 8 * rowB, ltB)
+                                         : make_smem_desc(b_addr + k * 32, 16, sbo, lt);
+              umma_bf16(d_tmem + (uint32_t)(j * p.block_n), da, db, idesc, (it > 0 || k > 0) ? 1u : 0u);
+            }
           }
           umma_commit(&empty[stage]);      // frees the smem slot once these MMAs have read it
           if (++stage == p.stages) { stage = 0; phase ^= 1; }
         }
-        umma_commit(&tfull[acc]);          // accumulator complete
-        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+        umma_commit(&tfull[acc]);          // accumulators complete
+        if (++acc == p.tstages) { acc = 0; acc_phase ^= 1; }
       }
     }
   } else {
@@ -168,48 +188,54 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const __grid_con
     const int groups = p.block_n / p.gw;
     for (int t = blockIdx.x; t < total; t += gridDim.x) {
       const int nt = t % p.n_tiles;
-      int mt = t / p.n_tiles;
-      const int w0 = (mt % p.tiles_w) * p.BW;
-      mt /= p.tiles_w;
-      const int h0 = (mt % p.tiles_h) * p.BH;
-      const int n0 = (mt / p.tiles_h) * p.BN;
+      const int mg = t / p.n_tiles;
+      int nvalid = m_tiles - mg * p.acc_m;
+      if (nvalid > p.acc_m) nvalid = p.acc_m;
       mbar_wait(&tfull[acc], acc_phase);
       tc_fence_after();
-      for (int g = 0; g < groups; ++g) {
-        // the TMA store that last read this staging buffer must have finished reading it
-        if (issuer) tma_store_wait_read<1>();
-        asm volatile("bar.sync 1, 128;" ::: "memory");
-        uint8_t* sb = epi_buf + buf * 16384;
-        const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(acc * p.block_n + g * p.gw);
-        for (int c0 = 0; c0 < p.gw; c0 += 16) {
-          uint32_t v[16];
-          tmem_ld_32x16(taddr + c0, v);
-          tmem_ld_wait();
-          uint32_t pk[8];
+      for (int j = 0; j < nvalid; ++j) {
+        int mt = mg * p.acc_m + j;
+        const int w0 = (mt % p.tiles_w) * p.BW;
+        mt /= p.tiles_w;
+        const int h0 = (mt % p.tiles_h) * p.BH;
+        const int n0 = (mt / p.tiles_h) * p.BN;
+        for (int g = 0; g < groups; ++g) {
+          // the TMA store that last read this staging buffer must have finished reading it
+          if (issuer) tma_store_wait_read<1>();
+          asm volatile("bar.sync 1, 128;" ::: "memory");
+          uint8_t* sb = epi_buf + buf * 16384;
+          const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) +
+                                 (uint32_t)((acc * p.acc_m + j) * p.block_n + g * p.gw);
+          for (int c0 = 0; c0 < p.gw; c0 += 16) {
+            uint32_t v[16];
+            tmem_ld_32x16(taddr + c0, v);
+            tmem_ld_wait();
+            uint32_t pk[8];
 #pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            __nv_bfloat162 h = __floats2bfloat162_rn(__uint_as_float(v[2 * i]), __uint_as_float(v[2 * i + 1]));
-            pk[i] = *reinterpret_cast<uint32_t*>(&h);
+            for (int i = 0; i < 8; ++i) {
+              __nv_bfloat162 h = __floats2bfloat162_rn(__uint_as_float(v[2 * i]), __uint_as_float(v[2 * i + 1]));
+              pk[i] = *reinterpret_cast<uint32_t*>(&h);
+            }
+            // 16 channels = two 16-byte chunks of this row, XOR-swizzled like the TMA store expects
+            const uint32_t off0 = (uint32_t)row * row_bytes_out + (uint32_t)c0 * 2;
+            *reinterpret_cast<uint4*>(sb + swizzle_offset(off0, row_bytes_out)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+            *reinterpret_cast<uint4*>(sb + swizzle_offset(off0 + 16, row_bytes_out)) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
           }
-          // 16 channels = two 16-byte chunks of this row, XOR-swizzled like the TMA store expects
-          const uint32_t off0 = (uint32_t)row * row_bytes_out + (uint32_t)c0 * 2;
-          *reinterpret_cast<uint4*>(sb + swizzle_offset(off0, row_bytes_out)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-          *reinterpret_cast<uint4*>(sb + swizzle_offset(off0 + 16, row_bytes_out)) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+          fence_proxy_async();
+          asm volatile("bar.sync 1, 128;" ::: "memory");
+          if (issuer) {
+            if (p.accumulate) tma_reduce_add_4d(&p.o_map, sb, nt * p.block_n + g * p.gw, w0, h0, n0);
+            else              tma_store_4d(&p.o_map, sb, nt * p.block_n + g * p.gw, w0, h0, n0);
+            tma_store_commit();
+          }
+          buf ^= 1;
         }
-        fence_proxy_async();
-        asm volatile("bar.sync 1, 128;" ::: "memory");
-        if (issuer) {
-          if (p.accumulate) tma_reduce_add_4d(&p.o_map, sb, nt * p.block_n + g * p.gw, w0, h0, n0);
-          else              tma_store_4d(&p.o_map, sb, nt * p.block_n + g * p.gw, w0, h0, n0);
-          tma_store_commit();
-        }
-        buf ^= 1;
       }
-      // all TMEM reads of this accumulator are complete (tcgen05.wait::ld above)
+      // all TMEM reads of this accumulator set are complete (tcgen05.wait::ld above)
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&tempty[acc]);
-      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+      if (++acc == p.tstages) { acc = 0; acc_phase ^= 1; }
     }
     if (issuer) tma_store_wait<0>();
   }
@@ -217,7 +243,6 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const __grid_con
   __syncthreads();
   if (warp == 1) tmem_dealloc(tmem_base, p.tmem_cols);
 }
-
 
 // ------------------------------------------------------------------------------------------
 // wgrad:  dW[(tap, ci), co] = sum_pixels  X[pixel shifted by tap, ci] * dY[pixel, co]
@@ -508,8 +533,17 @@ static void choose_pixel_box(int Wo, int Ho, int N, int* BW, int* BH, int* BN) {
   *BW = bw; *BH = bh; *BN = bn;
 }
 
+static int max_block_n() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("RN_TC_MAX_BLOCK_N");     // tuning knob
+    v = e ? atoi(e) : 256;
+    if (v < 16 || v > 256) v = 256;
+  }
+  return v;
+}
 static int choose_block_n(int ncols) {
-  for (int b = 256; b >= 16; b -= 16)
+  for (int b = max_block_n() / 16 * 16; b >= 16; b -= 16)
     if (ncols % b == 0) return b;
   return 0;
 }
@@ -690,16 +724,38 @@ static int create_sub(const rn_conv_desc* d, int kind, const void* a, const void
   p.a_bytes = ((uint32_t)TC_BLOCK_M * row_bytes + 1023u) & ~1023u;
   p.b_bytes = ((uint32_t)p.block_n * row_bytes + 1023u) & ~1023u;
   p.tx_bytes = box_rows * row_bytes + (uint32_t)p.block_n * row_bytes;
-  uint32_t cols = 32;
-  while (cols < 2u * p.block_n) cols <<= 1;
-  p.tmem_cols = cols;
+  // pixel tiles per CTA iteration: every extra tile re-uses the B tile (less L2 -> SM traffic per FLOP,
+  // which is what bounds these kernels), limited by the 512 TMEM columns, by shared memory (>= 3 stages)
+  // and by keeping every SM busy
+  const long m_tiles = (long)p.tiles_w * p.tiles_h * p.tiles_n;
   const size_t fixed = 2 * 16384 + 1024 + 1024;     // epilogue staging, barriers, alignment slack
   const size_t budget = 227 * 1024;
-  int stages = (int)((budget - fixed) / (p.a_bytes + p.b_bytes));
+  int acc_m = 1;
+  {
+    static int forced = -1;
+    if (forced < 0) { const char* e = getenv("RN_TC_ACC_M"); forced = e ? atoi(e) : 0; }
+    for (int cand = 4; cand >= 2; cand >>= 1) {
+      if (forced && cand != forced) continue;
+      if (cand * p.block_n > 512) continue;
+      if ((budget - fixed) / ((size_t)cand * p.a_bytes + p.b_bytes) < 3) continue;
+      // measured on B200: sharing B across two pixel tiles pays (+10..18 %) only while TMEM can still be
+      // double-buffered (2 * cand * BLOCK_N <= 512) and every SM keeps at least one work item
+      if (!forced && (2 * cand * p.block_n > 512 || cand > 2)) continue;
+      if (!forced && ((m_tiles + cand - 1) / cand) * p.n_tiles < RN_NUM_SMS) continue;
+      acc_m = cand;
+      break;
+    }
+  }
+  p.acc_m = acc_m;
+  p.tstages = (2 * acc_m * p.block_n <= 512) ? 2 : 1;
+  uint32_t cols = 32;
+  while (cols < (uint32_t)(p.tstages * acc_m * p.block_n)) cols <<= 1;
+  p.tmem_cols = cols;
+  int stages = (int)((budget - fixed) / ((size_t)acc_m * p.a_bytes + p.b_bytes));
   if (stages > 8) stages = 8;
   if (stages < 2) return fail(RN_ERR_UNSUPPORTED, "convtc: tile does not fit shared memory");
   p.stages = stages;
-  *smem_bytes = fixed + (size_t)stages * (p.a_bytes + p.b_bytes);
+  *smem_bytes = fixed + (size_t)stages * ((size_t)acc_m * p.a_bytes + p.b_bytes);
   int rc;
   const uint32_t abox[4] = {(uint32_t)p.kc, (uint32_t)p.BW, (uint32_t)p.BH, (uint32_t)p.BN};
   rc = encode_activation_maps(p.a_map, a, cred, aW, aH, d->N, kind == 0 ? d->stride : 1, abox, row_bytes);
@@ -728,7 +784,7 @@ static int create_sub(const rn_conv_desc* d, int kind, const void* a, const void
     rc = encode_map(&p.o_map, out_base, 4, dims, ostr, box, p.gw * 2, "output");
     if (rc) return rc;
   }
-  const long total = (long)p.tiles_w * p.tiles_h * p.tiles_n * p.n_tiles;
+  const long total = ((m_tiles + acc_m - 1) / acc_m) * p.n_tiles;
   *grid = (int)(total < RN_NUM_SMS ? total : RN_NUM_SMS);
   return RN_OK;
 }
