@@ -13,6 +13,7 @@
 //   bwd reduce       : 2*E*s          (dy, x)
 //   bwd apply        : 3*E*s          (+E*s with the shortcut-gradient addend)
 #include "rn_common.cuh"
+#include <stdlib.h>
 
 namespace rn {
 
@@ -308,7 +309,7 @@ bn_apply_kernel(const T* __restrict__ x, T* __restrict__ y, int64_t M, int C, Bn
 // ------------------------------------------------------------------------------------------
 // backward: reductions
 // ------------------------------------------------------------------------------------------
-template <typename T>
+template <typename T, int U, bool CS>
 __global__ void __launch_bounds__(BN_THREADS)
 bn_bwd_reduce_kernel(const T* __restrict__ dy, const T* __restrict__ x, int64_t M, int C, BnLayout L,
                      const float* __restrict__ gamma, const float* __restrict__ beta, const float* __restrict__ mean,
@@ -336,13 +337,17 @@ bn_bwd_reduce_kernel(const T* __restrict__ dy, const T* __restrict__ x, int64_t 
     const int64_t rows_per_cta = ((M + gridDim.x - 1) / gridDim.x + L.RY - 1) / L.RY * L.RY;
     const int64_t M_end = min(M, (int64_t)(blockIdx.x + 1) * rows_per_cta);
     int64_t r = (int64_t)blockIdx.x * rows_per_cta + ty;
-    constexpr int U = 2;   // 2 x 2 independent 128-bit loads in flight per thread
     for (; r + (U - 1) * stride < M_end; r += U * stride) {
       Vec<T> vx[U], vg[U];
 #pragma unroll
       for (int u = 0; u < U; ++u) {
-        vx[u].load(x + (r + u * stride) * C + col);
-        vg[u].load(dy + (r + u * stride) * C + col);
+        if (CS) {
+          vx[u].load_stream(x + (r + u * stride) * C + col);
+          vg[u].load_stream(dy + (r + u * stride) * C + col);
+        } else {
+          vx[u].load(x + (r + u * stride) * C + col);
+          vg[u].load(dy + (r + u * stride) * C + col);
+        }
       }
 #pragma unroll
       for (int u = 0; u < U; ++u) {
@@ -587,9 +592,27 @@ static int bn_bwd_reduce_launch(const void* dy, const void* x, int64_t M, int C,
   if (scratch == nullptr || scratch_bytes < need)
     return fail(RN_ERR_SCRATCH, "bn_bwd_reduce: scratch %zu < %zu bytes", scratch_bytes, need);
   size_t smem = (size_t)L.RY * L.CW * 2 * Vec<T>::N * sizeof(float);
-  bn_bwd_reduce_kernel<T><<<dim3(L.G, L.gridY), BN_THREADS, smem, st>>>(
-      (const T*)dy, (const T*)x, M, C, L, gamma, beta, mean, rstd, leak, dgamma, dbeta, (unsigned*)scratch,
-      (float*)((char*)scratch + 256));
+  static int variant = -1;
+  if (variant < 0) { const char* e = getenv("RN_BN_VARIANT"); variant = e ? atoi(e) : 0; }
+#define RN_LAUNCH_REDUCE(UU, CC)                                                                              \
+  bn_bwd_reduce_kernel<T, UU, CC><<<dim3(L.G, L.gridY), BN_THREADS, smem, st>>>(                             \
+      (const T*)dy, (const T*)x, M, C, L, gamma, beta, mean, rstd, leak, dgamma, dbeta, (unsigned*)scratch, \
+      (float*)((char*)scratch + 256))
+  // streaming (evict-first) loads measured +13 % on tensors that exceed L2; smaller tensors keep the
+  // default policy so that the dx pass that follows finds x and dy in L2
+  const bool big = (size_t)M * C * sizeof(T) > ((size_t)48 << 20);
+  switch (variant) {
+    case 1: RN_LAUNCH_REDUCE(2, true); break;
+    case 2: RN_LAUNCH_REDUCE(4, false); break;
+    case 3: RN_LAUNCH_REDUCE(4, true); break;
+    case 4: RN_LAUNCH_REDUCE(1, false); break;
+    case 5: RN_LAUNCH_REDUCE(2, false); break;
+    default:
+      if (big) RN_LAUNCH_REDUCE(2, true);
+      else RN_LAUNCH_REDUCE(2, false);
+      break;
+  }
+#undef RN_LAUNCH_REDUCE
   return check_launch("bn_bwd_reduce_kernel");
 }
 
