@@ -124,9 +124,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const __grid_con
               tma_load_4d(sa + (size_t)j * p.a_bytes, am, &full[stage], kk * p.kc, w0[j] + dw, h0[j] + dh, n0[j]);
             uint8_t* sb = sa + (size_t)p.acc_m * p.a_bytes;
             if (p.b_mn) {
-              for (int j = 0; j < p.b_boxes; ++j)
-                tma_load_3d(sb + (size_t)j * p.b_box_bytes, &p.b_map, &full[stage], nt * p.block_n + j * p.gw,
-                            kk * p.kc, tb);
+              // one op: (gw couts, kc cin rows, b_boxes cout blocks) lands as b_boxes consecutive MN-major boxes
+              tma_load_4d(sb, &p.b_map, &full[stage], 0, kk * p.kc, nt * p.b_boxes, tb);
             } else {
               tma_load_3d(sb, &p.b_map, &full[stage], kk * p.kc, nt * p.block_n, tb);
             }
@@ -260,6 +259,7 @@ struct TcWgradParams {
   CUtensorMap dy_map;
   float* partial;                 // [splits][taps*Cin][Cout]
   int Cin, Cout, taps, cin_blocks, RB;
+  int runA;                       // consecutive cin blocks fetched by one A op (5-D box); A ops per stage = rb_per_cta / runA
   int bwA, bwB;                   // channels per A / B box (64, 32 or 16 -> 128 / 64 / 32-byte swizzled rows)
   int blocksA;                    // A boxes per 128-row accumulator (128 / bwA)
   uint32_t a_box_bytes, b_box_bytes;
@@ -323,15 +323,14 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_wgrad_tc_kernel(const __gr
           mbar_wait(&empty[stage], phase ^ 1);
           uint8_t* sa = smem + (size_t)stage * p.stage_bytes;
           mbar_expect_tx(&full[stage], (uint32_t)valid * p.a_box_bytes + (uint32_t)nb * p.b_box_bytes);
-          for (int j = 0; j < valid; ++j) {
+          for (int j = 0; j < valid; j += p.runA) {      // `valid` is a multiple of runA (whole runs only)
             const int rb = rg * rb_per_cta + j;
             const int tap = rb / p.cin_blocks, cb = rb - tap * p.cin_blocks;
-            tma_load_4d(sa + (size_t)j * p.a_box_bytes, &p.x_map[p.tap_map[tap]], &full[stage], cb * p.bwA,
-                        w0 + p.tap_dw[tap], h0 + p.tap_dh[tap], n0);
+            tma_load_5d(sa + (size_t)j * p.a_box_bytes, &p.x_map[p.tap_map[tap]], &full[stage], 0,
+                        w0 + p.tap_dw[tap], h0 + p.tap_dh[tap], n0, cb);
           }
           uint8_t* sbm = sa + (size_t)rb_per_cta * p.a_box_bytes;
-          for (int j = 0; j < nb; ++j)
-            tma_load_4d(sbm + (size_t)j * p.b_box_bytes, &p.dy_map, &full[stage], nt * p.block_n + j * p.bwB, w0, h0, n0);
+          tma_load_5d(sbm, &p.dy_map, &full[stage], 0, w0, h0, n0, nt * nb);
           if (++stage == p.stages) { stage = 0; phase ^= 1; }
         }
       }
@@ -586,6 +585,26 @@ static int encode_activation_maps(CUtensorMap* maps, const void* base, int C, in
   return RN_OK;
 }
 
+// Same views with the channel axis split as (bw channels inside a block, ..., block index) so that one 5-D
+// box fetches `nblk` consecutive channel blocks: each block lands as its own [pixels][bw] swizzled tile.
+static int encode_activation_maps_5d(CUtensorMap* maps, const void* base, int C, int W, int H, int N, int stride, int bw,
+                                     int pw_, int ph_, int pn_, int nblk) {
+  const int nph = stride == 1 ? 1 : 2;
+  for (int ph = 0; ph < nph; ++ph)
+    for (int pw = 0; pw < nph; ++pw) {
+      const int W2 = stride == 1 ? W : (W - pw + 1) / 2, H2 = stride == 1 ? H : (H - ph + 1) / 2;
+      if (W2 <= 0 || H2 <= 0) continue;
+      const uint64_t st = (uint64_t)stride;
+      const uint64_t dims[5] = {(uint64_t)bw, (uint64_t)W2, (uint64_t)H2, (uint64_t)N, (uint64_t)(C / bw)};
+      const uint64_t str[4] = {st * C * 2, st * W * C * 2, (uint64_t)H * W * C * 2, (uint64_t)bw * 2};
+      const uint32_t box[5] = {(uint32_t)bw, (uint32_t)pw_, (uint32_t)ph_, (uint32_t)pn_, (uint32_t)nblk};
+      const char* b = (const char*)base + ((size_t)ph * W + pw) * C * 2;
+      int rc = encode_map(&maps[ph * 2 + pw], b, 5, dims, str, box, bw * 2, "activation (5-D)");
+      if (rc) return rc;
+    }
+  return RN_OK;
+}
+
 // tap (r, s) of a forward-style gather at `stride`: which map and which box offset
 static void forward_tap(int r, int s, int pad, int stride, int8_t* map, int8_t* dw, int8_t* dh) {
   if (stride == 1) { *map = 0; *dw = (int8_t)(s - pad); *dh = (int8_t)(r - pad); return; }
@@ -598,7 +617,7 @@ static void forward_tap(int r, int s, int pad, int stride, int8_t* map, int8_t* 
 
 struct WgradShape {
   int block_n, n_tiles, acc, cin_blocks, RB, row_groups, kp, stages, PW, PH, PN, tiles_w, tiles_h, tiles_n, k_tiles;
-  int splits, tiles_per_split, bwA, bwB, blocksA;
+  int splits, tiles_per_split, bwA, bwB, blocksA, runA;
   uint32_t a_box_bytes, b_box_bytes, stage_bytes, tmem_cols;
   size_t smem, scratch;
 };
@@ -615,23 +634,44 @@ static bool wgrad_shape(const rn_conv_desc* d, WgradShape* w) {
   w->blocksA = 128 / w->bwA;
   w->cin_blocks = d->Cin / w->bwA;
   w->RB = d->k * d->k * w->cin_blocks;
-  w->acc = 512 / w->block_n;
-  if (w->acc > 4) w->acc = 4;
-  const int need_acc = (w->RB + w->blocksA - 1) / w->blocksA;
-  if (w->acc > need_acc) w->acc = need_acc;
-  w->row_groups = (w->RB + w->blocksA * w->acc - 1) / (w->blocksA * w->acc);
   const int nb = w->block_n / w->bwB;
-  for (w->kp = 64; w->kp >= 32; w->kp /= 2) {
-    w->a_box_bytes = (uint32_t)w->kp * w->bwA * 2;
-    w->b_box_bytes = (uint32_t)w->kp * w->bwB * 2;
-    w->stage_bytes = (uint32_t)(w->blocksA * w->acc) * w->a_box_bytes + (uint32_t)nb * w->b_box_bytes;
-    if ((size_t)w->stage_bytes * 3 <= 200 * 1024) break;
+  static int f_acc = -1, f_kp = -1;
+  if (f_acc < 0) { const char* e = getenv("RN_WG_ACC"); f_acc = e ? atoi(e) : 0; }   // tuning knobs
+  if (f_kp < 0) { const char* e = getenv("RN_WG_KP"); f_kp = e ? atoi(e) : 0; }
+  // Choose (accumulators per CTA, pixels per stage).  Measured on B200: a stage costs ~300 cycles per TMA
+  // op issued, so the winner is the configuration with the fewest TMA ops per MAC that still leaves >= 3
+  // pipeline stages in shared memory (ties: fewer bytes per MAC).
+  double best = 1e30;
+  bool found = false;
+  const int need_acc = (w->RB + w->blocksA - 1) / w->blocksA;
+  for (int acc = 1; acc <= 4; acc <<= 1) {
+    if (acc * w->block_n > 512) break;
+    if (acc > 1 && acc / 2 >= need_acc) break;
+    if (f_acc && acc != f_acc) continue;
+    const int rbpc = w->blocksA * acc;
+    int run;
+    if (w->cin_blocks >= rbpc) run = (w->cin_blocks % rbpc == 0) ? rbpc : 1;
+    else run = (rbpc % w->cin_blocks == 0) ? w->cin_blocks : 1;
+    for (int kp = 128; kp >= 32; kp >>= 1) {
+      if (f_kp && kp != f_kp) continue;
+      const uint32_t abox = (uint32_t)kp * w->bwA * 2, bbox = (uint32_t)kp * w->bwB * 2;
+      if (abox % 1024 || bbox % 1024) continue;            // swizzle atoms must stay 1024-byte aligned
+      const size_t stage = (size_t)rbpc * abox + (size_t)nb * bbox;
+      const int stages = (int)((220 * 1024) / stage);
+      if (stages < 3) continue;
+      const double ops = (double)rbpc / run + 1.0;
+      const double macs = (double)acc * kp * w->block_n;
+      const double cost = ops / macs * 1e6 + (double)stage / macs * 1e-3;
+      if (cost < best) {
+        best = cost; found = true;
+        w->acc = acc; w->kp = kp; w->runA = run;
+        w->a_box_bytes = abox; w->b_box_bytes = bbox; w->stage_bytes = (uint32_t)stage;
+        w->stages = stages > 8 ? 8 : stages;
+      }
+    }
   }
-  if (w->kp < 32) return false;
-  if (w->a_box_bytes % 1024 || w->b_box_bytes % 1024) return false;   // swizzle atoms must stay 1024-byte aligned
-  w->stages = (int)((220 * 1024) / w->stage_bytes);
-  if (w->stages > 8) w->stages = 8;
-  if (w->stages < 2) return false;
+  if (!found) return false;
+  w->row_groups = (w->RB + w->blocksA * w->acc - 1) / (w->blocksA * w->acc);
   w->smem = (size_t)w->stages * w->stage_bytes + 2048;
   uint32_t cols = 32;
   while (cols < (uint32_t)(w->acc * w->block_n)) cols <<= 1;
@@ -641,8 +681,10 @@ static bool wgrad_shape(const rn_conv_desc* d, WgradShape* w) {
   w->tiles_h = (d->Ho + w->PH - 1) / w->PH;
   w->tiles_n = (d->N + w->PN - 1) / w->PN;
   w->k_tiles = w->tiles_w * w->tiles_h * w->tiles_n;
+  // split-K factor: as many work items as fit in ONE wave of the persistent grid (rounding up would leave a
+  // second, almost empty wave that doubles the kernel time)
   const int base = w->row_groups * w->n_tiles;
-  int splits = (RN_NUM_SMS + base - 1) / base;
+  int splits = RN_NUM_SMS / base;
   const int max_splits = w->k_tiles / 8 > 0 ? w->k_tiles / 8 : 1;
   if (splits > max_splits) splits = max_splits;
   if (splits < 1) splits = 1;
@@ -765,10 +807,11 @@ static int create_sub(const rn_conv_desc* d, int kind, const void* a, const void
     p.b_mn = 1;
     p.b_boxes = p.block_n / p.gw;
     p.b_box_bytes = (uint32_t)p.kc * p.gw * 2;
-    const uint64_t dims[3] = {(uint64_t)ncols, (uint64_t)cred, (uint64_t)(d->k * d->k)};
-    const uint64_t str[2] = {(uint64_t)ncols * 2, (uint64_t)ncols * cred * 2};
-    const uint32_t box[3] = {(uint32_t)p.gw, (uint32_t)p.kc, 1u};
-    rc = encode_map(&p.b_map, b, 3, dims, str, box, p.gw * 2, "weights (MN-major)");
+    // dims (gw couts inside a block, cin, cout block, tap): one TMA op fetches all cout blocks of the tile
+    const uint64_t dims[4] = {(uint64_t)p.gw, (uint64_t)cred, (uint64_t)(ncols / p.gw), (uint64_t)(d->k * d->k)};
+    const uint64_t str[3] = {(uint64_t)ncols * 2, (uint64_t)p.gw * 2, (uint64_t)ncols * cred * 2};
+    const uint32_t box[4] = {(uint32_t)p.gw, (uint32_t)p.kc, (uint32_t)p.b_boxes, 1u};
+    rc = encode_map(&p.b_map, b, 4, dims, str, box, p.gw * 2, "weights (MN-major)");
     if (rc) return rc;
   } else {
     // dgrad: the same bf16 HWIO tensor is K-major for this GEMM (K = Cout contiguous): dims (cred, ncols, taps)
@@ -853,20 +896,16 @@ static int create_wgrad_plan(const rn_conv_desc* d, const void* x, const void* d
   w.k_tiles = ws.k_tiles; w.splits = ws.splits; w.tiles_per_split = ws.tiles_per_split; w.kp = ws.kp;
   w.stages = ws.stages; w.stage_bytes = ws.stage_bytes; w.tmem_cols = ws.tmem_cols;
   w.bwA = ws.bwA; w.bwB = ws.bwB; w.blocksA = ws.blocksA; w.a_box_bytes = ws.a_box_bytes; w.b_box_bytes = ws.b_box_bytes;
+  w.runA = ws.runA;
   w.partial = ws.splits > 1 ? (float*)scratch : (float*)dw;
   for (int r = 0; r < d->k; ++r)
     for (int s = 0; s < d->k; ++s)
       forward_tap(r, s, d->pad, d->stride, &w.tap_map[r * d->k + s], &w.tap_dw[r * d->k + s], &w.tap_dh[r * d->k + s]);
-  const uint32_t box[4] = {(uint32_t)ws.bwA, (uint32_t)ws.PW, (uint32_t)ws.PH, (uint32_t)ws.PN};
-  int rc = encode_activation_maps(w.x_map, x, d->Cin, d->W, d->H, d->N, d->stride, box, ws.bwA * 2);
+  int rc = encode_activation_maps_5d(w.x_map, x, d->Cin, d->W, d->H, d->N, d->stride, ws.bwA, ws.PW, ws.PH, ws.PN, ws.runA);
   if (rc) return rc;
-  {
-    const uint64_t dims[4] = {(uint64_t)d->Cout, (uint64_t)d->Wo, (uint64_t)d->Ho, (uint64_t)d->N};
-    const uint64_t str[3] = {(uint64_t)d->Cout * 2, (uint64_t)d->Wo * d->Cout * 2, (uint64_t)d->Ho * d->Wo * d->Cout * 2};
-    const uint32_t boxb[4] = {(uint32_t)ws.bwB, (uint32_t)ws.PW, (uint32_t)ws.PH, (uint32_t)ws.PN};
-    rc = encode_map(&w.dy_map, dy, 4, dims, str, boxb, ws.bwB * 2, "dy");
-    if (rc) return rc;
-  }
+  rc = encode_activation_maps_5d(&w.dy_map, dy, d->Cout, d->Wo, d->Ho, d->N, 1, ws.bwB, ws.PW, ws.PH, ws.PN,
+                                 ws.block_n / ws.bwB);
+  if (rc) return rc;
   const long total = (long)ws.row_groups * ws.n_tiles * ws.splits;
   pl->wgrid = (int)(total < RN_NUM_SMS ? total : RN_NUM_SMS);
   pl->wsmem = ws.smem;
