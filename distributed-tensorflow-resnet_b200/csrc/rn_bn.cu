@@ -30,17 +30,21 @@ struct BnLayout {
 };
 
 template <typename T>
-static BnLayout bn_layout(int64_t M, int C, int waves) {
+static BnLayout bn_layout(int64_t M, int C, int waves, int max_cw = 32, int64_t bytes_per_cta = 65536) {
   BnLayout L;
   constexpr int V = Vec<T>::N;
   L.CV = C / V;
-  L.CW = L.CV < 32 ? L.CV : 32;
+  // Reducing kernels use narrow channel chunks (max_cw = 8 column groups): more chunks -> the serial
+  // last-CTA reduction runs in parallel across chunks and each CTA covers 4x more rows per iteration
+  // (fewer dependent load batches on small tensors).
+  if ((L.CV + max_cw - 1) / max_cw > BN_MAX_CHUNKS) max_cw = 32;
+  L.CW = L.CV < max_cw ? L.CV : max_cw;
   L.RY = BN_THREADS / L.CW;
   L.gridY = (L.CV + L.CW - 1) / L.CW;
   // at least ~64 KB of the tensor per CTA (per channel chunk): small tensors get few CTAs, which keeps
   // the serial last-CTA reduction over the per-CTA partials short
   const int64_t chunk_bytes = M * (int64_t)L.CW * V * (int64_t)sizeof(T);
-  int64_t want = (chunk_bytes + 65535) / 65536;
+  int64_t want = (chunk_bytes + bytes_per_cta - 1) / bytes_per_cta;
   int64_t cap = (int64_t)RN_NUM_SMS * waves / L.gridY;
   if (cap < 1) cap = 1;
   if (cap > BN_MAX_G) cap = BN_MAX_G;
@@ -138,6 +142,23 @@ __device__ __forceinline__ void final_reduce(const float* base, unsigned nparts,
   }
   out0 = s0;
   out1 = s1;
+}
+
+// layout knobs of the two reducing kernels (tunable from the environment for experiments)
+static int bn_reduce_cw() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("RN_BN_CW"); v = e ? atoi(e) : 8; if (v < 1 || v > 32) v = 8; }
+  return v;
+}
+static int bn_apply_cw() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("RN_BN_APPLY_CW"); v = e ? atoi(e) : 16; if (v < 1 || v > 32) v = 16; }
+  return v;
+}
+static int64_t bn_reduce_cta_bytes() {
+  static int64_t v = -1;
+  if (v < 0) { const char* e = getenv("RN_BN_CTA_KB"); v = (e ? atoi(e) : 64) * 1024; if (v < 4096) v = 65536; }
+  return v;
 }
 
 // ------------------------------------------------------------------------------------------
@@ -519,7 +540,7 @@ static int bn_stats_launch(const void* x, const void* addend, void* sum_out, int
                            size_t scratch_bytes, cudaStream_t st) {
   int rc = check_bn_args<T>(M, C);
   if (rc) return rc;
-  BnLayout L = bn_layout<T>(M, C, 4);
+  BnLayout L = bn_layout<T>(M, C, 4, bn_reduce_cw(), bn_reduce_cta_bytes());
   const size_t need = 256 + (size_t)L.gridY * L.G * 2 * L.CW * Vec<T>::N * sizeof(float);
   if (scratch == nullptr || scratch_bytes < need)
     return fail(RN_ERR_SCRATCH, "bn_stats: scratch %zu < %zu bytes", scratch_bytes, need);
@@ -563,7 +584,7 @@ static int bn_apply_launch(const void* x, void* y, int64_t M, int C, const float
                            const float* mean, const float* rstd, int moving, float eps, float leak, cudaStream_t st) {
   int rc = check_bn_args<T>(M, C);
   if (rc) return rc;
-  BnLayout L = bn_layout<T>(M, C, 8);
+  BnLayout L = bn_layout<T>(M, C, 8, bn_apply_cw(), 16384);
   bn_apply_kernel<T><<<dim3(L.G, L.gridY), BN_THREADS, 0, st>>>((const T*)x, (T*)y, M, C, L, gamma, beta, mean, rstd,
                                                                moving, eps, leak);
   return check_launch("bn_apply_kernel");
@@ -587,7 +608,7 @@ static int bn_bwd_reduce_launch(const void* dy, const void* x, int64_t M, int C,
                                 void* scratch, size_t scratch_bytes, cudaStream_t st) {
   int rc = check_bn_args<T>(M, C);
   if (rc) return rc;
-  BnLayout L = bn_layout<T>(M, C, 4);
+  BnLayout L = bn_layout<T>(M, C, 4, bn_reduce_cw(), bn_reduce_cta_bytes());
   const size_t need = 256 + (size_t)L.gridY * L.G * 2 * L.CW * Vec<T>::N * sizeof(float);
   if (scratch == nullptr || scratch_bytes < need)
     return fail(RN_ERR_SCRATCH, "bn_bwd_reduce: scratch %zu < %zu bytes", scratch_bytes, need);
@@ -636,7 +657,7 @@ static int bn_bwd_apply_launch(const void* dy, const void* x, void* dx, const vo
                                const float* dgamma, const float* dbeta, float leak, cudaStream_t st) {
   int rc = check_bn_args<T>(M, C);
   if (rc) return rc;
-  BnLayout L = bn_layout<T>(M, C, 8);
+  BnLayout L = bn_layout<T>(M, C, 8, bn_apply_cw(), 16384);
   dim3 grid(L.G, L.gridY);
   if (addend)
     bn_bwd_apply_kernel<T, true><<<grid, BN_THREADS, 0, st>>>((const T*)dy, (const T*)x, (T*)dx, (const T*)addend, M, C,
