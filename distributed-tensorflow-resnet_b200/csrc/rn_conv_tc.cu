@@ -95,33 +95,37 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const __grid_con
   const uint32_t b_tx = (uint32_t)p.block_n * (uint32_t)(p.kc * 2);
 
   if (warp == 0) {
-    if (lane == 0) {
-      // ===================== TMA producer =====================
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int t = blockIdx.x; t < total; t += gridDim.x) {
-        const int nt = t % p.n_tiles;
-        const int mg = t / p.n_tiles;
-        int nvalid = m_tiles - mg * p.acc_m;
-        if (nvalid > p.acc_m) nvalid = p.acc_m;
-        int w0[4], h0[4], n0[4];
-        for (int j = 0; j < nvalid; ++j) {
-          int mt = mg * p.acc_m + j;
-          w0[j] = (mt % p.tiles_w) * p.BW;
-          mt /= p.tiles_w;
-          h0[j] = (mt % p.tiles_h) * p.BH;
-          n0[j] = (mt / p.tiles_h) * p.BN;
-        }
-        for (int tap = 0; tap < p.taps; ++tap) {
-          const CUtensorMap* am = &p.a_map[p.tap_map[tap]];
-          const int dw = p.tap_dw[tap], dh = p.tap_dh[tap];
-          const int tb = p.tap_b[tap];
-          for (int kk = 0; kk < p.k_chunks; ++kk) {
-            mbar_wait(&empty[stage], phase ^ 1);
+    // ===================== TMA producer (whole warp loops, one elected lane issues) =====================
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int t = blockIdx.x; t < total; t += gridDim.x) {
+      const int nt = t % p.n_tiles;
+      const int mg = t / p.n_tiles;
+      int nvalid = m_tiles - mg * p.acc_m;
+      if (nvalid > p.acc_m) nvalid = p.acc_m;
+      int w0[4], h0[4], n0[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        int mt = mg * p.acc_m + j;
+        w0[j] = (mt % p.tiles_w) * p.BW;
+        mt /= p.tiles_w;
+        h0[j] = (mt % p.tiles_h) * p.BH;
+        n0[j] = (mt / p.tiles_h) * p.BN;
+      }
+      const uint32_t tx = (uint32_t)nvalid * a_tx + b_tx;
+      for (int tap = 0; tap < p.taps; ++tap) {
+        const CUtensorMap* am = &p.a_map[p.tap_map[tap]];
+        const int dw = p.tap_dw[tap], dh = p.tap_dh[tap];
+        const int tb = p.tap_b[tap];
+        for (int kk = 0; kk < p.k_chunks; ++kk) {
+          mbar_wait(&empty[stage], phase ^ 1);
+          if (elect_one()) {
             uint8_t* sa = smem + (size_t)stage * stage_bytes;
-            mbar_expect_tx(&full[stage], (uint32_t)nvalid * a_tx + b_tx);
-            for (int j = 0; j < nvalid; ++j)
-              tma_load_4d(sa + (size_t)j * p.a_bytes, am, &full[stage], kk * p.kc, w0[j] + dw, h0[j] + dh, n0[j]);
+            mbar_expect_tx(&full[stage], tx);
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+              if (j < nvalid)
+                tma_load_4d(sa + (size_t)j * p.a_bytes, am, &full[stage], kk * p.kc, w0[j] + dw, h0[j] + dh, n0[j]);
             uint8_t* sb = sa + (size_t)p.acc_m * p.a_bytes;
             if (p.b_mn) {
               // one op: (gw couts, kc cin rows, b_boxes cout blocks) lands as b_boxes consecutive MN-major boxes
@@ -129,58 +133,65 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const __grid_con
             } else {
               tma_load_3d(sb, &p.b_map, &full[stage], kk * p.kc, nt * p.block_n, tb);
             }
-            if (++stage == p.stages) { stage = 0; phase ^= 1; }
           }
+          __syncwarp();
+          if (++stage == p.stages) { stage = 0; phase ^= 1; }
         }
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      // ===================== MMA issuer =====================
-      const uint32_t idesc = make_idesc_bf16(TC_BLOCK_M, p.block_n, 0, p.b_mn);
-      const uint32_t rowB = (uint32_t)p.gw * 2, ltB = swizzle_layout_type(p.gw * 2);
-      const int row_bytes = p.kc * 2;
-      const uint32_t lt = swizzle_layout_type(row_bytes);
-      const uint32_t sbo = 8u * row_bytes;
-      const int ksteps = p.kc / 16;
-      int stage = 0;
-      uint32_t phase = 0;
-      int acc = 0;
-      uint32_t acc_phase = 0;
-      for (int t = blockIdx.x; t < total; t += gridDim.x) {
-        const int mg = t / p.n_tiles;
-        int nvalid = m_tiles - mg * p.acc_m;
-        if (nvalid > p.acc_m) nvalid = p.acc_m;
-        mbar_wait(&tempty[acc], acc_phase ^ 1);
+    // ===================== MMA issuer (whole warp loops, one elected lane issues) =====================
+    const uint32_t idesc = make_idesc_bf16(TC_BLOCK_M, p.block_n, 0, p.b_mn);
+    const uint32_t rowB = (uint32_t)p.gw * 2, ltB = swizzle_layout_type(p.gw * 2);
+    const int row_bytes = p.kc * 2;
+    const uint32_t lt = swizzle_layout_type(row_bytes);
+    const uint32_t sbo = 8u * row_bytes;
+    const int ksteps = p.kc / 16;
+    // Descriptors differ only in their 14-bit start-address field (bytes >> 4); every address lies inside this
+    // CTA's shared-memory window (< 256 KB), so stepping is a plain add on the low word.
+    const uint64_t da0 = make_smem_desc(base_u32, 16, sbo, lt);
+    // K-major B: +32 bytes per K step inside the swizzled row.  MN-major B (rows = input channels):
+    // +16 rows per K step, LBO = next 64-column box, SBO = 8 rows.
+    const uint64_t db0 = p.b_mn ? make_smem_desc(base_u32 + (uint32_t)p.acc_m * p.a_bytes, p.b_box_bytes, 8 * rowB, ltB)
+                                : make_smem_desc(base_u32 + (uint32_t)p.acc_m * p.a_bytes, 16, sbo, lt);
+    const uint32_t a_step = 2, b_step = p.b_mn ? (16u * rowB) >> 4 : 2u;
+    const uint32_t stage16 = stage_bytes >> 4, a16 = p.a_bytes >> 4;
+    int stage = 0;
+    uint32_t phase = 0;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int t = blockIdx.x; t < total; t += gridDim.x) {
+      const int mg = t / p.n_tiles;
+      int nvalid = m_tiles - mg * p.acc_m;
+      if (nvalid > p.acc_m) nvalid = p.acc_m;
+      mbar_wait(&tempty[acc], acc_phase ^ 1);
+      tc_fence_after();
+      const uint32_t d_tmem = tmem_base + (uint32_t)(acc * p.acc_m * p.block_n);
+      for (int it = 0; it < k_iters; ++it) {
+        mbar_wait(&full[stage], phase);
         tc_fence_after();
-        const uint32_t d_tmem = tmem_base + (uint32_t)(acc * p.acc_m * p.block_n);
-        for (int it = 0; it < k_iters; ++it) {
-          mbar_wait(&full[stage], phase);
-          tc_fence_after();
-          const uint32_t a_addr = base_u32 + (uint32_t)stage * stage_bytes;
-          const uint32_t b_addr = a_addr + (uint32_t)p.acc_m * p.a_bytes;
+        if (elect_one()) {
+          const uint64_t da_s = da0 + (uint64_t)((uint32_t)stage * stage16);
+          const uint64_t db_s = db0 + (uint64_t)((uint32_t)stage * stage16);
           for (int j = 0; j < nvalid; ++j) {
-            for (int k = 0; k < ksteps; ++k) {
-              const uint64_t da = make_smem_desc(a_addr + (uint32_t)j * p.a_bytes + k * 32, 16, sbo, lt);
-              // K-major B: +32 bytes per K step inside the swizzled row.  MN-major B (rows = input channels):
-              // +16 rows per K step, LBO = next 64-column box, SBO = 8 rows.
-              const uint64_t db = p.b_mn ? make_smem_desc(b_addr + k * 16 * rowB, p.b_box_bytes, 8 * rowB, ltB)
-                                         : make_smem_desc(b_addr + k * 32, 16, sbo, lt);
-              umma_bf16(d_tmem + (uint32_t)(j * p.block_n), da, db, idesc, (it > 0 || k > 0) ? 1u : 0u);
-            }
+            const uint64_t da_j = da_s + (uint64_t)((uint32_t)j * a16);
+            const uint32_t d = d_tmem + (uint32_t)(j * p.block_n);
+#pragma unroll 4
+            for (int k = 0; k < ksteps; ++k)
+              umma_bf16(d, da_j + (uint64_t)(k * a_step), db_s + (uint64_t)(k * b_step), idesc, (it > 0 || k > 0) ? 1u : 0u);
           }
           umma_commit(&empty[stage]);      // frees the smem slot once these MMAs have read it
-          if (++stage == p.stages) { stage = 0; phase ^= 1; }
+          if (it == k_iters - 1) umma_commit(&tfull[acc]);   // accumulators complete
         }
-        umma_commit(&tfull[acc]);          // accumulators complete
-        if (++acc == p.tstages) { acc = 0; acc_phase ^= 1; }
+        __syncwarp();
+        if (++stage == p.stages) { stage = 0; phase ^= 1; }
       }
+      if (++acc == p.tstages) { acc = 0; acc_phase ^= 1; }
     }
   } else {
     // ===================== epilogue (warps 2..5) =====================
     const int quad = warp & 3;                      // TMEM lane quadrant this warp may access
     const int row = quad * 32 + lane;
-    const bool issuer = (threadIdx.x == 64);
     int acc = 0;
     uint32_t acc_phase = 0;
     int buf = 0;
@@ -200,7 +211,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const __grid_con
         const int n0 = (mt / p.tiles_h) * p.BN;
         for (int g = 0; g < groups; ++g) {
           // the TMA store that last read this staging buffer must have finished reading it
-          if (issuer) tma_store_wait_read<1>();
+          if (warp == 2) {
+            if (elect_one()) tma_store_wait_read<1>();
+            __syncwarp();
+          }
           asm volatile("bar.sync 1, 128;" ::: "memory");
           uint8_t* sb = epi_buf + buf * 16384;
           const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) +
@@ -222,10 +236,14 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const __grid_con
           }
           fence_proxy_async();
           asm volatile("bar.sync 1, 128;" ::: "memory");
-          if (issuer) {
-            if (p.accumulate) tma_reduce_add_4d(&p.o_map, sb, nt * p.block_n + g * p.gw, w0, h0, n0);
-            else              tma_store_4d(&p.o_map, sb, nt * p.block_n + g * p.gw, w0, h0, n0);
-            tma_store_commit();
+          if (warp == 2) {
+            // the same (deterministically elected) lane issues, commits and later waits on the bulk stores
+            if (elect_one()) {
+              if (p.accumulate) tma_reduce_add_4d(&p.o_map, sb, nt * p.block_n + g * p.gw, w0, h0, n0);
+              else              tma_store_4d(&p.o_map, sb, nt * p.block_n + g * p.gw, w0, h0, n0);
+              tma_store_commit();
+            }
+            __syncwarp();
           }
           buf ^= 1;
         }
@@ -236,7 +254,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const __grid_con
       if (lane == 0) mbar_arrive(&tempty[acc]);
       if (++acc == p.tstages) { acc = 0; acc_phase ^= 1; }
     }
-    if (issuer) tma_store_wait<0>();
+    if (warp == 2) {
+      if (elect_one()) tma_store_wait<0>();
+      __syncwarp();
+    }
   }
   tc_fence_before();
   __syncthreads();
@@ -304,74 +325,87 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_wgrad_tc_kernel(const __gr
   const int nb = p.block_n / p.bwB;
 
   if (warp == 0) {
-    if (lane == 0) {
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int it = blockIdx.x; it < total; it += gridDim.x) {
-        const int z = it % p.splits;
-        const int nt = (it / p.splits) % p.n_tiles;
-        const int rg = it / (p.splits * p.n_tiles);
-        int valid = p.RB - rg * rb_per_cta;
-        if (valid > rb_per_cta) valid = rb_per_cta;
-        const int kt_end = min((z + 1) * p.tiles_per_split, p.k_tiles);
-        for (int kt = z * p.tiles_per_split; kt < kt_end; ++kt) {
-          int q = kt;
-          const int w0 = (q % p.tiles_w) * p.PW;
-          q /= p.tiles_w;
-          const int h0 = (q % p.tiles_h) * p.PH;
-          const int n0 = (q / p.tiles_h) * p.PN;
-          mbar_wait(&empty[stage], phase ^ 1);
+    // TMA producer: the whole warp loops, one elected lane issues
+    int stage = 0;
+    uint32_t phase = 0;
+    const uint32_t b_tx = (uint32_t)nb * p.b_box_bytes;
+    for (int it = blockIdx.x; it < total; it += gridDim.x) {
+      const int z = it % p.splits;
+      const int nt = (it / p.splits) % p.n_tiles;
+      const int rg = it / (p.splits * p.n_tiles);
+      int valid = p.RB - rg * rb_per_cta;
+      if (valid > rb_per_cta) valid = rb_per_cta;
+      const uint32_t tx = (uint32_t)valid * p.a_box_bytes + b_tx;
+      const int kt_end = min((z + 1) * p.tiles_per_split, p.k_tiles);
+      for (int kt = z * p.tiles_per_split; kt < kt_end; ++kt) {
+        int q = kt;
+        const int w0 = (q % p.tiles_w) * p.PW;
+        q /= p.tiles_w;
+        const int h0 = (q % p.tiles_h) * p.PH;
+        const int n0 = (q / p.tiles_h) * p.PN;
+        mbar_wait(&empty[stage], phase ^ 1);
+        if (elect_one()) {
           uint8_t* sa = smem + (size_t)stage * p.stage_bytes;
-          mbar_expect_tx(&full[stage], (uint32_t)valid * p.a_box_bytes + (uint32_t)nb * p.b_box_bytes);
+          mbar_expect_tx(&full[stage], tx);
+          int rb = rg * rb_per_cta;
+          int tap = rb / p.cin_blocks, cb = rb - tap * p.cin_blocks;
           for (int j = 0; j < valid; j += p.runA) {      // `valid` is a multiple of runA (whole runs only)
-            const int rb = rg * rb_per_cta + j;
-            const int tap = rb / p.cin_blocks, cb = rb - tap * p.cin_blocks;
             tma_load_5d(sa + (size_t)j * p.a_box_bytes, &p.x_map[p.tap_map[tap]], &full[stage], 0,
                         w0 + p.tap_dw[tap], h0 + p.tap_dh[tap], n0, cb);
+            cb += p.runA;
+            if (cb >= p.cin_blocks) { cb -= p.cin_blocks; ++tap; }   // runA divides cin_blocks
           }
           uint8_t* sbm = sa + (size_t)rb_per_cta * p.a_box_bytes;
           tma_load_5d(sbm, &p.dy_map, &full[stage], 0, w0, h0, n0, nt * nb);
-          if (++stage == p.stages) { stage = 0; phase ^= 1; }
         }
+        __syncwarp();
+        if (++stage == p.stages) { stage = 0; phase ^= 1; }
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      const uint32_t idesc = make_idesc_bf16(TC_BLOCK_M, p.block_n, 1, 1);
-      const int ksteps = p.kp / 16;
-      int stage = 0;
-      uint32_t phase = 0, tphase = 0;
-      for (int it = blockIdx.x; it < total; it += gridDim.x) {
-        const int z = it % p.splits;
-        const int rg = it / (p.splits * p.n_tiles);
-        int valid = p.RB - rg * rb_per_cta;
-        if (valid > rb_per_cta) valid = rb_per_cta;
-        const int nacc = (valid + p.blocksA - 1) / p.blocksA;
-        const uint32_t rowA = (uint32_t)p.bwA * 2, rowB = (uint32_t)p.bwB * 2;
-        const uint32_t ltA = swizzle_layout_type(rowA), ltB = swizzle_layout_type(rowB);
-        mbar_wait(tempty, tphase ^ 1);
+    // MMA issuer: the whole warp loops, one elected lane issues
+    const uint32_t idesc = make_idesc_bf16(TC_BLOCK_M, p.block_n, 1, 1);
+    const int ksteps = p.kp / 16;
+    const uint32_t rowA = (uint32_t)p.bwA * 2, rowB = (uint32_t)p.bwB * 2;
+    const uint32_t ltA = swizzle_layout_type(rowA), ltB = swizzle_layout_type(rowB);
+    // MN-major operands: LBO = distance between consecutive channel boxes, SBO = 8 pixel rows; descriptors differ
+    // only in the start-address field (bytes >> 4)
+    const uint64_t da0 = make_smem_desc(base_u32, p.a_box_bytes, 8 * rowA, ltA);
+    const uint64_t db0 = make_smem_desc(base_u32 + (uint32_t)rb_per_cta * p.a_box_bytes, p.b_box_bytes, 8 * rowB, ltB);
+    const uint32_t a_step = (16u * rowA) >> 4, b_step = (16u * rowB) >> 4;
+    const uint32_t stage16 = p.stage_bytes >> 4, acc16 = ((uint32_t)p.blocksA * p.a_box_bytes) >> 4;
+    int stage = 0;
+    uint32_t phase = 0, tphase = 0;
+    for (int it = blockIdx.x; it < total; it += gridDim.x) {
+      const int z = it % p.splits;
+      const int rg = it / (p.splits * p.n_tiles);
+      int valid = p.RB - rg * rb_per_cta;
+      if (valid > rb_per_cta) valid = rb_per_cta;
+      const int nacc = (valid + p.blocksA - 1) / p.blocksA;
+      mbar_wait(tempty, tphase ^ 1);
+      tc_fence_after();
+      const int kt_begin = z * p.tiles_per_split, kt_end = min((z + 1) * p.tiles_per_split, p.k_tiles);
+      for (int kt = kt_begin; kt < kt_end; ++kt) {
+        mbar_wait(&full[stage], phase);
         tc_fence_after();
-        const int kt_begin = z * p.tiles_per_split, kt_end = min((z + 1) * p.tiles_per_split, p.k_tiles);
-        for (int kt = kt_begin; kt < kt_end; ++kt) {
-          mbar_wait(&full[stage], phase);
-          tc_fence_after();
-          const uint32_t a_addr = base_u32 + (uint32_t)stage * p.stage_bytes;
-          const uint32_t b_addr = a_addr + (uint32_t)rb_per_cta * p.a_box_bytes;
+        if (elect_one()) {
+          const uint64_t da_s = da0 + (uint64_t)((uint32_t)stage * stage16);
+          const uint64_t db_s = db0 + (uint64_t)((uint32_t)stage * stage16);
           for (int a = 0; a < nacc; ++a) {
-            for (int ks = 0; ks < ksteps; ++ks) {
-              // MN-major operands: LBO = distance between consecutive channel boxes, SBO = 8 pixel rows
-              const uint64_t da = make_smem_desc(a_addr + (uint32_t)(p.blocksA * a) * p.a_box_bytes + ks * 16 * rowA,
-                                                 p.a_box_bytes, 8 * rowA, ltA);
-              const uint64_t db = make_smem_desc(b_addr + ks * 16 * rowB, p.b_box_bytes, 8 * rowB, ltB);
-              umma_bf16(tmem_base + (uint32_t)(a * p.block_n), da, db, idesc, (kt > kt_begin || ks > 0) ? 1u : 0u);
-            }
+            const uint64_t da_a = da_s + (uint64_t)((uint32_t)a * acc16);
+            const uint32_t d = tmem_base + (uint32_t)(a * p.block_n);
+#pragma unroll 4
+            for (int ks = 0; ks < ksteps; ++ks)
+              umma_bf16(d, da_a + (uint64_t)(ks * a_step), db_s + (uint64_t)(ks * b_step), idesc,
+                        (kt > kt_begin || ks > 0) ? 1u : 0u);
           }
           umma_commit(&empty[stage]);
-          if (++stage == p.stages) { stage = 0; phase ^= 1; }
+          if (kt == kt_end - 1) umma_commit(tfull);
         }
-        umma_commit(tfull);
-        tphase ^= 1;
+        __syncwarp();
+        if (++stage == p.stages) { stage = 0; phase ^= 1; }
       }
+      tphase ^= 1;
     }
   } else {
     const int quad = warp & 3;
