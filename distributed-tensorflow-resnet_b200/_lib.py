@@ -59,6 +59,13 @@ SIGNATURES = {
     "rn_weights_to_bf16_batched": (C.c_int, [vp, i32, vp]),
     "rn_im2col": (C.c_int, [vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, i32, i32, i32, vp]),
     "rn_stem_weights": (C.c_int, [vp, i32, i32, i32, vp, vp]),
+    "rn_stem_s2d_supported": (C.c_int, [pdesc]),
+    "rn_stem_s2d_geometry": (C.c_int, [pdesc, C.POINTER(i32), C.POINTER(i32), C.POINTER(i32)]),
+    "rn_stem_s2d_pack": (C.c_int, [pdesc, vp, i32, vp, vp]),
+    "rn_stem_s2d_weights": (C.c_int, [pdesc, vp, vp, vp]),
+    "rn_stem_s2d_wgrad_unpack": (C.c_int, [pdesc, vp, vp, vp]),
+    "rn_stem_s2d_scratch_bytes": (sz, [pdesc, C.c_int]),
+    "rn_stem_s2d_plan_create": (C.c_int, [pdesc, C.c_int, vp, vp, vp, vp, sz, C.POINTER(vp)]),
     "rn_bn_scratch_bytes": (sz, [i64, i32]),
     "rn_bn_stats_fwd": (C.c_int, [vp, vp, vp, i64, i32, i32, f32, f32, i32, vp, vp, vp, vp, vp, sz, vp]),
     "rn_bn_stats_fwd_noalloc": (C.c_int, [vp, vp, vp, i64, i32, i32, f32, f32, i32, vp, vp, vp, vp, vp]),

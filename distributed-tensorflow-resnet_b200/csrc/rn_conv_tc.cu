@@ -639,6 +639,22 @@ static int encode_activation_maps_5d(CUtensorMap* maps, const void* base, int C,
   return RN_OK;
 }
 
+// An explicitly strided [N,H,W,C] bf16 view (strides in bytes; the W stride may be SMALLER than C*2, i.e. the
+// "channel" rows of neighbouring pixels overlap: the space-to-depth stem reads a 4-pixel window per row).
+struct ActView { int C, W, H, N; uint64_t sw, sh, sn; };
+
+static int encode_view(CUtensorMap* m, const void* base, const ActView& v, const uint32_t* box, int row_bytes) {
+  const uint64_t dims[4] = {(uint64_t)v.C, (uint64_t)v.W, (uint64_t)v.H, (uint64_t)v.N};
+  const uint64_t str[3] = {v.sw, v.sh, v.sn};
+  return encode_map(m, base, 4, dims, str, box, row_bytes, "activation view");
+}
+static int encode_view_5d(CUtensorMap* m, const void* base, const ActView& v, int bw, int pw_, int ph_, int pn_, int nblk) {
+  const uint64_t dims[5] = {(uint64_t)bw, (uint64_t)v.W, (uint64_t)v.H, (uint64_t)v.N, (uint64_t)(v.C / bw)};
+  const uint64_t str[4] = {v.sw, v.sh, v.sn, (uint64_t)bw * 2};
+  const uint32_t box[5] = {(uint32_t)bw, (uint32_t)pw_, (uint32_t)ph_, (uint32_t)pn_, (uint32_t)nblk};
+  return encode_map(m, base, 5, dims, str, box, bw * 2, "activation view (5-D)");
+}
+
 // tap (r, s) of a forward-style gather at `stride`: which map and which box offset
 static void forward_tap(int r, int s, int pad, int stride, int8_t* map, int8_t* dw, int8_t* dh) {
   if (stride == 1) { *map = 0; *dw = (int8_t)(s - pad); *dh = (int8_t)(r - pad); return; }
@@ -776,7 +792,7 @@ struct TapSpec { int8_t map, dw, dh, b; };
 
 static int create_sub(const rn_conv_desc* d, int kind, const void* a, const void* b, const void* out_base,
                       int oW, int oH, const uint64_t* ostr, const TapSpec* taps, int ntaps, TcConvParams* pp,
-                      int* grid, size_t* smem_bytes) {
+                      int* grid, size_t* smem_bytes, const ActView* view = nullptr, int b_taps = 0) {
   TcConvParams& p = *pp;
   memset(&p, 0, sizeof(p));
   const int cred = kind == 0 ? d->Cin : d->Cout;
@@ -834,7 +850,9 @@ static int create_sub(const rn_conv_desc* d, int kind, const void* a, const void
   *smem_bytes = fixed + (size_t)stages * ((size_t)acc_m * p.a_bytes + p.b_bytes);
   int rc;
   const uint32_t abox[4] = {(uint32_t)p.kc, (uint32_t)p.BW, (uint32_t)p.BH, (uint32_t)p.BN};
-  rc = encode_activation_maps(p.a_map, a, cred, aW, aH, d->N, kind == 0 ? d->stride : 1, abox, row_bytes);
+  if (b_taps == 0) b_taps = d->k * d->k;
+  rc = view ? encode_view(&p.a_map[0], a, *view, abox, row_bytes)
+            : encode_activation_maps(p.a_map, a, cred, aW, aH, d->N, kind == 0 ? d->stride : 1, abox, row_bytes);
   if (rc) return rc;
   if (kind == 0) {
     // fprop: bf16 HWIO [tap][Cin][Cout] read as an MN-major B operand: dims (Cout, Cin, taps)
@@ -842,14 +860,14 @@ static int create_sub(const rn_conv_desc* d, int kind, const void* a, const void
     p.b_boxes = p.block_n / p.gw;
     p.b_box_bytes = (uint32_t)p.kc * p.gw * 2;
     // dims (gw couts inside a block, cin, cout block, tap): one TMA op fetches all cout blocks of the tile
-    const uint64_t dims[4] = {(uint64_t)p.gw, (uint64_t)cred, (uint64_t)(ncols / p.gw), (uint64_t)(d->k * d->k)};
+    const uint64_t dims[4] = {(uint64_t)p.gw, (uint64_t)cred, (uint64_t)(ncols / p.gw), (uint64_t)b_taps};
     const uint64_t str[3] = {(uint64_t)ncols * 2, (uint64_t)p.gw * 2, (uint64_t)ncols * cred * 2};
     const uint32_t box[4] = {(uint32_t)p.gw, (uint32_t)p.kc, (uint32_t)p.b_boxes, 1u};
     rc = encode_map(&p.b_map, b, 4, dims, str, box, p.gw * 2, "weights (MN-major)");
     if (rc) return rc;
   } else {
     // dgrad: the same bf16 HWIO tensor is K-major for this GEMM (K = Cout contiguous): dims (cred, ncols, taps)
-    const uint64_t dims[3] = {(uint64_t)cred, (uint64_t)ncols, (uint64_t)(d->k * d->k)};
+    const uint64_t dims[3] = {(uint64_t)cred, (uint64_t)ncols, (uint64_t)b_taps};
     const uint64_t str[2] = {(uint64_t)cred * 2, (uint64_t)ncols * cred * 2};
     const uint32_t box[3] = {(uint32_t)p.kc, (uint32_t)p.block_n, 1u};
     rc = encode_map(&p.b_map, b, 3, dims, str, box, row_bytes, "weights");
@@ -918,7 +936,8 @@ static int create_gemm_plan(const rn_conv_desc* d, int kind, const void* a, cons
 }
 
 static int create_wgrad_plan(const rn_conv_desc* d, const void* x, const void* dy, void* dw, void* scratch,
-                             size_t scratch_bytes, rn_convtc_plan* pl) {
+                             size_t scratch_bytes, rn_convtc_plan* pl, const ActView* view = nullptr,
+                             const TapSpec* taps = nullptr) {
   WgradShape ws;
   if (!wgrad_shape(d, &ws)) return fail(RN_ERR_UNSUPPORTED, "convtc wgrad: shape not supported");
   if (ws.scratch > 0 && (scratch == nullptr || scratch_bytes < ws.scratch))
@@ -935,7 +954,10 @@ static int create_wgrad_plan(const rn_conv_desc* d, const void* x, const void* d
   for (int r = 0; r < d->k; ++r)
     for (int s = 0; s < d->k; ++s)
       forward_tap(r, s, d->pad, d->stride, &w.tap_map[r * d->k + s], &w.tap_dw[r * d->k + s], &w.tap_dh[r * d->k + s]);
-  int rc = encode_activation_maps_5d(w.x_map, x, d->Cin, d->W, d->H, d->N, d->stride, ws.bwA, ws.PW, ws.PH, ws.PN, ws.runA);
+  if (taps)
+    for (int t = 0; t < d->k * d->k; ++t) { w.tap_map[t] = taps[t].map; w.tap_dw[t] = taps[t].dw; w.tap_dh[t] = taps[t].dh; }
+  int rc = view ? encode_view_5d(&w.x_map[0], x, *view, ws.bwA, ws.PW, ws.PH, ws.PN, ws.runA)
+                : encode_activation_maps_5d(w.x_map, x, d->Cin, d->W, d->H, d->N, d->stride, ws.bwA, ws.PW, ws.PH, ws.PN, ws.runA);
   if (rc) return rc;
   rc = encode_activation_maps_5d(&w.dy_map, dy, d->Cout, d->Wo, d->Ho, d->N, 1, ws.bwB, ws.PW, ws.PH, ws.PN,
                                  ws.block_n / ws.bwB);
@@ -1111,4 +1133,200 @@ extern "C" int rn_weights_to_bf16_batched(const void* jobs_device, int32_t njobs
   RN_REQUIRE(jobs_device && njobs > 0 && njobs <= 65535, "weights_to_bf16_batched: bad arguments");
   weights_to_bf16_batched_kernel<<<dim3(16, njobs), 256, 0, as_stream(stream)>>>((const rn::RelayoutJob*)jobs_device);
   return check_launch("weights_to_bf16_batched_kernel");
+}
+
+// ------------------------------------------------------------------------------------------
+// Stride-2 stem (ImageNet 7x7/2 over the 3-channel image, resnet_model_official.py:310) without an
+// unfolded matrix.  The padded image is packed 2x2 -> channels ("space to depth"):
+//     U[n, h2, w2, (dy*2 + dx)*Cin + c] = x[n, 2*h2 + dy - pad, 2*w2 + dx - pad, c]      (16 bf16 = 32 bytes per pixel)
+// so the k x k / 2 convolution becomes a T x T / 1 one, T = ceil(k/2), over U.  A TMA view of U whose
+// W stride (32 B) is smaller than its 128-byte rows hands the kernels, per output pixel and kernel row
+// kh2, the 4 horizontally neighbouring packed pixels as ONE 64-channel row: the layer runs as T
+// vertical taps over 64 channels (fprop K = T*64; wgrad 2 accumulators), reading U (tens of MB,
+// L2-resident) instead of a [pixels][k*k*Cin] matrix.
+// ------------------------------------------------------------------------------------------
+namespace rn {
+struct S2dGeom { int T, H2, W2, Cp; };
+static bool s2d_geometry(const rn_conv_desc* d, S2dGeom* g) {
+  if (!d || d->stride != 2 || d->Cin < 1 || d->Cin > 4 || d->k < 2 || d->k > 8 || d->pad < 0) return false;
+  g->T = (d->k + 1) / 2;
+  g->H2 = d->Ho + g->T - 1;
+  g->W2 = d->Wo + 3;            // every row reads a 4-pixel window
+  g->Cp = 16;
+  return true;
+}
+
+template <typename T, int CIN>
+__global__ void __launch_bounds__(256)
+s2d_pack_kernel(const T* __restrict__ x, __nv_bfloat16* __restrict__ u, int N, int H, int W, int H2, int W2, int pad) {
+  const int64_t total = (int64_t)N * H2 * W2;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int w2 = (int)(i % W2);
+    int64_t q = i / W2;
+    const int h2 = (int)(q % H2);
+    const int n = (int)(q / H2);
+    float lo[8], hi[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { lo[j] = 0.f; hi[j] = 0.f; }
+#pragma unroll
+    for (int dy = 0; dy < 2; ++dy) {
+      const int h = 2 * h2 + dy - pad;
+#pragma unroll
+      for (int dx = 0; dx < 2; ++dx) {
+        const int w = 2 * w2 + dx - pad;
+        if (h >= 0 && h < H && w >= 0 && w < W) {
+          const T* src = x + (((int64_t)n * H + h) * W + w) * CIN;
+#pragma unroll
+          for (int c = 0; c < CIN; ++c) {
+            const int j = (dy * 2 + dx) * CIN + c;       // compile-time after unrolling
+            const float v = to_f<T>(src[c]);
+            if (j < 8) lo[j] = v; else hi[j - 8] = v;
+          }
+        }
+      }
+    }
+    Vec<__nv_bfloat16> o;
+    o.pack(lo);
+    o.store(u + i * 16);
+    o.pack(hi);
+    o.store(u + i * 16 + 8);
+  }
+}
+
+template <typename T>
+static void s2d_pack_launch(const T* x, __nv_bfloat16* u, const rn_conv_desc* d, const S2dGeom& g, cudaStream_t st) {
+  const int64_t total = (int64_t)d->N * g.H2 * g.W2;
+  const int grid = grid_for(total, 256, 16);
+  switch (d->Cin) {
+    case 1: s2d_pack_kernel<T, 1><<<grid, 256, 0, st>>>(x, u, d->N, d->H, d->W, g.H2, g.W2, d->pad); break;
+    case 2: s2d_pack_kernel<T, 2><<<grid, 256, 0, st>>>(x, u, d->N, d->H, d->W, g.H2, g.W2, d->pad); break;
+    case 3: s2d_pack_kernel<T, 3><<<grid, 256, 0, st>>>(x, u, d->N, d->H, d->W, g.H2, g.W2, d->pad); break;
+    default: s2d_pack_kernel<T, 4><<<grid, 256, 0, st>>>(x, u, d->N, d->H, d->W, g.H2, g.W2, d->pad); break;
+  }
+}
+
+// bf16 HWIO [k][k][Cin][Cout] -> bf16 [T][64 = kw2*16 + (dy*2+dx)*Cin + c][Cout]  (zero where kh or kw >= k)
+__global__ void s2d_weights_kernel(const __nv_bfloat16* __restrict__ w, __nv_bfloat16* __restrict__ w2, int k, int Cin,
+                                   int Cout, int T) {
+  const int64_t total = (int64_t)T * 64 * Cout;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int co = (int)(i % Cout);
+    const int r = (int)((i / Cout) % 64);
+    const int kh2 = (int)(i / ((int64_t)Cout * 64));
+    const int kw2 = r / 16, c16 = r % 16;
+    const int q = c16 / Cin, c = c16 % Cin;
+    const int kh = 2 * kh2 + (q >> 1), kw = 2 * kw2 + (q & 1);
+    __nv_bfloat16 v = __float2bfloat16_rn(0.f);
+    if (q < 4 && kh < k && kw < k) v = w[(((int64_t)kh * k + kw) * Cin + c) * Cout + co];
+    w2[i] = v;
+  }
+}
+
+// fp32 [T][64][Cout] packed gradient -> fp32 HWIO [k][k][Cin][Cout]
+__global__ void s2d_wgrad_unpack_kernel(const float* __restrict__ dw2, float* __restrict__ dw, int k, int Cin, int Cout) {
+  const int64_t total = (int64_t)k * k * Cin * Cout;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int co = (int)(i % Cout);
+    int64_t q = i / Cout;
+    const int c = (int)(q % Cin);
+    q /= Cin;
+    const int kw = (int)(q % k), kh = (int)(q / k);
+    const int r = (kw >> 1) * 16 + ((kh & 1) * 2 + (kw & 1)) * Cin + c;
+    dw[i] = dw2[((int64_t)(kh >> 1) * 64 + r) * Cout + co];
+  }
+}
+
+// the T-tap, 64-channel stand-in geometry handed to the GEMM plan builders
+static void s2d_fake_desc(const rn_conv_desc* d, const S2dGeom& g, rn_conv_desc* f, ActView* v, TapSpec* taps) {
+  *f = *d;
+  f->H = g.H2; f->W = d->Wo; f->Cin = 64; f->stride = 1; f->pad = 0; f->k = 2;   // k*k = 4 >= T tap slots
+  v->C = 64; v->W = d->Wo; v->H = g.H2; v->N = d->N;
+  v->sw = (uint64_t)g.Cp * 2;
+  v->sh = (uint64_t)g.W2 * g.Cp * 2;
+  v->sn = (uint64_t)g.H2 * g.W2 * g.Cp * 2;
+  for (int t = 0; t < 4; ++t) { taps[t].map = 0; taps[t].dw = 0; taps[t].dh = (int8_t)t; taps[t].b = (int8_t)t; }
+}
+}  // namespace rn
+
+extern "C" int rn_stem_s2d_supported(const rn_conv_desc* d) {
+  S2dGeom g;
+  if (!s2d_geometry(d, &g) || d->dtype != RN_BF16) return 0;
+  if (g.T != 4) return 0;                        // the plan builders below carry exactly four tap slots (k = 7 or 8)
+  if (d->Cout % 8 || choose_block_n(d->Cout) == 0) return 0;
+  return 1;
+}
+
+extern "C" int rn_stem_s2d_geometry(const rn_conv_desc* d, int32_t* H2, int32_t* W2, int32_t* taps) {
+  S2dGeom g;
+  if (!s2d_geometry(d, &g)) return fail(RN_ERR_UNSUPPORTED, "stem_s2d: needs stride 2, Cin <= 4, k <= 8");
+  if (H2) *H2 = g.H2;
+  if (W2) *W2 = g.W2;
+  if (taps) *taps = g.T;
+  return RN_OK;
+}
+
+extern "C" int rn_stem_s2d_pack(const rn_conv_desc* d, const void* x, int32_t src_dtype, void* u, void* stream) {
+  S2dGeom g;
+  RN_REQUIRE(x && u, "stem_s2d_pack: NULL pointer");
+  if (!s2d_geometry(d, &g)) return fail(RN_ERR_UNSUPPORTED, "stem_s2d: needs stride 2, Cin <= 4, k <= 8");
+  if (src_dtype == RN_BF16) s2d_pack_launch((const __nv_bfloat16*)x, (__nv_bfloat16*)u, d, g, as_stream(stream));
+  else if (src_dtype == RN_F32) s2d_pack_launch((const float*)x, (__nv_bfloat16*)u, d, g, as_stream(stream));
+  else return fail(RN_ERR_INVALID, "stem_s2d_pack: bad src_dtype %d", src_dtype);
+  return check_launch("s2d_pack_kernel");
+}
+
+extern "C" int rn_stem_s2d_weights(const rn_conv_desc* d, const void* w_hwio_bf16, void* w2, void* stream) {
+  S2dGeom g;
+  RN_REQUIRE(w_hwio_bf16 && w2, "stem_s2d_weights: NULL pointer");
+  if (!s2d_geometry(d, &g)) return fail(RN_ERR_UNSUPPORTED, "stem_s2d: needs stride 2, Cin <= 4, k <= 8");
+  const int64_t total = (int64_t)g.T * 64 * d->Cout;
+  s2d_weights_kernel<<<grid_for(total, 256), 256, 0, as_stream(stream)>>>((const __nv_bfloat16*)w_hwio_bf16,
+                                                                         (__nv_bfloat16*)w2, d->k, d->Cin, d->Cout, g.T);
+  return check_launch("s2d_weights_kernel");
+}
+
+extern "C" int rn_stem_s2d_wgrad_unpack(const rn_conv_desc* d, const float* dw2, float* dw_hwio, void* stream) {
+  S2dGeom g;
+  RN_REQUIRE(dw2 && dw_hwio, "stem_s2d_wgrad_unpack: NULL pointer");
+  if (!s2d_geometry(d, &g)) return fail(RN_ERR_UNSUPPORTED, "stem_s2d: needs stride 2, Cin <= 4, k <= 8");
+  const int64_t total = (int64_t)d->k * d->k * d->Cin * d->Cout;
+  s2d_wgrad_unpack_kernel<<<grid_for(total, 256), 256, 0, as_stream(stream)>>>(dw2, dw_hwio, d->k, d->Cin, d->Cout);
+  return check_launch("s2d_wgrad_unpack_kernel");
+}
+
+extern "C" size_t rn_stem_s2d_scratch_bytes(const rn_conv_desc* d, int kind) {
+  S2dGeom g;
+  if (!rn_stem_s2d_supported(d) || kind != 2 || !s2d_geometry(d, &g)) return 0;
+  rn_conv_desc f; ActView v; TapSpec taps[4];
+  s2d_fake_desc(d, g, &f, &v, taps);
+  WgradShape w;
+  return wgrad_shape(&f, &w) ? w.scratch : 0;
+}
+
+extern "C" int rn_stem_s2d_plan_create(const rn_conv_desc* d, int kind, const void* u, const void* b, void* out,
+                                       void* scratch, size_t scratch_bytes, rn_convtc_plan** plan) {
+  RN_REQUIRE(d && u && b && out && plan, "stem_s2d_plan_create: NULL pointer");
+  RN_REQUIRE(kind == 0 || kind == 2, "stem_s2d_plan_create: kind must be 0 (fprop) or 2 (wgrad)");
+  if (!rn_stem_s2d_supported(d)) return fail(RN_ERR_UNSUPPORTED, "stem_s2d: shape not supported");
+  RN_REQUIRE((((uintptr_t)u | (uintptr_t)b | (uintptr_t)out) & 15) == 0, "stem_s2d: pointers must be 16-byte aligned");
+  S2dGeom g;
+  s2d_geometry(d, &g);
+  rn_conv_desc f; ActView v; TapSpec taps[4];
+  s2d_fake_desc(d, g, &f, &v, taps);
+  rn_convtc_plan* pl = new rn_convtc_plan();
+  memset(pl, 0, sizeof(*pl));
+  pl->kind = kind;
+  int rc;
+  if (kind == 0) {
+    cudaError_t e = cudaFuncSetAttribute(conv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024));
+    if (e != cudaSuccess) { delete pl; return fail(RN_ERR_CUDA, "stem_s2d: cudaFuncSetAttribute: %s", cudaGetErrorString(e)); }
+    const uint64_t ostr[3] = {(uint64_t)d->Cout * 2, (uint64_t)d->Wo * d->Cout * 2, (uint64_t)d->Ho * d->Wo * d->Cout * 2};
+    pl->nsub = 1;
+    rc = create_sub(&f, 0, u, b, out, d->Wo, d->Ho, ostr, taps, g.T, &pl->p[0], &pl->grid[0], &pl->smem_sub[0], &v, g.T);
+  } else {
+    rc = create_wgrad_plan(&f, u, b, out, scratch, scratch_bytes, pl, &v, taps);
+  }
+  if (rc) { delete pl; return rc; }
+  *plan = pl;
+  return RN_OK;
 }

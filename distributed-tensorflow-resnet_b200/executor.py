@@ -15,6 +15,7 @@ HBM layout
   per-BN saved batch mean / rstd, activations (NHWC) and their gradients: one buffer each.
 """
 import ctypes as C
+import os
 import math
 from collections import OrderedDict
 
@@ -321,6 +322,42 @@ class Executor:
         d1 = ConvDesc(d.N, d.Ho, d.Wo, kpad, d.Ho, d.Wo, d.Cout, 1, 1, 0, self.rn_dt)
         return bool(lib.rn_convtc_supported(C.byref(d1), 0))
 
+    def _stem_s2d(self, n):
+        """Stride-2 stem (ImageNet 7x7/2): space-to-depth packing + 4 vertical taps over 64 channels instead
+        of the unfolded matrix (rn_stem_s2d_* in include/rn_b200.h).  RN_STEM_IM2COL=1 forces the unfold path."""
+        d = self._desc(n)
+        return (self._is_stem(n) and not os.environ.get("RN_STEM_IM2COL")
+                and bool(lib.rn_stem_s2d_supported(C.byref(d))))
+
+    def _stem_s2d_setup(self, n):
+        if hasattr(n, "_s2d"):
+            return n._s2d
+        d = self._desc(n)
+        kv = n.vars["kernel"]
+        H2, W2, T = C.c_int32(), C.c_int32(), C.c_int32()
+        check(lib.rn_stem_s2d_geometry(C.byref(d), C.byref(H2), C.byref(W2), C.byref(T)), "rn_stem_s2d_geometry")
+        u = torch.zeros(d.N, H2.value, W2.value, 16, dtype=torch.bfloat16, device=self.dev)
+        wp = torch.zeros(T.value, 64, d.Cout, dtype=torch.bfloat16, device=self.dev)
+        fn = (lambda s, d=d, a=self._wptr(kv, "Wb"), b=ptr(wp):
+              check(lib.rn_stem_s2d_weights(C.byref(d), a, b, s), "rn_stem_s2d_weights"))
+        if not hasattr(self, "_relayout"):
+            self._relayout = []
+        self._relayout.append(fn)
+        fn(torch.cuda.current_stream().cuda_stream)
+        self._keep += [d, u, wp]
+        n._s2d = dict(d=d, u=u, wp=wp, taps=T.value)
+        return n._s2d
+
+    def _s2d_plan(self, d, kind, u, b, out):
+        nbytes = lib.rn_stem_s2d_scratch_bytes(C.byref(d), kind)
+        scratch = torch.zeros(max(nbytes, 16), dtype=torch.uint8, device=self.dev)
+        self._keep.append(scratch)
+        plan = C.c_void_p()
+        check(lib.rn_stem_s2d_plan_create(C.byref(d), kind, ptr(u), ptr(b), ptr(out), ptr(scratch), nbytes,
+                                          C.byref(plan)), "rn_stem_s2d_plan_create")
+        self._plans.append(plan)
+        return lambda s, p=plan: check(lib.rn_convtc_run(p, 0.0, s), "rn_convtc_run")
+
     def _stem_setup(self, n):
         if hasattr(n, "_stem"):
             return n._stem
@@ -358,6 +395,13 @@ class Executor:
         d = self._desc(n)
         self._keep.append(d)
         kv = n.vars["kernel"]
+        if self._stem_s2d(n):
+            st = self._stem_s2d_setup(n)
+            sdt = RN_BF16 if x.buf.dtype == torch.bfloat16 else RN_F32
+            pack = (lambda s, d=d, px=ptr(x.buf), pu=ptr(st["u"]), sdt=sdt:
+                    check(lib.rn_stem_s2d_pack(C.byref(d), px, sdt, pu, s), "rn_stem_s2d_pack"))
+            run = self._s2d_plan(d, 0, st["u"], st["wp"], y.buf)
+            return ("conv_fprop_tc:" + y.name, lambda s, pack=pack, run=run: (pack(s), run(s)))
         if self._is_stem(n):
             st = self._stem_setup(n)
             sdt = RN_BF16 if x.buf.dtype == torch.bfloat16 else RN_F32
@@ -581,7 +625,15 @@ class Executor:
                     self._emit(bwd, "conv_dgrad:" + y.name, lambda s, d=d, pdy=ptr(dy), w=w, pdx=ptr(dxb), beta=beta:
                                check(lib.rn_conv2d_dgrad(C.byref(d), pdy, w, pdx, beta, s), "rn_conv2d_dgrad"),
                                node=n, dy=dy, dx=dxb, beta=beta)
-            if self._is_stem(n) and lib.rn_convtc_supported(C.byref(self._stem_setup(n)["d1"]), 2):
+            if self._stem_s2d(n):
+                st = self._stem_s2d_setup(n)
+                tmp = torch.zeros(st["taps"] * 64, d.Cout, dtype=torch.float32, device=self.dev)
+                self._keep.append(tmp)
+                run = self._s2d_plan(d, 2, st["u"], dy, tmp)
+                up = (lambda s, d=d, a=ptr(tmp), b=self._wptr(kv, "G"):
+                      check(lib.rn_stem_s2d_wgrad_unpack(C.byref(d), a, b, s), "rn_stem_s2d_wgrad_unpack"))
+                self._emit(bwd, "conv_wgrad_tc:" + y.name, lambda s, run=run, up=up: (run(s), up(s)), node=n, dy=dy)
+            elif self._is_stem(n) and lib.rn_convtc_supported(C.byref(self._stem_setup(n)["d1"]), 2):
                 st = self._stem_setup(n)
                 tmp = torch.zeros(st["kpad"], d.Cout, dtype=torch.float32, device=self.dev)
                 self._keep.append(tmp)

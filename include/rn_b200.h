@@ -107,6 +107,24 @@ int rn_im2col(const void* x, void* cols, int32_t N, int32_t H, int32_t W, int32_
               int32_t k, int32_t stride, int32_t pad, int32_t Kpad, int32_t src_dtype, void* stream);
 int rn_stem_weights(const float* w_hwio, int32_t rows, int32_t Cout, int32_t Kpad, void* w_fprop, void* stream);
 
+/* Stride-2 stem without the unfolded matrix (the ImageNet 7x7/2 `conv2d_fixed_padding` over the image,
+ * resnet_model_official.py:310; Cin <= 4, k = 7 or 8).  The padded image is packed 2x2 -> channels once per
+ * step:  U[n, h2, w2, (dy*2+dx)*Cin + c] = x[n, 2*h2+dy-pad, 2*w2+dx-pad, c]  (bf16, 16 channels per pixel,
+ * dims from rn_stem_s2d_geometry: [N][H2][W2][16]).  A TMA view of U with a 32-byte W stride and 128-byte rows
+ * presents 4 neighbouring packed pixels as one 64-channel row, so the layer runs on the tensor-core kernels as
+ * `taps` (= 4) vertical taps over 64 channels:
+ *   kind 0: u, b = packed weights bf16 [taps][64][Cout] (rn_stem_s2d_weights from the bf16 HWIO kernel), out = y
+ *   kind 2: u, b = dy, out = packed gradient fp32 [taps][64][Cout]; rn_stem_s2d_wgrad_unpack scatters it back
+ *           to fp32 HWIO.  Plans run with rn_convtc_run and are freed with rn_convtc_plan_destroy. */
+int rn_stem_s2d_supported(const rn_conv_desc* d);
+int rn_stem_s2d_geometry(const rn_conv_desc* d, int32_t* H2, int32_t* W2, int32_t* taps);
+int rn_stem_s2d_pack(const rn_conv_desc* d, const void* x, int32_t src_dtype, void* u, void* stream);
+int rn_stem_s2d_weights(const rn_conv_desc* d, const void* w_hwio_bf16, void* w_packed, void* stream);
+int rn_stem_s2d_wgrad_unpack(const rn_conv_desc* d, const float* dw_packed, float* dw_hwio, void* stream);
+size_t rn_stem_s2d_scratch_bytes(const rn_conv_desc* d, int kind);
+int rn_stem_s2d_plan_create(const rn_conv_desc* d, int kind, const void* u, const void* b, void* out,
+                            void* scratch, size_t scratch_bytes, rn_convtc_plan** plan);
+
 /* ------------------------------------------------------------------------------------------
  * Batch normalisation + (leaky) ReLU (+ residual add)
  *   replaces tf.layers.batch_normalization(fused=True) + tf.nn.relu, resnet_model_official.py:41-50

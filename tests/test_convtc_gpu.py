@@ -188,3 +188,73 @@ def test_convtc_rejects_unsupported():
     assert lib.rn_convtc_supported(C.byref(d), 0) == 0
     d = ConvDesc(2, 8, 8, 64, 8, 8, 64, 3, 1, 1, 0)            # fp32 verification mode stays on CUDA cores
     assert lib.rn_convtc_supported(C.byref(d), 0) == 0
+
+
+STEM_S2D_CASES = [
+    # N, H, W, Cin, Cout, k, pad, (Ho, Wo), source dtype
+    (4, 224, 224, 3, 64, 7, 3, (112, 112), torch.float32),    # ImageNet stem (fixed_padding 3 + VALID)
+    (3, 64, 64, 3, 64, 7, 3, (32, 32), BF),
+    (2, 37, 41, 3, 64, 7, 2, (19, 21), torch.float32),         # odd sizes, TF-SAME style padding (2 before)
+    (2, 32, 32, 4, 32, 8, 3, (16, 16), BF),                    # k = 8, four channels: every packed slot used
+]
+
+
+@pytest.mark.parametrize("case", STEM_S2D_CASES)
+def test_stem_space_to_depth_fprop_and_wgrad(case):
+    """7x7/2 stem as space-to-depth + 4 vertical taps over a 64-channel overlapping-window view
+    (rn_stem_s2d_*), forward and weight gradient, against the oracle's direct convolution."""
+    N, H, W, Cin, Cout, k, pad, (Ho, Wo), sdt = case
+    g = torch.Generator().manual_seed(sum(case[:7]))
+    x = torch.randn(N, H, W, Cin, generator=g).to(BF)
+    w = (torch.randn(k, k, Cin, Cout, generator=g) / (k * k * Cin) ** 0.5).to(BF)
+    dy = torch.randn(N, Ho, Wo, Cout, generator=g).to(BF)
+    net = ro.Net(dtype=torch.float64, params={"w": w.double().numpy()})
+    xv = ro.Var(x.double())
+    yv = net.conv2d(xv, "w", k, Cin, Cout, 2, pad, (Ho, Wo), None, "y")
+    yv.grad = dy.double()
+    net.backward()
+    d = ConvDesc(N, H, W, Cin, Ho, Wo, Cout, k, 2, pad, RN_BF16)
+    assert lib.rn_stem_s2d_supported(C.byref(d)) == 1
+    H2, W2, T = C.c_int32(), C.c_int32(), C.c_int32()
+    check(lib.rn_stem_s2d_geometry(C.byref(d), C.byref(H2), C.byref(W2), C.byref(T)), "geometry")
+    assert (H2.value, W2.value, T.value) == (Ho + 3, Wo + 3, 4)
+    X = dev(x.to(sdt))
+    U = torch.full((N, H2.value, W2.value, 16), float("nan"), dtype=BF, device="cuda")
+    check(lib.rn_stem_s2d_pack(C.byref(d), ptr(X), 1 if sdt == BF else 0, ptr(U), stream()), "pack")
+    torch.cuda.synchronize()
+    # the packing itself is exact: U[n,h2,w2,(dy*2+dx)*Cin+c] = x_padded[n, 2h2+dy, 2w2+dx, c]
+    xp = torch.zeros(N, 2 * H2.value, 2 * W2.value, Cin, dtype=BF)
+    hh, ww = min(H, 2 * H2.value - pad), min(W, 2 * W2.value - pad)
+    xp[:, pad:pad + hh, pad:pad + ww] = x[:, :hh, :ww]
+    want_u = torch.zeros(N, H2.value, W2.value, 16, dtype=BF)
+    for dy_ in range(2):
+        for dx_ in range(2):
+            q = (dy_ * 2 + dx_) * Cin
+            want_u[..., q:q + Cin] = xp[:, dy_::2, dx_::2]
+    assert torch.equal(U.cpu(), want_u)
+    WB = dev(w)
+    WP = torch.full((4, 64, Cout), float("nan"), dtype=BF, device="cuda")
+    check(lib.rn_stem_s2d_weights(C.byref(d), ptr(WB), ptr(WP), stream()), "weights")
+    Y = torch.full((N, Ho, Wo, Cout), float("nan"), dtype=BF, device="cuda")
+    plan = C.c_void_p()
+    check(lib.rn_stem_s2d_plan_create(C.byref(d), 0, ptr(U), ptr(WP), ptr(Y), None, 0, C.byref(plan)), "plan fprop")
+    for _ in range(2):
+        check(lib.rn_convtc_run(plan, 0.0, stream()), "run")
+    torch.cuda.synchronize()
+    lib.rn_convtc_plan_destroy(plan)
+    assert torch.isfinite(Y.float()).all()
+    assert rel_err(Y.float(), yv.val) < 2e-2
+    # weight gradient
+    DY = dev(dy)
+    nb = lib.rn_stem_s2d_scratch_bytes(C.byref(d), 2)
+    scratch = torch.zeros(max(nb, 16), dtype=torch.uint8, device="cuda")
+    DWP = torch.full((4 * 64, Cout), float("nan"), dtype=torch.float32, device="cuda")
+    DW = torch.full((k, k, Cin, Cout), float("nan"), dtype=torch.float32, device="cuda")
+    check(lib.rn_stem_s2d_plan_create(C.byref(d), 2, ptr(U), ptr(DY), ptr(DWP), ptr(scratch), nb, C.byref(plan)), "plan wgrad")
+    for _ in range(2):
+        check(lib.rn_convtc_run(plan, 0.0, stream()), "run")
+    check(lib.rn_stem_s2d_wgrad_unpack(C.byref(d), ptr(DWP), ptr(DW), stream()), "unpack")
+    torch.cuda.synchronize()
+    lib.rn_convtc_plan_destroy(plan)
+    assert torch.isfinite(DW).all()
+    assert rel_err(DW, net.param_grads["w"]) < 1e-3             # fp32 accumulation of exact bf16 products
