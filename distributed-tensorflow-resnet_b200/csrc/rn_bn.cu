@@ -27,6 +27,7 @@ struct BnLayout {
   int RY;     // rows per CTA iteration
   int gridY;  // channel chunks
   int G;      // row CTAs
+  int il;     // 1: CTAs take row blocks round-robin (b, b+G, ...) instead of one contiguous range each
 };
 
 template <typename T>
@@ -49,6 +50,7 @@ static BnLayout bn_layout(int64_t M, int C, int waves, int max_cw = 32, int64_t 
   if (cap < 1) cap = 1;
   if (cap > BN_MAX_G) cap = BN_MAX_G;
   L.G = (int)(want < 1 ? 1 : (want > cap ? cap : want));
+  L.il = 0;
   return L;
 }
 
@@ -155,6 +157,18 @@ static int bn_apply_cw() {
   if (v < 0) { const char* e = getenv("RN_BN_APPLY_CW"); v = e ? atoi(e) : 16; if (v < 1 || v > 32) v = 16; }
   return v;
 }
+// CTAs per SM that are actually resident: the statistics kernel (<= 64 registers) fits 4 x 256 threads, the
+// backward reduction (80 registers) only 3 — a 4th "wave" would run as a tail after the first three finish.
+static int bn_reduce_waves(int dflt) {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("RN_BN_WAVES"); v = e ? atoi(e) : 0; if (v < 0 || v > 16) v = 0; }
+  return v ? v : dflt;
+}
+static int bn_interleave() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("RN_BN_IL"); v = e ? atoi(e) : 1; }
+  return v;
+}
 static int64_t bn_reduce_cta_bytes() {
   static int64_t v = -1;
   if (v < 0) { const char* e = getenv("RN_BN_CTA_KB"); v = (e ? atoi(e) : 64) * 1024; if (v < 4096) v = 65536; }
@@ -164,7 +178,7 @@ static int64_t bn_reduce_cta_bytes() {
 // ------------------------------------------------------------------------------------------
 // forward statistics (+ fused residual add)
 // ------------------------------------------------------------------------------------------
-template <typename T, bool ADD>
+template <typename T, bool ADD, int U>
 __global__ void __launch_bounds__(BN_THREADS)
 bn_stats_kernel(const T* __restrict__ x, const T* __restrict__ addend, T* __restrict__ sum_out, int64_t M, int C,
                 BnLayout L, float eps, float decay, int unbiased, float* __restrict__ mean_out,
@@ -182,55 +196,59 @@ bn_stats_kernel(const T* __restrict__ x, const T* __restrict__ addend, T* __rest
     const int64_t stride = L.RY;
     const int64_t col = (int64_t)cg * V;
     const int64_t rows_per_cta = ((M + gridDim.x - 1) / gridDim.x + L.RY - 1) / L.RY * L.RY;
-    const int64_t M_end = min(M, (int64_t)(blockIdx.x + 1) * rows_per_cta);
-    int64_t r = (int64_t)blockIdx.x * rows_per_cta + ty;
-    constexpr int U = ADD ? 1 : 2;   // independent 128-bit loads in flight per thread and stream
-    for (; r + (U - 1) * stride < M_end; r += U * stride) {
-      Vec<T> v[U], w[U];
+    const int64_t M_end = L.il ? M : min(M, (int64_t)(blockIdx.x + 1) * rows_per_cta);
+    int64_t r = (L.il ? (int64_t)blockIdx.x * (U * stride) : (int64_t)blockIdx.x * rows_per_cta) + ty;
+    const int64_t step = L.il ? (int64_t)gridDim.x * (U * stride) : (int64_t)U * stride;
+    // U = independent 128-bit loads in flight per thread and stream
+    for (; r < M_end; r += step) {
+      if (r + (U - 1) * stride < M_end) {
+        Vec<T> v[U], w[U];
 #pragma unroll
-      for (int u = 0; u < U; ++u) v[u].load(x + (r + u * stride) * C + col);
-      if (ADD) {
-#pragma unroll
-        for (int u = 0; u < U; ++u) w[u].load(addend + (r + u * stride) * C + col);
-      }
-#pragma unroll
-      for (int u = 0; u < U; ++u) {
-        float f[V];
-        v[u].unpack(f);
+        for (int u = 0; u < U; ++u) v[u].load(x + (r + u * stride) * C + col);
         if (ADD) {
-          float g[V];
-          w[u].unpack(g);
 #pragma unroll
-          for (int i = 0; i < V; ++i) f[i] += g[i];
-          Vec<T> o;
-          o.pack(f);
-          o.store(sum_out + (r + u * stride) * C + col);
-          o.unpack(f);  // statistics of the value as stored (matters in bf16 mode)
+          for (int u = 0; u < U; ++u) w[u].load(addend + (r + u * stride) * C + col);
         }
 #pragma unroll
-        for (int i = 0; i < V; ++i) { s[i] += f[i]; q[i] = fmaf(f[i], f[i], q[i]); }
-      }
-    }
-    for (; r < M_end; r += stride) {
-      Vec<T> v;
-      float f[V];
-      const int64_t off = r * C + col;
-      v.load(x + off);
-      v.unpack(f);
-      if (ADD) {
-        Vec<T> w;
-        float g[V];
-        w.load(addend + off);
-        w.unpack(g);
+        for (int u = 0; u < U; ++u) {
+          float f[V];
+          v[u].unpack(f);
+          if (ADD) {
+            float g[V];
+            w[u].unpack(g);
 #pragma unroll
-        for (int i = 0; i < V; ++i) f[i] += g[i];
-        Vec<T> o;
-        o.pack(f);
-        o.store(sum_out + off);
-        o.unpack(f);
-      }
+            for (int i = 0; i < V; ++i) f[i] += g[i];
+            Vec<T> o;
+            o.pack(f);
+            o.store(sum_out + (r + u * stride) * C + col);
+            o.unpack(f);  // statistics of the value as stored (matters in bf16 mode)
+          }
 #pragma unroll
-      for (int i = 0; i < V; ++i) { s[i] += f[i]; q[i] = fmaf(f[i], f[i], q[i]); }
+          for (int i = 0; i < V; ++i) { s[i] += f[i]; q[i] = fmaf(f[i], f[i], q[i]); }
+        }
+      } else {
+        for (int64_t rr = r; rr < M_end && rr < r + U * stride; rr += stride) {
+          Vec<T> v;
+          float f[V];
+          const int64_t off = rr * C + col;
+          v.load(x + off);
+          v.unpack(f);
+          if (ADD) {
+            Vec<T> w;
+            float g[V];
+            w.load(addend + off);
+            w.unpack(g);
+#pragma unroll
+            for (int i = 0; i < V; ++i) f[i] += g[i];
+            Vec<T> o;
+            o.pack(f);
+            o.store(sum_out + off);
+            o.unpack(f);
+          }
+#pragma unroll
+          for (int i = 0; i < V; ++i) { s[i] += f[i]; q[i] = fmaf(f[i], f[i], q[i]); }
+        }
+      }
     }
   }
   cta_reduce_cols<V>(s, q, tx, ty, L.CW, L.RY, active, smem);
@@ -356,48 +374,52 @@ bn_bwd_reduce_kernel(const T* __restrict__ dy, const T* __restrict__ x, int64_t 
     const int64_t stride = L.RY;
     const int64_t col = (int64_t)cg * V;
     const int64_t rows_per_cta = ((M + gridDim.x - 1) / gridDim.x + L.RY - 1) / L.RY * L.RY;
-    const int64_t M_end = min(M, (int64_t)(blockIdx.x + 1) * rows_per_cta);
-    int64_t r = (int64_t)blockIdx.x * rows_per_cta + ty;
-    for (; r + (U - 1) * stride < M_end; r += U * stride) {
-      Vec<T> vx[U], vg[U];
+    const int64_t M_end = L.il ? M : min(M, (int64_t)(blockIdx.x + 1) * rows_per_cta);
+    int64_t r = (L.il ? (int64_t)blockIdx.x * (U * stride) : (int64_t)blockIdx.x * rows_per_cta) + ty;
+    const int64_t step = L.il ? (int64_t)gridDim.x * (U * stride) : (int64_t)U * stride;
+    for (; r < M_end; r += step) {
+      if (r + (U - 1) * stride < M_end) {
+        Vec<T> vx[U], vg[U];
 #pragma unroll
-      for (int u = 0; u < U; ++u) {
-        if (CS) {
-          vx[u].load_stream(x + (r + u * stride) * C + col);
-          vg[u].load_stream(dy + (r + u * stride) * C + col);
-        } else {
-          vx[u].load(x + (r + u * stride) * C + col);
-          vg[u].load(dy + (r + u * stride) * C + col);
+        for (int u = 0; u < U; ++u) {
+          if (CS) {
+            vx[u].load_stream(x + (r + u * stride) * C + col);
+            vg[u].load_stream(dy + (r + u * stride) * C + col);
+          } else {
+            vx[u].load(x + (r + u * stride) * C + col);
+            vg[u].load(dy + (r + u * stride) * C + col);
+          }
         }
-      }
 #pragma unroll
-      for (int u = 0; u < U; ++u) {
-        float fx[V], fg[V];
-        vx[u].unpack(fx);
-        vg[u].unpack(fg);
+        for (int u = 0; u < U; ++u) {
+          float fx[V], fg[V];
+          vx[u].unpack(fx);
+          vg[u].unpack(fg);
 #pragma unroll
-        for (int i = 0; i < V; ++i) {
-          const float pre = fmaf(fx[i], a[i], b[i]);
-          const float g = pre < 0.f ? leak * fg[i] : fg[i];
-          sb[i] += g;
-          sg[i] = fmaf(g, (fx[i] - mu[i]) * rs[i], sg[i]);
+          for (int i = 0; i < V; ++i) {
+            const float pre = fmaf(fx[i], a[i], b[i]);
+            const float g = pre < 0.f ? leak * fg[i] : fg[i];
+            sb[i] += g;
+            sg[i] = fmaf(g, (fx[i] - mu[i]) * rs[i], sg[i]);
+          }
         }
-      }
-    }
-    for (; r < M_end; r += stride) {
-      const int64_t off = r * C + col;
-      Vec<T> vx, vg;
-      float fx[V], fg[V];
-      vx.load(x + off);
-      vg.load(dy + off);
-      vx.unpack(fx);
-      vg.unpack(fg);
+      } else {
+        for (int64_t rr = r; rr < M_end && rr < r + U * stride; rr += stride) {
+          const int64_t off = rr * C + col;
+          Vec<T> vx, vg;
+          float fx[V], fg[V];
+          vx.load(x + off);
+          vg.load(dy + off);
+          vx.unpack(fx);
+          vg.unpack(fg);
 #pragma unroll
-      for (int i = 0; i < V; ++i) {
-        const float pre = fmaf(fx[i], a[i], b[i]);
-        const float g = pre < 0.f ? leak * fg[i] : fg[i];
-        sb[i] += g;
-        sg[i] = fmaf(g, (fx[i] - mu[i]) * rs[i], sg[i]);
+          for (int i = 0; i < V; ++i) {
+            const float pre = fmaf(fx[i], a[i], b[i]);
+            const float g = pre < 0.f ? leak * fg[i] : fg[i];
+            sb[i] += g;
+            sg[i] = fmaf(g, (fx[i] - mu[i]) * rs[i], sg[i]);
+          }
+        }
       }
     }
   }
@@ -540,7 +562,8 @@ static int bn_stats_launch(const void* x, const void* addend, void* sum_out, int
                            size_t scratch_bytes, cudaStream_t st) {
   int rc = check_bn_args<T>(M, C);
   if (rc) return rc;
-  BnLayout L = bn_layout<T>(M, C, 4, bn_reduce_cw(), bn_reduce_cta_bytes());
+  BnLayout L = bn_layout<T>(M, C, bn_reduce_waves(4), bn_reduce_cw(), bn_reduce_cta_bytes());
+  L.il = bn_interleave();
   const size_t need = 256 + (size_t)L.gridY * L.G * 2 * L.CW * Vec<T>::N * sizeof(float);
   if (scratch == nullptr || scratch_bytes < need)
     return fail(RN_ERR_SCRATCH, "bn_stats: scratch %zu < %zu bytes", scratch_bytes, need);
@@ -548,14 +571,28 @@ static int bn_stats_launch(const void* x, const void* addend, void* sum_out, int
   float* partials = (float*)((char*)scratch + 256);
   dim3 grid(L.G, L.gridY);
   size_t smem = (size_t)L.RY * L.CW * 2 * Vec<T>::N * sizeof(float);
+  static int u_plain = -1, u_add = -1;
+  if (u_plain < 0) { const char* e = getenv("RN_BN_STATS_U"); u_plain = e ? atoi(e) : 2; }
+  if (u_add < 0) { const char* e = getenv("RN_BN_STATS_ADD_U"); u_add = e ? atoi(e) : 4; }
+#define RN_LAUNCH_STATS(ADDV, UU)                                                                              \
+  bn_stats_kernel<T, ADDV, UU><<<grid, BN_THREADS, smem, st>>>((const T*)x, (const T*)addend, (T*)sum_out, M, C, L,  \
+                                                               eps, decay, unbiased, mean, rstd, mm, mv, counters, partials)
   if (addend != nullptr) {
     RN_REQUIRE(sum_out != nullptr, "bn_stats: addend given but sum_out is NULL");
-    bn_stats_kernel<T, true><<<grid, BN_THREADS, smem, st>>>((const T*)x, (const T*)addend, (T*)sum_out, M, C, L, eps,
-                                                             decay, unbiased, mean, rstd, mm, mv, counters, partials);
+    switch (u_add) {
+      case 2: RN_LAUNCH_STATS(true, 2); break;
+      case 4: RN_LAUNCH_STATS(true, 4); break;
+      default: RN_LAUNCH_STATS(true, 1); break;
+    }
   } else {
-    bn_stats_kernel<T, false><<<grid, BN_THREADS, smem, st>>>((const T*)x, nullptr, nullptr, M, C, L, eps, decay,
-                                                              unbiased, mean, rstd, mm, mv, counters, partials);
+    switch (u_plain) {
+      case 1: RN_LAUNCH_STATS(false, 1); break;
+      case 4: RN_LAUNCH_STATS(false, 4); break;
+      case 8: RN_LAUNCH_STATS(false, 8); break;
+      default: RN_LAUNCH_STATS(false, 2); break;
+    }
   }
+#undef RN_LAUNCH_STATS
   return check_launch("bn_stats_kernel");
 }
 
@@ -608,7 +645,8 @@ static int bn_bwd_reduce_launch(const void* dy, const void* x, int64_t M, int C,
                                 void* scratch, size_t scratch_bytes, cudaStream_t st) {
   int rc = check_bn_args<T>(M, C);
   if (rc) return rc;
-  BnLayout L = bn_layout<T>(M, C, 4, bn_reduce_cw(), bn_reduce_cta_bytes());
+  BnLayout L = bn_layout<T>(M, C, bn_reduce_waves(3), bn_reduce_cw(), bn_reduce_cta_bytes());
+  L.il = bn_interleave();
   const size_t need = 256 + (size_t)L.gridY * L.G * 2 * L.CW * Vec<T>::N * sizeof(float);
   if (scratch == nullptr || scratch_bytes < need)
     return fail(RN_ERR_SCRATCH, "bn_bwd_reduce: scratch %zu < %zu bytes", scratch_bytes, need);
@@ -757,10 +795,10 @@ static int bn_stats_noalloc_launch(const void* x, const void* addend, void* sum_
   dim3 grid(L.G, L.gridY);
   const size_t smem = (size_t)L.RY * L.CW * 2 * Vec<T>::N * sizeof(float);
   if (addend != nullptr)
-    bn_stats_kernel<T, true><<<grid, BN_THREADS, smem, st>>>((const T*)x, (const T*)addend, (T*)sum_out, M, C, L, eps,
+    bn_stats_kernel<T, true, 1><<<grid, BN_THREADS, smem, st>>>((const T*)x, (const T*)addend, (T*)sum_out, M, C, L, eps,
                                                              decay, unbiased, mean, rstd, mm, mv, counters, partials);
   else
-    bn_stats_kernel<T, false><<<grid, BN_THREADS, smem, st>>>((const T*)x, nullptr, nullptr, M, C, L, eps, decay,
+    bn_stats_kernel<T, false, 2><<<grid, BN_THREADS, smem, st>>>((const T*)x, nullptr, nullptr, M, C, L, eps, decay,
                                                               unbiased, mean, rstd, mm, mv, counters, partials);
   return check_launch("bn_stats_kernel (static scratch)");
 }
