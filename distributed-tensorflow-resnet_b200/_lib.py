@@ -78,7 +78,8 @@ SIGNATURES = {
     "rn_avgpool_bwd": (C.c_int, [vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, i32, i32, f32, vp]),
     "rn_dense_scratch_bytes": (sz, [i32, i32, i32]),
     "rn_dense_fwd": (C.c_int, [vp, vp, vp, vp, i32, i32, i32, vp, sz, vp]),
-    "rn_dense_bwd": (C.c_int, [vp, vp, vp, vp, vp, vp, i32, i32, i32, vp]),
+    "rn_dense_bwd_scratch_bytes": (sz, [i32, i32, i32]),
+    "rn_dense_bwd": (C.c_int, [vp, vp, vp, vp, vp, vp, i32, i32, i32, vp, sz, vp]),
     "rn_softmax_xent": (C.c_int, [vp, vp, i32, i32, vp, vp, vp, vp]),
     "rn_optimizer_scratch_bytes": (sz, [i64]),
     "rn_sgd_momentum_fused": (C.c_int, [vp, vp, vp, vp, i64, vp, vp, f32, f32, f32, i32, vp, vp, sz, vp]),

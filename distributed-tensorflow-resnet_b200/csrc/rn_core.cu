@@ -64,7 +64,7 @@ __global__ void pad_channels_kernel(const S* __restrict__ src, D* __restrict__ d
 using namespace rn;
 
 extern "C" const char* rn_last_error(void) { return g_err; }
-extern "C" int rn_abi_version(void) { return 2; }
+extern "C" int rn_abi_version(void) { return 3; }
 extern "C" uint64_t rn_launch_count(void) { return g_launches.load(); }
 
 extern "C" int rn_cast(const void* src, void* dst, int64_t n, int32_t sd, int32_t dd, void* stream) {

@@ -18,11 +18,12 @@ sgemm_strided_kernel(const float* __restrict__ A, int64_t a_rs, int64_t a_cs, co
   const int m0 = blockIdx.y * 64, n0 = blockIdx.x * 64;
   float acc[4][4] = {};
   for (int k0 = 0; k0 < K; k0 += 16) {
+    // consecutive threads follow whichever index is contiguous in memory (either operand may be transposed)
     for (int e = tid; e < 64 * 16; e += 256) {
-      const int kk = e % 16, mm = e / 16;
+      const int kk = a_cs == 1 ? e % 16 : e / 64, mm = a_cs == 1 ? e / 16 : e % 64;
       const int gm = m0 + mm, gk = k0 + kk;
       As[kk][mm] = (gm < M && gk < K) ? A[gm * a_rs + gk * a_cs] : 0.f;
-      const int nn = e % 64, k2 = e / 64;
+      const int nn = b_cs == 1 ? e % 64 : e / 16, k2 = b_cs == 1 ? e / 64 : e % 16;
       const int gn = n0 + nn, gk2 = k0 + k2;
       Bs[k2][nn] = (gn < N && gk2 < K) ? Bm[gk2 * b_rs + gn * b_cs] : 0.f;
     }
@@ -63,11 +64,12 @@ sgemm_splitk_kernel(const float* __restrict__ A, int64_t a_rs, int64_t a_cs, con
   const int ke = min(K, kb + kslice);
   float acc[4][4] = {};
   for (int k0 = kb; k0 < ke; k0 += 16) {
+    // consecutive threads follow whichever index is contiguous in memory (either operand may be transposed)
     for (int e = tid; e < 64 * 16; e += 256) {
-      const int kk = e % 16, mm = e / 16;
+      const int kk = a_cs == 1 ? e % 16 : e / 64, mm = a_cs == 1 ? e / 16 : e % 64;
       const int gm = m0 + mm, gk = k0 + kk;
       As[kk][mm] = (gm < M && gk < ke) ? A[gm * a_rs + gk * a_cs] : 0.f;
-      const int nn = e % 64, k2 = e / 64;
+      const int nn = b_cs == 1 ? e % 64 : e / 16, k2 = b_cs == 1 ? e / 64 : e % 16;
       const int gn = n0 + nn, gk2 = k0 + k2;
       Bs[k2][nn] = (gn < N && gk2 < ke) ? Bm[gk2 * b_rs + gn * b_cs] : 0.f;
     }
@@ -122,14 +124,21 @@ static int sgemm(const float* A, int64_t a_rs, int64_t a_cs, const float* B, int
 // ------------------------------------------------------------------------------------------
 // softmax + cross-entropy + precision, one CTA, one warp per row, fixed-order final sum.
 // ------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(1024)
+// One warp per row, 8 rows per CTA; per-row loss / hit flags go to a small static device buffer and the last
+// CTA (atomic ticket) sums them in a fixed order.  The buffer is shared by all calls on a device: two
+// rn_softmax_xent calls running CONCURRENTLY on different streams would race on it (calls on one stream,
+// or ordered by events, are fine).
+constexpr int XENT_MAX_ROWS = 4096;
+__device__ float g_xent_rows[2 * XENT_MAX_ROWS];
+__device__ unsigned g_xent_ticket;
+
+__global__ void __launch_bounds__(256)
 softmax_xent_kernel(const float* __restrict__ logits, const float* __restrict__ onehot, int B, int K,
                     float* __restrict__ probs, float* __restrict__ dlogits, float* __restrict__ out) {
-  extern __shared__ float rows[];  // [B] loss, [B] correct
-  float* correct = rows + B;
-  const int warp = threadIdx.x / 32, lane = threadIdx.x % 32, nwarps = blockDim.x / 32;
+  const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
   const float invB = 1.f / (float)B;
-  for (int r = warp; r < B; r += nwarps) {
+  const int r = blockIdx.x * 8 + warp;
+  if (r < B) {
     const float* z = logits + (int64_t)r * K;
     const float* y = onehot + (int64_t)r * K;
     float mx = -INFINITY;
@@ -168,14 +177,29 @@ softmax_xent_kernel(const float* __restrict__ logits, const float* __restrict__ 
       if (dlogits) dlogits[(int64_t)r * K + j] = (p * ysum - yv) * invB;
     }
     loss = warp_sum(loss);
-    if (lane == 0) { rows[r] = loss; correct[r] = (amx == aymx) ? 1.f : 0.f; }
+    if (lane == 0) { g_xent_rows[r] = loss; g_xent_rows[XENT_MAX_ROWS + r] = (amx == aymx) ? 1.f : 0.f; }
   }
+  __shared__ bool is_last;
   __syncthreads();
   if (threadIdx.x == 0) {
-    double s = 0.0, c = 0.0;
-    for (int r = 0; r < B; ++r) { s += rows[r]; c += correct[r]; }
+    __threadfence();
+    is_last = atomicAdd(&g_xent_ticket, 1u) == gridDim.x - 1;
+    __threadfence();
+  }
+  __syncthreads();
+  if (!is_last || warp != 0) return;
+  // fixed order: lane l sums rows l, l+32, ...; then a shuffle tree
+  double s = 0.0, c = 0.0;
+  for (int i = lane; i < B; i += 32) { s += (double)__ldcg(&g_xent_rows[i]); c += (double)__ldcg(&g_xent_rows[XENT_MAX_ROWS + i]); }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    s += __shfl_xor_sync(0xffffffffu, s, o);
+    c += __shfl_xor_sync(0xffffffffu, c, o);
+  }
+  if (lane == 0) {
     out[0] = (float)(s / B);
     out[1] = (float)(c / B);
+    g_xent_ticket = 0;
   }
 }
 
@@ -273,8 +297,16 @@ extern "C" int rn_dense_fwd(const float* x, const float* w, const float* b, floa
   return check_launch("splitk_bias_reduce_kernel");
 }
 
+extern "C" size_t rn_dense_bwd_scratch_bytes(int32_t B, int32_t D, int32_t K) {
+  const int tiles = ((D + 63) / 64) * ((B + 63) / 64);
+  int splits = (2 * RN_NUM_SMS + tiles - 1) / tiles;
+  if (splits > K / 64) splits = K / 64;
+  if (splits < 2) return 0;
+  return (size_t)splits * B * D * sizeof(float);
+}
+
 extern "C" int rn_dense_bwd(const float* x, const float* w, const float* dy, float* dw, float* db, float* dx, int32_t B,
-                            int32_t D, int32_t K, void* stream) {
+                            int32_t D, int32_t K, void* scratch, size_t scratch_bytes, void* stream) {
   RN_REQUIRE(x && w && dy && B > 0 && D > 0 && K > 0, "dense_bwd: bad arguments");
   cudaStream_t st = as_stream(stream);
   int rc;
@@ -287,9 +319,24 @@ extern "C" int rn_dense_bwd(const float* x, const float* w, const float* dy, flo
     rc = check_launch("colsum_kernel");
     if (rc) return rc;
   }
-  if (dx) {  // dx[B,D] = dy [B,K] . w^T [K,D]
-    rc = sgemm(dy, K, 1, w, 1, K, nullptr, dx, B, D, K, st);
-    if (rc) return rc;
+  if (dx) {  // dx[B,D] = dy [B,K] . w^T [K,D]; with scratch: deterministic split-K over the classes
+    const size_t need = rn_dense_bwd_scratch_bytes(B, D, K);
+    if (need == 0 || scratch == nullptr || scratch_bytes < need) {
+      rc = sgemm(dy, K, 1, w, 1, K, nullptr, dx, B, D, K, st);
+      if (rc) return rc;
+    } else {
+      const int splits = (int)(need / ((size_t)B * D * sizeof(float)));
+      int kslice = (K + splits - 1) / splits;
+      kslice = (kslice + 15) / 16 * 16;
+      dim3 grid((D + 63) / 64, (B + 63) / 64, splits);
+      sgemm_splitk_kernel<<<grid, 256, 0, st>>>(dy, K, 1, w, 1, K, (float*)scratch, B, D, K, kslice);
+      rc = check_launch("sgemm_splitk_kernel");
+      if (rc) return rc;
+      splitk_bias_reduce_kernel<<<grid_for((int64_t)B * D, 256), 256, 0, st>>>((const float*)scratch, nullptr, dx, B, D,
+                                                                             splits);
+      rc = check_launch("splitk_bias_reduce_kernel");
+      if (rc) return rc;
+    }
   }
   return RN_OK;
 }
@@ -298,8 +345,7 @@ extern "C" int rn_softmax_xent(const float* logits, const float* onehot, int32_t
                                float* dlogits, float* out_scalars, void* stream) {
   RN_REQUIRE(logits && onehot && out_scalars && B > 0 && K > 0, "softmax_xent: bad arguments");
   RN_REQUIRE(B <= 4096, "softmax_xent: batch %d > 4096 rows per call", B);
-  softmax_xent_kernel<<<1, 1024, 2 * B * sizeof(float), as_stream(stream)>>>(logits, onehot, B, K, probs, dlogits,
-                                                                             out_scalars);
+  softmax_xent_kernel<<<(B + 7) / 8, 256, 0, as_stream(stream)>>>(logits, onehot, B, K, probs, dlogits, out_scalars);
   return check_launch("softmax_xent_kernel");
 }
 

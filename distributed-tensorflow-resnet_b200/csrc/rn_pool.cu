@@ -76,14 +76,12 @@ __global__ void maxpool_fwd_vec_kernel(const T* __restrict__ x, T* __restrict__ 
                                        int H, int W, int C, int Ho, int Wo, int pad) {
   constexpr int V = Vec<T>::N;
   const int CV = C / V;
-  const int64_t total = (int64_t)N * Ho * Wo * CV;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-    const int cg = (int)(i % CV);
-    int64_t p = i / CV;
-    const int wo = (int)(p % Wo);
-    p /= Wo;
-    const int ho = (int)(p % Ho);
-    const int n = (int)(p / Ho);
+  // one output row (n, ho) per CTA iteration; threads walk (wo, channel group): no 64-bit divisions per element
+  const int rows = N * Ho, per_row = Wo * CV;
+  for (int row = blockIdx.x; row < rows; row += gridDim.x)
+  for (int e = threadIdx.x; e < per_row; e += blockDim.x) {
+    const int cg = e % CV, wo = e / CV;
+    const int ho = row % Ho, n = row / Ho;
     float best[V];
     int bi[V];
     bool any = false;
@@ -109,8 +107,11 @@ __global__ void maxpool_fwd_vec_kernel(const T* __restrict__ x, T* __restrict__ 
     o.pack(best);
     const int64_t ob = (((int64_t)n * Ho + ho) * Wo + wo) * C + (int64_t)cg * V;
     o.store(y + ob);
+    uint8_t am[V];
 #pragma unroll
-    for (int j = 0; j < V; ++j) argmax[ob + j] = (uint8_t)bi[j];
+    for (int j = 0; j < V; ++j) am[j] = (uint8_t)bi[j];
+    if (V == 8) *reinterpret_cast<uint2*>(argmax + ob) = *reinterpret_cast<const uint2*>(am);
+    else        *reinterpret_cast<uint32_t*>(argmax + ob) = *reinterpret_cast<const uint32_t*>(am);
   }
 }
 
@@ -119,39 +120,49 @@ __global__ void maxpool_bwd_vec_kernel(const T* __restrict__ dy, const uint8_t* 
                                        int W, int C, int Ho, int Wo, int pad, float beta) {
   constexpr int V = Vec<T>::N;
   const int CV = C / V;
-  const int64_t total = (int64_t)N * H * W * CV;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-    const int cg = (int)(i % CV);
-    int64_t p = i / CV;
-    const int w = (int)(p % W);
-    p /= W;
-    const int h = (int)(p % H);
-    const int n = (int)(p / H);
+  const int rows = N * H, per_row = W * CV;
+  for (int row = blockIdx.x; row < rows; row += gridDim.x)
+  for (int e = threadIdx.x; e < per_row; e += blockDim.x) {
+    const int cg = e % CV, w = e / CV;
+    const int h = row % H, n = row / H;
     float acc[V];
 #pragma unroll
     for (int j = 0; j < V; ++j) acc[j] = 0.f;
-    for (int r = 0; r < 3; ++r) {
-      const int t = h + pad - r;
-      if (t < 0 || (t & 1)) continue;
-      const int ho = t >> 1;
-      if (ho >= Ho) continue;
-      for (int s = 0; s < 3; ++s) {
-        const int u = w + pad - s;
-        if (u < 0 || (u & 1)) continue;
-        const int wo = u >> 1;
-        if (wo >= Wo) continue;
-        const int64_t ob = (((int64_t)n * Ho + ho) * Wo + wo) * C + (int64_t)cg * V;
-        Vec<T> g;
-        float f[V];
-        g.load(dy + ob);
-        g.unpack(f);
-        uint8_t am[V];
-        if (V == 8) *reinterpret_cast<uint2*>(am) = *reinterpret_cast<const uint2*>(argmax + ob);
-        else        *reinterpret_cast<uint32_t*>(am) = *reinterpret_cast<const uint32_t*>(argmax + ob);
-        const uint8_t me = (uint8_t)(r * 3 + s);
+    // a pixel lies in at most 2 x 2 windows of a 3x3 / stride-2 pooling: window rows r = r0, r0 + 2 with
+    // r0 = (h + pad) & 1.  All (up to four) loads are issued before any of them is consumed.
+    const int r0 = (h + pad) & 1, s0 = (w + pad) & 1;
+    Vec<T> g[4];
+    uint2 amv[4];
+    bool ok[4];
 #pragma unroll
-        for (int j = 0; j < V; ++j)
-          if (am[j] == me) acc[j] += f[j];
+    for (int a = 0; a < 2; ++a) {
+      const int r = r0 + 2 * a;
+      const int ho = (h + pad - r) >> 1;
+      const bool okh = r < 3 && h + pad - r >= 0 && ho < Ho;
+#pragma unroll
+      for (int b = 0; b < 2; ++b) {
+        const int sft = s0 + 2 * b;
+        const int wo = (w + pad - sft) >> 1;
+        const int q = a * 2 + b;
+        ok[q] = okh && sft < 3 && w + pad - sft >= 0 && wo < Wo;
+        if (ok[q]) {
+          const int64_t ob = (((int64_t)n * Ho + ho) * Wo + wo) * C + (int64_t)cg * V;
+          g[q].load(dy + ob);
+          if (V == 8) amv[q] = *reinterpret_cast<const uint2*>(argmax + ob);
+          else        amv[q] = make_uint2(*reinterpret_cast<const uint32_t*>(argmax + ob), 0u);
+        }
+      }
+    }
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      if (!ok[q]) continue;
+      float f[V];
+      g[q].unpack(f);
+      const uint32_t me = (uint32_t)((r0 + 2 * (q >> 1)) * 3 + s0 + 2 * (q & 1));
+#pragma unroll
+      for (int j = 0; j < V; ++j) {
+        const uint32_t word = j < 4 ? amv[q].x : amv[q].y;
+        if (((word >> (8 * (j & 3))) & 0xffu) == me) acc[j] += f[j];
       }
     }
     const int64_t xb = (((int64_t)n * H + h) * W + w) * C + (int64_t)cg * V;
@@ -214,6 +225,55 @@ __global__ void avgpool_bwd_kernel(const TO* __restrict__ dy, TI* dx, int N, int
         acc += to_f<TO>(dy[(((int64_t)n * Ho + ho) * Wo + wo) * Cout + cb + c]);
     acc *= inv;
     dx[i] = from_f<TI>(beta != 0.f ? to_f<TI>(dx[i]) + acc : acc);
+  }
+}
+
+// 8 channels per thread (bf16 dx, C / Cout / cb multiples of 8): one 128-bit store per pixel x channel group
+template <typename TO>
+__global__ void avgpool_bwd_vec_kernel(const TO* __restrict__ dy, __nv_bfloat16* dx, int N, int H, int W, int C, int k,
+                                       int s, int Ho, int Wo, int Cout, int cb, float beta) {
+  const int CV = C / 8;
+  const int64_t total = (int64_t)N * H * W * CV;
+  const float inv = 1.f / (float)(k * k);
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int cg = (int)(i % CV);
+    int64_t p = i / CV;
+    const int w = (int)(p % W);
+    p /= W;
+    const int h = (int)(p % H);
+    const int n = (int)(p / H);
+    float acc[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+    const int ho_lo = h - k + 1 <= 0 ? 0 : (h - k + 1 + s - 1) / s;
+    const int wo_lo = w - k + 1 <= 0 ? 0 : (w - k + 1 + s - 1) / s;
+    for (int ho = ho_lo; ho < Ho && ho * s <= h; ++ho)
+      for (int wo = wo_lo; wo < Wo && wo * s <= w; ++wo) {
+        const TO* src = dy + (((int64_t)n * Ho + ho) * Wo + wo) * Cout + cb + cg * 8;
+        float f[8];
+        if (sizeof(TO) == 4) {
+          const float4 a = *reinterpret_cast<const float4*>(src), b = *reinterpret_cast<const float4*>(src + 4);
+          f[0] = a.x; f[1] = a.y; f[2] = a.z; f[3] = a.w; f[4] = b.x; f[5] = b.y; f[6] = b.z; f[7] = b.w;
+        } else {
+          Vec<__nv_bfloat16> v;
+          v.load(reinterpret_cast<const __nv_bfloat16*>(src));
+          v.unpack(f);
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] += f[j];
+      }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] *= inv;
+    Vec<__nv_bfloat16> o;
+    if (beta != 0.f) {
+      float f[8];
+      o.load(dx + i * 8);
+      o.unpack(f);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[j] += f[j];
+    }
+    o.pack(acc);
+    o.store(dx + i * 8);
   }
 }
 
@@ -293,6 +353,20 @@ extern "C" int rn_avgpool_bwd(const void* dy, void* dx, int32_t N, int32_t H, in
   const int Ho = (H - k) / s + 1, Wo = (W - k) / s + 1;
   const int g = grid_for((int64_t)N * H * W * C, 256);
   cudaStream_t st = as_stream(stream);
+  const bool vec = idt == RN_BF16 && C % 8 == 0 && Cout % 8 == 0 && cb % 8 == 0 &&
+                   (((uintptr_t)dy | (uintptr_t)dx) & 15) == 0;
+  if (vec) {
+    const int gv = grid_for((int64_t)N * H * W * (C / 8), 256);
+    if (odt == RN_F32)
+      avgpool_bwd_vec_kernel<float><<<gv, 256, 0, st>>>((const float*)dy, (__nv_bfloat16*)dx, N, H, W, C, k, s, Ho, Wo,
+                                                        Cout, cb, beta);
+    else if (odt == RN_BF16)
+      avgpool_bwd_vec_kernel<__nv_bfloat16><<<gv, 256, 0, st>>>((const __nv_bfloat16*)dy, (__nv_bfloat16*)dx, N, H, W, C,
+                                                                k, s, Ho, Wo, Cout, cb, beta);
+    else
+      return fail(RN_ERR_INVALID, "avgpool_bwd: bad dtypes %d -> %d", idt, odt);
+    return check_launch("avgpool_bwd_vec_kernel");
+  }
   if (idt == RN_F32 && odt == RN_F32)
     avgpool_bwd_kernel<float, float><<<g, 256, 0, st>>>((const float*)dy, (float*)dx, N, H, W, C, k, s, Ho, Wo, Cout, cb, beta);
   else if (idt == RN_BF16 && odt == RN_F32)

@@ -561,11 +561,21 @@ class Executor:
                 if beta != 0.0:
                     raise NotImplementedError("dense input gradient fan-in")
                 dxp = ptr(dxb)
+            # input gradient (and the cheap bias gradient) on the main stream; the weight gradient is only needed
+            # by the update, so it is forked to the side stream together with the conv weight gradients
+            nbb = lib.rn_dense_bwd_scratch_bytes(B, D, K)
+            bsc = torch.zeros(max(nbb, 16), dtype=torch.uint8, device=self.dev)
+            self._keep.append(bsc)
             self._emit(bwd, "dense_bwd:" + y.name,
-                       lambda s, args=(ptr(x.buf), self._wptr(n.vars["kernel"]), ptr(dy), self._wptr(n.vars["kernel"], "G"),
-                                       self._wptr(n.vars["bias"], "G"), dxp, B, D, K):
+                       lambda s, args=(ptr(x.buf), self._wptr(n.vars["kernel"]), ptr(dy), None,
+                                       self._wptr(n.vars["bias"], "G"), dxp, B, D, K, ptr(bsc), nbb):
                        check(lib.rn_dense_bwd(*args, s), "rn_dense_bwd"),
                        node=n, dy=dy, dx=dxb if x.requires_grad else None, beta=0.0)
+            self._emit(bwd, "dense_wgrad:" + y.name,
+                       lambda s, args=(ptr(x.buf), self._wptr(n.vars["kernel"]), ptr(dy), self._wptr(n.vars["kernel"], "G"),
+                                       None, None, B, D, K, None, 0):
+                       check(lib.rn_dense_bwd(*args, s), "rn_dense_bwd"),
+                       node=n, dy=dy)
         elif n.op == "avgpool":
             x = n.inputs[0]
             if not x.requires_grad:
@@ -726,7 +736,7 @@ class Executor:
         pending = []
         for name, fn in lst:
             m = self.meta.get(name)
-            if name.startswith("conv_wgrad"):
+            if name.startswith(("conv_wgrad", "dense_wgrad")):
                 ev = torch.cuda.Event()
                 ev.record(cur)
                 side.wait_event(ev)

@@ -201,9 +201,14 @@ int rn_avgpool_bwd(const void* dy, void* dx, int32_t N, int32_t H, int32_t W, in
 size_t rn_dense_scratch_bytes(int32_t B, int32_t D, int32_t K);
 int rn_dense_fwd(const float* x, const float* w, const float* b, float* y, int32_t B, int32_t D, int32_t K,
                  void* scratch, size_t scratch_bytes, void* stream);
+/* dw / db / dx may each be NULL (skipped).  `scratch` (optional, rn_dense_bwd_scratch_bytes) enables the
+ * deterministic split-K pass for dx, whose reduction runs over the K classes. */
+size_t rn_dense_bwd_scratch_bytes(int32_t B, int32_t D, int32_t K);
 int rn_dense_bwd(const float* x, const float* w, const float* dy, float* dw, float* db, float* dx,
-                 int32_t B, int32_t D, int32_t K, void* stream);
-/* out_scalars[0] = mean xent, out_scalars[1] = precision. probs / dlogits may be NULL. */
+                 int32_t B, int32_t D, int32_t K, void* scratch, size_t scratch_bytes, void* stream);
+/* out_scalars[0] = mean xent, out_scalars[1] = precision. probs / dlogits may be NULL.  B <= 4096.
+ * Per-row results pass through a static device buffer: calls must not run CONCURRENTLY on two streams of
+ * one device (same-stream or event-ordered calls are fine). */
 int rn_softmax_xent(const float* logits, const float* onehot, int32_t B, int32_t K, float* probs, float* dlogits,
                     float* out_scalars, void* stream);
 

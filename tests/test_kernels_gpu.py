@@ -286,9 +286,15 @@ def test_dense_and_softmax_xent(cfg):
     prec = (probs.argmax(1) == lab).double().mean().item()
     assert abs(S[1].item() - prec) < 1e-6
     DW, DB, DX = torch.empty(D, K, device="cuda"), torch.empty(K, device="cuda"), torch.empty(B, D, device="cuda")
-    check(lib.rn_dense_bwd(ptr(X), ptr(Wd), ptr(DL), ptr(DW), ptr(DB), ptr(DX), B, D, K, stream()), "dense bwd")
+    check(lib.rn_dense_bwd(ptr(X), ptr(Wd), ptr(DL), ptr(DW), ptr(DB), ptr(DX), B, D, K, None, 0, stream()), "dense bwd")
     assert rel_err(DW, net.param_grads["w"]) < 1e-4 and rel_err(DB, net.param_grads["b"]) < 1e-4
     assert rel_err(DX, xv.grad) < 1e-4
+    nbb = lib.rn_dense_bwd_scratch_bytes(B, D, K)
+    if nbb:      # deterministic split-K path for dx (reduction over the classes)
+        sc = torch.empty(nbb, dtype=torch.uint8, device="cuda")
+        DX2 = torch.full((B, D), float("nan"), device="cuda")
+        check(lib.rn_dense_bwd(ptr(X), ptr(Wd), ptr(DL), None, None, ptr(DX2), B, D, K, ptr(sc), nbb, stream()), "dense bwd split-K")
+        assert rel_err(DX2, xv.grad) < 1e-4
 
 
 # ------------------------------------------------------------------------------------------ optimizer

@@ -173,10 +173,12 @@ class Verifier:
             x = node.inputs[0]
             w = _d(ex.var_view(node.vars["kernel"].name))
             x2 = _d(x.buf).reshape(x.shape[0], -1)
-            self.check(name + "/dw", ex.var_view(node.vars["kernel"].name, "G"), x2.t() @ dy, 1e-4)
             self.check(name + "/db", ex.var_view(node.vars["bias"].name, "G"), dy.sum(0), 1e-4)
             if dx_buf is not None:
                 self.check(name + "/dx", dx_buf, (dy @ w.t()).reshape(x.shape), 1e-4)
+        elif fam == "dense_wgrad":
+            x2 = _d(node.inputs[0].buf).reshape(node.inputs[0].shape[0], -1)
+            self.check(name + "/dw", ex.var_view(node.vars["kernel"].name, "G"), x2.t() @ dy, 1e-4)
         elif fam == "avgpool_bwd":
             a = node.attrs
             x, y = node.inputs[0], node.outputs[0]
