@@ -450,14 +450,45 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_wgrad_tc_kernel(const __gr
   if (warp == 1) tmem_dealloc(tmem_base, p.tmem_cols);
 }
 
-__global__ void wgrad_reduce_kernel(const float* __restrict__ part, float* __restrict__ out, int64_t n4, int splits) {
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
-    float4 s = reinterpret_cast<const float4*>(part)[i];
-    for (int z = 1; z < splits; ++z) {
-      const float4 t = reinterpret_cast<const float4*>(part)[(int64_t)z * n4 + i];
-      s.x += t.x; s.y += t.y; s.z += t.z; s.w += t.w;
+// Sum of the split-K partials in a fixed order.  A CTA covers 256/S consecutive float4 outputs with S thread
+// slices; slice s adds partials s, s+S, ... (independent loads, several in flight), then the slices are combined
+// in slice order through shared memory.  With one thread per output the 100+ dependent-latency loads of a
+// 148-way split took longer than the GEMM itself.
+__global__ void __launch_bounds__(256)
+wgrad_reduce_kernel(const float* __restrict__ part, float* __restrict__ out, int64_t n4, int splits, int S) {
+  __shared__ float4 sh[256];
+  const int per = 256 / S;
+  const int o = threadIdx.x % per, slice = threadIdx.x / per;
+  const int64_t i = (int64_t)blockIdx.x * per + o;
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (i < n4) {
+    const float4* p = reinterpret_cast<const float4*>(part) + i;
+    int z = slice;
+    for (; z + 3 * S < splits; z += 4 * S) {
+      const float4 a = __ldcg(p + (int64_t)z * n4), b = __ldcg(p + (int64_t)(z + S) * n4);
+      const float4 c = __ldcg(p + (int64_t)(z + 2 * S) * n4), d = __ldcg(p + (int64_t)(z + 3 * S) * n4);
+      acc.x += a.x; acc.y += a.y; acc.z += a.z; acc.w += a.w;
+      acc.x += b.x; acc.y += b.y; acc.z += b.z; acc.w += b.w;
+      acc.x += c.x; acc.y += c.y; acc.z += c.z; acc.w += c.w;
+      acc.x += d.x; acc.y += d.y; acc.z += d.z; acc.w += d.w;
     }
-    reinterpret_cast<float4*>(out)[i] = s;
+    for (; z < splits; z += S) {
+      const float4 a = __ldcg(p + (int64_t)z * n4);
+      acc.x += a.x; acc.y += a.y; acc.z += a.z; acc.w += a.w;
+    }
+  }
+  if (S == 1) {
+    if (i < n4) reinterpret_cast<float4*>(out)[i] = acc;
+    return;
+  }
+  sh[threadIdx.x] = acc;
+  __syncthreads();
+  if (slice == 0 && i < n4) {
+    for (int q = 1; q < S; ++q) {
+      const float4 t = sh[q * per + o];
+      acc.x += t.x; acc.y += t.y; acc.z += t.z; acc.w += t.w;
+    }
+    reinterpret_cast<float4*>(out)[i] = acc;
   }
 }
 
@@ -998,7 +1029,10 @@ extern "C" int rn_convtc_run(rn_convtc_plan* plan, float beta, void* stream) {
     if (rc) return rc;
     if (plan->w.splits > 1) {
       const int64_t n4 = plan->dw_elems / 4;
-      wgrad_reduce_kernel<<<grid_for(n4, 256), 256, 0, st>>>(plan->w.partial, plan->dw, n4, plan->w.splits);
+      const int sp = plan->w.splits;
+      const int S = sp <= 4 ? 1 : (sp <= 16 ? 4 : (sp <= 48 ? 16 : 32));
+      const int64_t blocks = (n4 + 256 / S - 1) / (256 / S);
+      wgrad_reduce_kernel<<<(unsigned)blocks, 256, 0, st>>>(plan->w.partial, plan->dw, n4, sp, S);
       rc = check_launch("wgrad_reduce_kernel");
     }
     return rc;
