@@ -185,6 +185,8 @@ bn_stats_kernel(const T* __restrict__ x, const T* __restrict__ addend, T* __rest
                 float* __restrict__ rstd_out, float* moving_mean, float* moving_var, unsigned* counters,
                 float* partials) {
   constexpr int V = Vec<T>::N;
+  pdl_trigger();
+  pdl_wait();
   extern __shared__ float smem[];
   const int tx = threadIdx.x % L.CW, ty = threadIdx.x / L.CW;
   const int cg = blockIdx.y * L.CW + tx;
@@ -301,6 +303,8 @@ bn_apply_kernel(const T* __restrict__ x, T* __restrict__ y, int64_t M, int C, Bn
                 const float* __restrict__ gamma, const float* __restrict__ beta, const float* __restrict__ mean,
                 const float* __restrict__ rstd, int stats_are_moving, float eps, float leak) {
   constexpr int V = Vec<T>::N;
+  pdl_trigger();
+  pdl_wait();
   const int tx = threadIdx.x % L.CW, ty = threadIdx.x / L.CW;
   const int cg = blockIdx.y * L.CW + tx;
   if (!(ty < L.RY && cg < L.CV)) return;
@@ -355,6 +359,8 @@ bn_bwd_reduce_kernel(const T* __restrict__ dy, const T* __restrict__ x, int64_t 
                      const float* __restrict__ rstd, float leak, float* __restrict__ dgamma, float* __restrict__ dbeta,
                      unsigned* counters, float* partials) {
   constexpr int V = Vec<T>::N;
+  pdl_trigger();
+  pdl_wait();
   extern __shared__ float smem[];
   const int tx = threadIdx.x % L.CW, ty = threadIdx.x / L.CW;
   const int cg = blockIdx.y * L.CW + tx;
@@ -465,6 +471,8 @@ bn_bwd_apply_kernel(const T* __restrict__ dy, const T* __restrict__ x, T* dx, co
                     const float* __restrict__ mean, const float* __restrict__ rstd, const float* __restrict__ dgamma,
                     const float* __restrict__ dbeta, float leak) {
   constexpr int V = Vec<T>::N;
+  pdl_trigger();
+  pdl_wait();
   const int tx = threadIdx.x % L.CW, ty = threadIdx.x / L.CW;
   const int cg = blockIdx.y * L.CW + tx;
   if (!(ty < L.RY && cg < L.CV)) return;
@@ -575,8 +583,8 @@ static int bn_stats_launch(const void* x, const void* addend, void* sum_out, int
   if (u_plain < 0) { const char* e = getenv("RN_BN_STATS_U"); u_plain = e ? atoi(e) : 2; }
   if (u_add < 0) { const char* e = getenv("RN_BN_STATS_ADD_U"); u_add = e ? atoi(e) : 4; }
 #define RN_LAUNCH_STATS(ADDV, UU)                                                                              \
-  bn_stats_kernel<T, ADDV, UU><<<grid, BN_THREADS, smem, st>>>((const T*)x, (const T*)addend, (T*)sum_out, M, C, L,  \
-                                                               eps, decay, unbiased, mean, rstd, mm, mv, counters, partials)
+  launch_pdl(bn_stats_kernel<T, ADDV, UU>, grid, BN_THREADS, smem, st, (const T*)x, (const T*)addend, (T*)sum_out, M, \
+             C, L, eps, decay, unbiased, mean, rstd, mm, mv, counters, partials)
   if (addend != nullptr) {
     RN_REQUIRE(sum_out != nullptr, "bn_stats: addend given but sum_out is NULL");
     switch (u_add) {
@@ -622,8 +630,8 @@ static int bn_apply_launch(const void* x, void* y, int64_t M, int C, const float
   int rc = check_bn_args<T>(M, C);
   if (rc) return rc;
   BnLayout L = bn_layout<T>(M, C, 8, bn_apply_cw(), 16384);
-  bn_apply_kernel<T><<<dim3(L.G, L.gridY), BN_THREADS, 0, st>>>((const T*)x, (T*)y, M, C, L, gamma, beta, mean, rstd,
-                                                               moving, eps, leak);
+  launch_pdl(bn_apply_kernel<T>, dim3(L.G, L.gridY), BN_THREADS, 0, st, (const T*)x, (T*)y, M, C, L, gamma, beta, mean,
+             rstd, moving, eps, leak);
   return check_launch("bn_apply_kernel");
 }
 
@@ -654,9 +662,8 @@ static int bn_bwd_reduce_launch(const void* dy, const void* x, int64_t M, int C,
   static int variant = -1;
   if (variant < 0) { const char* e = getenv("RN_BN_VARIANT"); variant = e ? atoi(e) : 0; }
 #define RN_LAUNCH_REDUCE(UU, CC)                                                                              \
-  bn_bwd_reduce_kernel<T, UU, CC><<<dim3(L.G, L.gridY), BN_THREADS, smem, st>>>(                             \
-      (const T*)dy, (const T*)x, M, C, L, gamma, beta, mean, rstd, leak, dgamma, dbeta, (unsigned*)scratch, \
-      (float*)((char*)scratch + 256))
+  launch_pdl(bn_bwd_reduce_kernel<T, UU, CC>, dim3(L.G, L.gridY), BN_THREADS, smem, st, (const T*)dy, (const T*)x, M,   \
+             C, L, gamma, beta, mean, rstd, leak, dgamma, dbeta, (unsigned*)scratch, (float*)((char*)scratch + 256))
   // streaming (evict-first) loads measured +13 % on tensors that exceed L2; smaller tensors keep the
   // default policy so that the dx pass that follows finds x and dy in L2
   const bool big = (size_t)M * C * sizeof(T) > ((size_t)48 << 20);
@@ -698,11 +705,11 @@ static int bn_bwd_apply_launch(const void* dy, const void* x, void* dx, const vo
   BnLayout L = bn_layout<T>(M, C, 8, bn_apply_cw(), 16384);
   dim3 grid(L.G, L.gridY);
   if (addend)
-    bn_bwd_apply_kernel<T, true><<<grid, BN_THREADS, 0, st>>>((const T*)dy, (const T*)x, (T*)dx, (const T*)addend, M, C,
-                                                             L, gamma, beta, mean, rstd, dgamma, dbeta, leak);
+    launch_pdl(bn_bwd_apply_kernel<T, true>, grid, BN_THREADS, 0, st, (const T*)dy, (const T*)x, (T*)dx,
+               (const T*)addend, M, C, L, gamma, beta, mean, rstd, dgamma, dbeta, leak);
   else
-    bn_bwd_apply_kernel<T, false><<<grid, BN_THREADS, 0, st>>>((const T*)dy, (const T*)x, (T*)dx, nullptr, M, C, L,
-                                                              gamma, beta, mean, rstd, dgamma, dbeta, leak);
+    launch_pdl(bn_bwd_apply_kernel<T, false>, grid, BN_THREADS, 0, st, (const T*)dy, (const T*)x, (T*)dx,
+               (const T*)nullptr, M, C, L, gamma, beta, mean, rstd, dgamma, dbeta, leak);
   return check_launch("bn_bwd_apply_kernel");
 }
 

@@ -85,6 +85,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const __grid_con
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  // everything above (barriers, TMEM, descriptor prefetch) overlapped the previous kernel's tail
+  pdl_trigger();
+  pdl_wait();
 
   // work item = (group of acc_m consecutive pixel tiles, column tile); the acc_m tiles share each B tile
   const int m_tiles = p.tiles_w * p.tiles_h * p.tiles_n;
@@ -219,6 +222,26 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const __grid_con
           uint8_t* sb = epi_buf + buf * 16384;
           const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) +
                                  (uint32_t)((acc * p.acc_m + j) * p.block_n + g * p.gw);
+          if (p.gw == 64) {
+            // both 32-column loads in flight before the single wait; then 8 x (4 cvt + one 128-bit store)
+            uint32_t va[32], vb[32];
+            tmem_ld_32x32(taddr, va);
+            tmem_ld_32x32(taddr + 32, vb);
+            tmem_ld_wait();
+            const uint32_t rbase = (uint32_t)row * 128u;
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+              uint32_t pk[4];
+#pragma unroll
+              for (int i = 0; i < 4; ++i) {
+                const uint32_t lo = c < 4 ? va[8 * c + 2 * i] : vb[8 * (c - 4) + 2 * i];
+                const uint32_t hi = c < 4 ? va[8 * c + 2 * i + 1] : vb[8 * (c - 4) + 2 * i + 1];
+                __nv_bfloat162 h = __floats2bfloat162_rn(__uint_as_float(lo), __uint_as_float(hi));
+                pk[i] = *reinterpret_cast<uint32_t*>(&h);
+              }
+              *reinterpret_cast<uint4*>(sb + swizzle_offset(rbase + 16u * c, 128)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+            }
+          } else
           for (int c0 = 0; c0 < p.gw; c0 += 16) {
             uint32_t v[16];
             tmem_ld_32x16(taddr + c0, v);
@@ -320,6 +343,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_wgrad_tc_kernel(const __gr
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_trigger();
+  pdl_wait();
   const int total = p.row_groups * p.n_tiles * p.splits;
   const int rb_per_cta = p.blocksA * p.acc;
   const int nb = p.block_n / p.bwB;
@@ -457,6 +482,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_wgrad_tc_kernel(const __gr
 __global__ void __launch_bounds__(256)
 wgrad_reduce_kernel(const float* __restrict__ part, float* __restrict__ out, int64_t n4, int splits, int S) {
   __shared__ float4 sh[256];
+  pdl_trigger();
+  pdl_wait();
   const int per = 256 / S;
   const int o = threadIdx.x % per, slice = threadIdx.x / per;
   const int64_t i = (int64_t)blockIdx.x * per + o;
@@ -1024,7 +1051,7 @@ extern "C" int rn_convtc_run(rn_convtc_plan* plan, float beta, void* stream) {
   cudaStream_t st = as_stream(stream);
   if (plan->kind == 2) {
     if (beta != 0.f) return fail(RN_ERR_UNSUPPORTED, "convtc_run: wgrad overwrites its output (beta must be 0)");
-    conv_wgrad_tc_kernel<<<plan->wgrid, TC_THREADS, plan->wsmem, st>>>(plan->w);
+    launch_pdl(conv_wgrad_tc_kernel, plan->wgrid, TC_THREADS, plan->wsmem, st, plan->w);
     int rc = check_launch("conv_wgrad_tc_kernel");
     if (rc) return rc;
     if (plan->w.splits > 1) {
@@ -1032,7 +1059,7 @@ extern "C" int rn_convtc_run(rn_convtc_plan* plan, float beta, void* stream) {
       const int sp = plan->w.splits;
       const int S = sp <= 4 ? 1 : (sp <= 16 ? 4 : (sp <= 48 ? 16 : 32));
       const int64_t blocks = (n4 + 256 / S - 1) / (256 / S);
-      wgrad_reduce_kernel<<<(unsigned)blocks, 256, 0, st>>>(plan->w.partial, plan->dw, n4, sp, S);
+      launch_pdl(wgrad_reduce_kernel, (unsigned)blocks, 256, 0, st, (const float*)plan->w.partial, plan->dw, n4, sp, S);
       rc = check_launch("wgrad_reduce_kernel");
     }
     return rc;
@@ -1044,7 +1071,7 @@ extern "C" int rn_convtc_run(rn_convtc_plan* plan, float beta, void* stream) {
   for (int i = 0; i < plan->nsub; ++i) {
     TcConvParams p = plan->p[i];
     p.accumulate = beta != 0.f ? 1 : 0;
-    conv_tc_kernel<<<plan->grid[i], TC_THREADS, plan->smem_sub[i], st>>>(p);
+    launch_pdl(conv_tc_kernel, plan->grid[i], TC_THREADS, plan->smem_sub[i], st, p);
     int rc = check_launch("conv_tc_kernel");
     if (rc) return rc;
   }
