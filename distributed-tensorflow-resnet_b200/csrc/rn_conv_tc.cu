@@ -213,6 +213,15 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const __grid_con
         const int h0 = (mt % p.tiles_h) * p.BH;
         const int n0 = (mt / p.tiles_h) * p.BN;
         for (int g = 0; g < groups; ++g) {
+          const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) +
+                                 (uint32_t)((acc * p.acc_m + j) * p.block_n + g * p.gw);
+          // 64-column groups: both 32-column TMEM loads are issued before waiting for the staging buffer, so
+          // their latency overlaps the barrier; then one wait, 8 x (4 cvt + one 128-bit shared store)
+          uint32_t va[32], vb[32];
+          if (p.gw == 64) {
+            tmem_ld_32x32(taddr, va);
+            tmem_ld_32x32(taddr + 32, vb);
+          }
           // the TMA store that last read this staging buffer must have finished reading it
           if (warp == 2) {
             if (elect_one()) tma_store_wait_read<1>();
@@ -220,13 +229,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const __grid_con
           }
           asm volatile("bar.sync 1, 128;" ::: "memory");
           uint8_t* sb = epi_buf + buf * 16384;
-          const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) +
-                                 (uint32_t)((acc * p.acc_m + j) * p.block_n + g * p.gw);
           if (p.gw == 64) {
-            // both 32-column loads in flight before the single wait; then 8 x (4 cvt + one 128-bit store)
-            uint32_t va[32], vb[32];
-            tmem_ld_32x32(taddr, va);
-            tmem_ld_32x32(taddr + 32, vb);
             tmem_ld_wait();
             const uint32_t rbase = (uint32_t)row * 128u;
 #pragma unroll
