@@ -608,6 +608,67 @@ static int bn_stats_launch(const void* x, const void* addend, void* sum_out, int
 
 using namespace rn;
 
+// Finalisation of statistics whose per-CTA sums were produced by a convolution epilogue
+// (rn_convtc_plan_create_fused): partials[nparts][C][2] = (sum, sum of squares) per channel.
+// A CTA handles 32 channels with 8 thread slices over the partial rows (fixed order, fp64).
+namespace rn {
+__global__ void __launch_bounds__(256)
+bn_finalize_kernel(const float* __restrict__ partials, int nparts, int64_t M, int C, float eps, float decay, int unbiased,
+                   float* __restrict__ mean_out, float* __restrict__ rstd_out, float* moving_mean, float* moving_var) {
+  pdl_trigger();
+  pdl_wait();
+  __shared__ double sh[2][8][32];
+  const int cl = threadIdx.x % 32, slice = threadIdx.x / 32;
+  const int c = blockIdx.x * 32 + cl;
+  double s = 0.0, q = 0.0;
+  if (c < C) {
+    const float2* p = reinterpret_cast<const float2*>(partials) + c;
+    int z = slice;
+    for (; z + 24 < nparts; z += 32) {
+      const float2 a = __ldcg(p + (size_t)z * C), b = __ldcg(p + (size_t)(z + 8) * C);
+      const float2 d = __ldcg(p + (size_t)(z + 16) * C), e = __ldcg(p + (size_t)(z + 24) * C);
+      s += (double)a.x; q += (double)a.y;
+      s += (double)b.x; q += (double)b.y;
+      s += (double)d.x; q += (double)d.y;
+      s += (double)e.x; q += (double)e.y;
+    }
+    for (; z < nparts; z += 8) {
+      const float2 a = __ldcg(p + (size_t)z * C);
+      s += (double)a.x; q += (double)a.y;
+    }
+  }
+  sh[0][slice][cl] = s;
+  sh[1][slice][cl] = q;
+  __syncthreads();
+  if (slice == 0 && c < C) {
+    double S = 0.0, Q = 0.0;
+    for (int j = 0; j < 8; ++j) { S += sh[0][j][cl]; Q += sh[1][j][cl]; }
+    const double mean = S / (double)M;
+    double var = Q / (double)M - mean * mean;
+    if (var < 0.0) var = 0.0;
+    mean_out[c] = (float)mean;
+    rstd_out[c] = (float)(1.0 / sqrt(var + (double)eps));
+    if (moving_mean != nullptr) {
+      const double mv = unbiased ? var * ((double)M / (double)(M > 1 ? M - 1 : 1)) : var;
+      const float om = 1.f - decay;
+      moving_mean[c] -= (moving_mean[c] - (float)mean) * om;
+      moving_var[c] -= (moving_var[c] - (float)mv) * om;
+    }
+  }
+}
+}  // namespace rn
+
+extern "C" int rn_bn_finalize(const float* partials, int32_t nparts, int64_t M, int32_t C, float eps, float decay,
+                              int32_t unbiased, float* mean, float* rstd, float* moving_mean, float* moving_var,
+                              void* stream) {
+  RN_REQUIRE(partials && mean && rstd && nparts > 0 && M > 0 && C > 0, "bn_finalize: bad arguments");
+  RN_REQUIRE((moving_mean == nullptr) == (moving_var == nullptr), "bn_finalize: moving_mean/var must both be set or NULL");
+  RN_REQUIRE(((uintptr_t)partials & 7) == 0, "bn_finalize: partials must be 8-byte aligned");
+  launch_pdl(rn::bn_finalize_kernel, (C + 31) / 32, 256, 0, rn::as_stream(stream), partials, (int)nparts, M, (int)C, eps,
+             decay, (int)unbiased, mean, rstd, moving_mean, moving_var);
+  return rn::check_launch("bn_finalize_kernel");
+}
+
 extern "C" size_t rn_bn_scratch_bytes(int64_t M, int32_t C) { return bn_scratch_bytes(M, C); }
 
 extern "C" int rn_bn_stats_fwd(const void* x, const void* addend, void* sum_out, int64_t M, int32_t C, int32_t dtype,

@@ -51,36 +51,56 @@ struct TcConvParams {
   int b_mn;                       // 1: B operand is MN-major (fprop reads the HWIO weights as they are)
   int b_boxes;                    // MN-major: TMA boxes per stage (block_n / gw), each kc rows of gw channels
   uint32_t b_box_bytes;
+  // fused epilogue (fprop, 64-channel store groups only)
+  int fuse_stats;                 // per-channel sum / sum of squares of the STORED bf16 output -> stat_partials[CTA][ncols][2]
+  int fuse_add;                   // OUT = bf16(bf16(result) + residual): the residual tile arrives through r_map (warp 6)
+  int ncols_total;
+  float* stat_partials;
+  CUtensorMap r_map;
   int8_t tap_map[TC_MAX_TAPS], tap_dw[TC_MAX_TAPS], tap_dh[TC_MAX_TAPS], tap_b[TC_MAX_TAPS];
 };
 
-__global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const __grid_constant__ TcConvParams p) {
+constexpr int TC_RES_SLOTS = 3;            // residual tiles in flight (16 KB each)
+constexpr int TC_THREADS_RES = TC_THREADS + 32;
+
+__global__ void __launch_bounds__(TC_THREADS_RES, 1) conv_tc_kernel(const __grid_constant__ TcConvParams p) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base_u32 = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* smem = smem_raw + (base_u32 - smem_u32(smem_raw));
   const uint32_t stage_bytes = (uint32_t)p.acc_m * p.a_bytes + p.b_bytes;
   const int row_bytes_out = p.gw * 2;
   uint8_t* epi_buf = smem + (size_t)p.stages * stage_bytes;                  // 2 x 16 KB
-  uint64_t* bars = reinterpret_cast<uint64_t*>(epi_buf + 2 * 16384);
+  uint8_t* res_buf = epi_buf + 2 * 16384;                                     // TC_RES_SLOTS x 16 KB (fused add)
+  uint8_t* after_res = res_buf + (p.fuse_add ? TC_RES_SLOTS * 16384 : 0);
+  float* cs = reinterpret_cast<float*>(after_res);                            // 2 x [4 warps][32 column pairs][4] (fused stats)
+  float* pacc = cs + 1024;                                                    // [ncols_total][2]
+  uint8_t* after_stats = after_res + (p.fuse_stats ? 4096 + (size_t)p.ncols_total * 8 : 0);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(after_stats);
   uint64_t* full = bars;                  // [stages]
   uint64_t* empty = bars + p.stages;      // [stages]
   uint64_t* tfull = bars + 2 * p.stages;  // [2]
   uint64_t* tempty = tfull + 2;           // [2]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+  uint64_t* rfull = tempty + 2;           // [TC_RES_SLOTS]
+  uint64_t* rempty = rfull + TC_RES_SLOTS;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(rempty + TC_RES_SLOTS);
 
   const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
   if (warp == 0 && lane == 0) {
     for (int i = 0; i < p.stages; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
     for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], 4); }
+    for (int i = 0; i < TC_RES_SLOTS; ++i) { mbar_init(&rfull[i], 1); mbar_init(&rempty[i], 4); }
     fence_barrier_init();
     tma_prefetch_desc(&p.a_map[0]);
     tma_prefetch_desc(&p.b_map);
     tma_prefetch_desc(&p.o_map);
+    if (p.fuse_add) tma_prefetch_desc(&p.r_map);
   }
   if (warp == 1) {
     tmem_alloc(tmem_slot, p.tmem_cols);
     tmem_relinquish();
   }
+  if (p.fuse_stats && warp >= 2 && warp < 6)
+    for (int i = threadIdx.x - 64; i < 2 * p.ncols_total; i += 128) pacc[i] = 0.f;
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -191,14 +211,30 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const __grid_con
       }
       if (++acc == p.tstages) { acc = 0; acc_phase ^= 1; }
     }
-  } else {
+  } else if (warp < 6) {
     // ===================== epilogue (warps 2..5) =====================
     const int quad = warp & 3;                      // TMEM lane quadrant this warp may access
     const int row = quad * 32 + lane;
+    const int te = threadIdx.x - 64;                // 0..127
+    const int box_rows = p.BW * p.BH * p.BN;
     int acc = 0;
     uint32_t acc_phase = 0;
     int buf = 0;
+    int rslot = 0;
+    uint32_t rphase = 0;
+    int csb = 0, pend_col = -1;                     // fused statistics: cs buffer in use, column base awaiting its combine
     const int groups = p.block_n / p.gw;
+    // Fused statistics, second half: add the four row-quarter sums of the PREVIOUS store group (written to
+    // cs[csb ^ 1] before that group's second barrier) into the CTA's running per-channel totals.  Thread te owns
+    // (column te & 63, statistic te >> 6); fixed quarter order.
+    auto combine = [&](int col0, int which) {
+      const float* c = cs + which * 512;
+      const int col = te & 63, st = te >> 6;
+      float v = 0.f;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) v += c[(q * 32 + (col >> 1)) * 4 + st * 2 + (col & 1)];
+      pacc[(col0 + col) * 2 + st] += v;
+    };
     for (int t = blockIdx.x; t < total; t += gridDim.x) {
       const int nt = t % p.n_tiles;
       const int mg = t / p.n_tiles;
@@ -230,8 +266,11 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const __grid_con
           asm volatile("bar.sync 1, 128;" ::: "memory");
           uint8_t* sb = epi_buf + buf * 16384;
           if (p.gw == 64) {
+            if (p.fuse_stats && pend_col >= 0) combine(pend_col, csb ^ 1);
             tmem_ld_wait();
             const uint32_t rbase = (uint32_t)row * 128u;
+            const uint8_t* rb = res_buf + rslot * 16384;
+            if (p.fuse_add) mbar_wait(&rfull[rslot], rphase);
 #pragma unroll
             for (int c = 0; c < 8; ++c) {
               uint32_t pk[4];
@@ -242,7 +281,42 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const __grid_con
                 __nv_bfloat162 h = __floats2bfloat162_rn(__uint_as_float(lo), __uint_as_float(hi));
                 pk[i] = *reinterpret_cast<uint32_t*>(&h);
               }
-              *reinterpret_cast<uint4*>(sb + swizzle_offset(rbase + 16u * c, 128)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+              const uint32_t so = swizzle_offset(rbase + 16u * c, 128);
+              if (p.fuse_add) {
+                // z = bf16(bf16(conv) + residual): the same two roundings as a stored conv output followed by the add
+                const uint4 rv = *reinterpret_cast<const uint4*>(rb + so);
+                const uint32_t rw[4] = {rv.x, rv.y, rv.z, rv.w};
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                  const float z0 = __uint_as_float(pk[i] << 16) + __uint_as_float(rw[i] << 16);
+                  const float z1 = __uint_as_float(pk[i] & 0xffff0000u) + __uint_as_float(rw[i] & 0xffff0000u);
+                  __nv_bfloat162 h = __floats2bfloat162_rn(z0, z1);
+                  pk[i] = *reinterpret_cast<uint32_t*>(&h);
+                }
+              }
+              *reinterpret_cast<uint4*>(sb + so) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+            }
+            if (p.fuse_add) {
+              __syncwarp();
+              if (lane == 0) mbar_arrive(&rempty[rslot]);
+              if (++rslot == TC_RES_SLOTS) { rslot = 0; rphase ^= 1; }
+            }
+            if (p.fuse_stats) {
+              // first half: this warp re-reads the 32 rows it just wrote, one column pair per lane (a row is the
+              // 32 lanes' 128 bytes: conflict-free under the swizzle), and sums value / value^2 of the STORED bf16
+              __syncwarp();
+              float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
+              const int nrow = min(32, box_rows - quad * 32);      // rows past the pixel box hold stale data
+              for (int r = 0; r < nrow; ++r) {
+                const uint32_t w = *reinterpret_cast<const uint32_t*>(
+                    sb + swizzle_offset((uint32_t)(quad * 32 + r) * 128u + (uint32_t)lane * 4u, 128));
+                const float f0 = __uint_as_float(w << 16), f1 = __uint_as_float(w & 0xffff0000u);
+                s0 += f0; s1 += f1;
+                q0 = fmaf(f0, f0, q0); q1 = fmaf(f1, f1, q1);
+              }
+              *reinterpret_cast<float4*>(cs + csb * 512 + (quad * 32 + lane) * 4) = make_float4(s0, s1, q0, q1);
+              pend_col = nt * p.block_n + g * 64;
+              csb ^= 1;
             }
           } else
           for (int c0 = 0; c0 < p.gw; c0 += 16) {
@@ -280,9 +354,45 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_tc_kernel(const __grid_con
       if (lane == 0) mbar_arrive(&tempty[acc]);
       if (++acc == p.tstages) { acc = 0; acc_phase ^= 1; }
     }
+    if (p.fuse_stats) {
+      // last group's quarter sums, then this CTA's totals go to its row of the partial table (the finalize
+      // kernel sums the <= 148 rows in fp64 in a fixed order)
+      if (pend_col >= 0) combine(pend_col, csb ^ 1);      // ordered after the last group's second barrier
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      float* dst = p.stat_partials + (size_t)blockIdx.x * 2 * p.ncols_total;
+      for (int i = te; i < 2 * p.ncols_total; i += 128) dst[i] = pacc[i];
+    }
     if (warp == 2) {
       if (elect_one()) tma_store_wait<0>();
       __syncwarp();
+    }
+  } else {
+    // ===================== residual-tile producer (warp 6; only launched with the fused add) =====================
+    const uint32_t rtx = (uint32_t)(p.BW * p.BH * p.BN) * 128u;
+    const int groups = p.block_n / 64;
+    int rslot = 0;
+    uint32_t rphase = 0;
+    for (int t = blockIdx.x; t < total; t += gridDim.x) {
+      const int nt = t % p.n_tiles;
+      const int mg = t / p.n_tiles;
+      int nvalid = m_tiles - mg * p.acc_m;
+      if (nvalid > p.acc_m) nvalid = p.acc_m;
+      for (int j = 0; j < nvalid; ++j) {
+        int mt = mg * p.acc_m + j;
+        const int w0 = (mt % p.tiles_w) * p.BW;
+        mt /= p.tiles_w;
+        const int h0 = (mt % p.tiles_h) * p.BH;
+        const int n0 = (mt / p.tiles_h) * p.BN;
+        for (int g = 0; g < groups; ++g) {
+          mbar_wait(&rempty[rslot], rphase ^ 1);
+          if (elect_one()) {
+            mbar_expect_tx(&rfull[rslot], rtx);
+            tma_load_4d(res_buf + rslot * 16384, &p.r_map, &rfull[rslot], nt * p.block_n + g * 64, w0, h0, n0);
+          }
+          __syncwarp();
+          if (++rslot == TC_RES_SLOTS) { rslot = 0; rphase ^= 1; }
+        }
+      }
     }
   }
   tc_fence_before();
@@ -853,7 +963,8 @@ struct TapSpec { int8_t map, dw, dh, b; };
 
 static int create_sub(const rn_conv_desc* d, int kind, const void* a, const void* b, const void* out_base,
                       int oW, int oH, const uint64_t* ostr, const TapSpec* taps, int ntaps, TcConvParams* pp,
-                      int* grid, size_t* smem_bytes, const ActView* view = nullptr, int b_taps = 0) {
+                      int* grid, size_t* smem_bytes, const ActView* view = nullptr, int b_taps = 0,
+                      const void* residual = nullptr, float* stat_partials = nullptr) {
   TcConvParams& p = *pp;
   memset(&p, 0, sizeof(p));
   const int cred = kind == 0 ? d->Cin : d->Cout;
@@ -881,7 +992,16 @@ static int create_sub(const rn_conv_desc* d, int kind, const void* a, const void
   // which is what bounds these kernels), limited by the 512 TMEM columns, by shared memory (>= 3 stages)
   // and by keeping every SM busy
   const long m_tiles = (long)p.tiles_w * p.tiles_h * p.tiles_n;
-  const size_t fixed = 2 * 16384 + 1024 + 1024;     // epilogue staging, barriers, alignment slack
+  // epilogue staging, barriers, alignment slack; fused epilogue: residual tile ring, statistics scratch
+  const bool want_fused = residual != nullptr || stat_partials != nullptr;
+  if (want_fused && (kind != 0 || p.gw != 64))
+    return fail(RN_ERR_UNSUPPORTED, "convtc: the fused epilogue needs fprop and output channels in multiples of 64");
+  p.fuse_add = residual != nullptr;
+  p.fuse_stats = stat_partials != nullptr;
+  p.ncols_total = ncols;
+  p.stat_partials = stat_partials;
+  const size_t fixed = 2 * 16384 + 1024 + 1024 + (p.fuse_add ? (size_t)TC_RES_SLOTS * 16384 : 0) +
+                       (p.fuse_stats ? 4096 + (size_t)ncols * 8 : 0);
   const size_t budget = 227 * 1024;
   int acc_m = 1;
   {
@@ -939,6 +1059,10 @@ static int create_sub(const rn_conv_desc* d, int kind, const void* a, const void
     const uint32_t box[4] = {(uint32_t)p.gw, (uint32_t)p.BW, (uint32_t)p.BH, (uint32_t)p.BN};
     rc = encode_map(&p.o_map, out_base, 4, dims, ostr, box, p.gw * 2, "output");
     if (rc) return rc;
+    if (p.fuse_add) {
+      rc = encode_map(&p.r_map, residual, 4, dims, ostr, box, p.gw * 2, "residual");
+      if (rc) return rc;
+    }
   }
   const long total = ((m_tiles + acc_m - 1) / acc_m) * p.n_tiles;
   *grid = (int)(total < RN_NUM_SMS ? total : RN_NUM_SMS);
@@ -1048,6 +1172,47 @@ extern "C" int rn_convtc_plan_create(const rn_conv_desc* d, int kind, const void
   return RN_OK;
 }
 
+extern "C" int rn_convtc_fused_supported(const rn_conv_desc* d) {
+  if (!rn_convtc_supported(d, 0)) return 0;
+  const int bn_ = choose_block_n(d->Cout);
+  return (bn_ % 64 == 0 && d->Cout <= 4096) ? 1 : 0;
+}
+
+extern "C" int rn_convtc_stat_rows(const rn_conv_desc* d) {
+  (void)d;
+  return RN_NUM_SMS;            // the persistent grid never exceeds one CTA per SM
+}
+
+extern "C" int rn_convtc_plan_create_fused(const rn_conv_desc* d, const void* x, const void* w_bf16, void* out,
+                                           const void* residual, float* stat_partials, int32_t* stat_rows,
+                                           rn_convtc_plan** plan) {
+  RN_REQUIRE(d && x && w_bf16 && out && plan, "convtc_plan_create_fused: NULL pointer");
+  RN_REQUIRE(residual || stat_partials, "convtc_plan_create_fused: nothing to fuse");
+  if (!rn_convtc_fused_supported(d)) return fail(RN_ERR_UNSUPPORTED, "convtc: fused epilogue not supported for this shape");
+  RN_REQUIRE((((uintptr_t)x | (uintptr_t)w_bf16 | (uintptr_t)out | (uintptr_t)residual) & 15) == 0,
+             "convtc: pointers must be 16-byte aligned");
+  cudaError_t e = cudaFuncSetAttribute(conv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024));
+  if (e != cudaSuccess) return fail(RN_ERR_CUDA, "convtc: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+  rn_convtc_plan* pl = new rn_convtc_plan();
+  memset(pl, 0, sizeof(*pl));
+  pl->kind = 0;
+  pl->nsub = 1;
+  TapSpec taps[TC_MAX_TAPS];
+  for (int r = 0; r < d->k; ++r)
+    for (int s = 0; s < d->k; ++s) {
+      TapSpec& t = taps[r * d->k + s];
+      t.b = (int8_t)(r * d->k + s);
+      forward_tap(r, s, d->pad, d->stride, &t.map, &t.dw, &t.dh);
+    }
+  const uint64_t ostr[3] = {(uint64_t)d->Cout * 2, (uint64_t)d->Wo * d->Cout * 2, (uint64_t)d->Ho * d->Wo * d->Cout * 2};
+  const int rc = create_sub(d, 0, x, w_bf16, out, d->Wo, d->Ho, ostr, taps, d->k * d->k, &pl->p[0], &pl->grid[0],
+                            &pl->smem_sub[0], nullptr, 0, residual, stat_partials);
+  if (rc) { delete pl; return rc; }
+  if (stat_rows) *stat_rows = pl->grid[0];
+  *plan = pl;
+  return RN_OK;
+}
+
 extern "C" int rn_convtc_run(rn_convtc_plan* plan, float beta, void* stream) {
   RN_REQUIRE(plan, "convtc_run: NULL plan");
   RN_REQUIRE(beta == 0.f || beta == 1.f, "convtc_run: beta must be 0 or 1");
@@ -1067,6 +1232,8 @@ extern "C" int rn_convtc_run(rn_convtc_plan* plan, float beta, void* stream) {
     }
     return rc;
   }
+  if (beta != 0.f && (plan->p[0].fuse_add || plan->p[0].fuse_stats))
+    return fail(RN_ERR_UNSUPPORTED, "convtc_run: a plan with a fused epilogue overwrites its output (beta must be 0)");
   if (beta == 0.f && plan->clear_ptr) {
     cudaError_t e = cudaMemsetAsync(plan->clear_ptr, 0, plan->clear_bytes, st);
     if (e != cudaSuccess) return fail(RN_ERR_CUDA, "convtc_run: cudaMemsetAsync: %s", cudaGetErrorString(e));
@@ -1074,7 +1241,7 @@ extern "C" int rn_convtc_run(rn_convtc_plan* plan, float beta, void* stream) {
   for (int i = 0; i < plan->nsub; ++i) {
     TcConvParams p = plan->p[i];
     p.accumulate = beta != 0.f ? 1 : 0;
-    launch_pdl(conv_tc_kernel, plan->grid[i], TC_THREADS, plan->smem_sub[i], st, p);
+    launch_pdl(conv_tc_kernel, plan->grid[i], p.fuse_add ? TC_THREADS_RES : TC_THREADS, plan->smem_sub[i], st, p);
     int rc = check_launch("conv_tc_kernel");
     if (rc) return rc;
   }

@@ -86,6 +86,20 @@ size_t rn_convtc_scratch_bytes(const rn_conv_desc* d, int kind);
 int rn_convtc_plan_create(const rn_conv_desc* d, int kind, const void* a, const void* b, void* out,
                           void* scratch, size_t scratch_bytes, rn_convtc_plan** plan);
 /* beta (dgrad only): 0 overwrite, 1 accumulate into `out`. */
+/* fprop with a fused epilogue (Cout a multiple of 64; beta must be 0 at run time):
+ *   residual != NULL      : out = bf16(bf16(conv) + residual) — the bottleneck's `inputs + shortcut`
+ *                           (resnet_model_official.py:130 / :175) without materialising the conv output;
+ *                           residual has the shape and layout of out.
+ *   stat_partials != NULL : per-channel (sum, sum of squares) of the STORED bf16 output, one row
+ *                           [Cout][2] fp32 per CTA; rn_convtc_stat_rows() bounds the rows to allocate,
+ *                           *stat_rows receives the number this plan writes; rn_bn_finalize turns them
+ *                           into the batch-norm statistics (FusedBatchNorm, :41-50) without a pass over
+ *                           the tensor. */
+int rn_convtc_fused_supported(const rn_conv_desc* d);
+int rn_convtc_stat_rows(const rn_conv_desc* d);
+int rn_convtc_plan_create_fused(const rn_conv_desc* d, const void* x, const void* w_bf16, void* out,
+                                const void* residual, float* stat_partials, int32_t* stat_rows,
+                                rn_convtc_plan** plan);
 int rn_convtc_run(rn_convtc_plan* plan, float beta, void* stream);
 int rn_convtc_plan_destroy(rn_convtc_plan* plan);
 /* Re-layout of the fp32 HWIO master weights into the two bf16 operand layouts above
@@ -135,6 +149,10 @@ int rn_stem_s2d_plan_create(const rn_conv_desc* d, int kind, const void* u, cons
  *   C % 8 == 0 (bf16) for the vector path, any C otherwise.
  * ------------------------------------------------------------------------------------------ */
 size_t rn_bn_scratch_bytes(int64_t M, int32_t C);
+/* Statistics from per-CTA partial sums partials[nparts][C][2] written by a fused convolution epilogue
+ * (rn_convtc_plan_create_fused): same outputs and moving-average update as rn_bn_stats_fwd. */
+int rn_bn_finalize(const float* partials, int32_t nparts, int64_t M, int32_t C, float eps, float decay,
+                   int32_t unbiased, float* mean, float* rstd, float* moving_mean, float* moving_var, void* stream);
 /* Training statistics.  If `addend` != NULL the statistics are of z = x + addend and z is written
  * to `sum_out` (the residual add fused into the statistics pass).  Writes mean[C], rstd[C]
  * (= 1/sqrt(biased_var + eps)) and, if moving_mean != NULL, updates

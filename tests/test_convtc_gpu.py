@@ -258,3 +258,70 @@ def test_stem_space_to_depth_fprop_and_wgrad(case):
     lib.rn_convtc_plan_destroy(plan)
     assert torch.isfinite(DW).all()
     assert rel_err(DW, net.param_grads["w"]) < 1e-3             # fp32 accumulation of exact bf16 products
+
+
+FUSED_CASES = [
+    # N, H, W, Cin, Cout, k, stride, pad, (Ho, Wo), residual?, stats?
+    (4, 16, 16, 64, 64, 3, 1, 1, (16, 16), False, True),       # conv-fed BN: statistics only
+    (8, 14, 14, 256, 256, 3, 1, 1, (14, 14), False, True),
+    (4, 28, 28, 64, 256, 1, 1, 0, (28, 28), True, True),       # bottleneck conv3 + shortcut + next block's BN statistics
+    (6, 7, 7, 512, 2048, 1, 1, 0, (7, 7), True, True),         # stage-4 widths: 8 column tiles, ragged pixel box (98 of 128 rows)
+    (3, 9, 11, 64, 128, 1, 1, 0, (9, 11), True, False),        # add only, ragged everything
+    (2, 56, 56, 64, 256, 1, 1, 0, (56, 56), True, True),       # C3 stage-1 shape
+    (4, 16, 16, 64, 128, 3, 2, 1, (8, 8), False, True),        # stride 2
+]
+
+
+@pytest.mark.parametrize("case", FUSED_CASES)
+def test_convtc_fused_epilogue(case):
+    """fprop with the residual add and / or the batch-norm statistics fused into the epilogue
+    (rn_convtc_plan_create_fused + rn_bn_finalize) against conv -> add -> statistics of the oracle.
+    The fused output must equal bf16(bf16(conv) + residual) — the value the unfused pipeline stores —
+    and the statistics must be those of the stored tensor."""
+    N, H, W, Cin, Cout, k, s, pad, (Ho, Wo), use_res, use_stats = case
+    g = torch.Generator().manual_seed(sum(case[:8]) + 7)
+    x = torch.randn(N, H, W, Cin, generator=g).to(BF)
+    w = (torch.randn(k, k, Cin, Cout, generator=g) / (k * k * Cin) ** 0.5).to(BF)
+    res = torch.randn(N, Ho, Wo, Cout, generator=g).to(BF)
+    net = ro.Net(dtype=torch.float64, params={"w": w.double().numpy()})
+    yv = net.conv2d(ro.Var(x.double()), "w", k, Cin, Cout, s, pad, (Ho, Wo), None, "y")
+    d = ConvDesc(N, H, W, Cin, Ho, Wo, Cout, k, s, pad, RN_BF16)
+    assert lib.rn_convtc_fused_supported(C.byref(d)) == 1
+    X, WB, R = dev(x), dev(w), dev(res)
+    # unfused reference through the library itself: conv -> (add) -> statistics kernel
+    Y0 = torch.empty(N, Ho, Wo, Cout, dtype=BF, device="cuda")
+    plan = C.c_void_p()
+    check(lib.rn_convtc_plan_create(C.byref(d), 0, ptr(X), ptr(WB), ptr(Y0), None, 0, C.byref(plan)), "plan")
+    check(lib.rn_convtc_run(plan, 0.0, stream()), "run")
+    torch.cuda.synchronize()
+    lib.rn_convtc_plan_destroy(plan)
+    want = (Y0.float() + R.float()).to(BF) if use_res else Y0
+    rows_cap = lib.rn_convtc_stat_rows(C.byref(d))
+    PART = torch.full((rows_cap, Cout, 2), float("nan"), dtype=torch.float32, device="cuda")
+    Z = torch.full((N, Ho, Wo, Cout), float("nan"), dtype=BF, device="cuda")
+    nrows = C.c_int32(0)
+    check(lib.rn_convtc_plan_create_fused(C.byref(d), ptr(X), ptr(WB), ptr(Z), ptr(R) if use_res else None,
+                                          ptr(PART) if use_stats else None, C.byref(nrows), C.byref(plan)), "plan fused")
+    for _ in range(2):
+        check(lib.rn_convtc_run(plan, 0.0, stream()), "run fused")
+    torch.cuda.synchronize()
+    assert torch.isfinite(Z.float()).all()
+    assert torch.equal(Z, want), "fused output differs from bf16(bf16(conv) + residual): max |d| = %g" % (
+        (Z.float() - want.float()).abs().max().item())
+    assert rel_err(Z.float(), yv.val + (res.double() if use_res else 0.0)) < 2e-2
+    assert lib.rn_convtc_run(plan, 1.0, stream()) != 0          # a fused plan cannot accumulate
+    lib.rn_convtc_plan_destroy(plan)
+    if use_stats:
+        M = N * Ho * Wo
+        assert 0 < nrows.value <= rows_cap and torch.isfinite(PART[:nrows.value]).all()
+        mean = torch.empty(Cout, device="cuda"); rstd = torch.empty(Cout, device="cuda")
+        mm = torch.zeros(Cout, device="cuda"); mv = torch.ones(Cout, device="cuda")
+        check(lib.rn_bn_finalize(ptr(PART), nrows.value, M, Cout, 1e-5, 0.9, 1, ptr(mean), ptr(rstd), ptr(mm), ptr(mv),
+                                 stream()), "finalize")
+        torch.cuda.synchronize()
+        z = Z.double().reshape(M, Cout).cpu()
+        m_ref, v_ref = z.mean(0), z.var(0, unbiased=False)
+        assert (mean.cpu().double() - m_ref).abs().max() < 1e-5 * max(1.0, float(m_ref.abs().max()))
+        assert rel_err(rstd.cpu().double(), 1.0 / torch.sqrt(v_ref + 1e-5)) < 1e-5
+        assert rel_err(mm.cpu().double(), 0.1 * m_ref) < 1e-4
+        assert rel_err(mv.cpu().double(), 0.9 + 0.1 * v_ref * M / (M - 1)) < 1e-5
