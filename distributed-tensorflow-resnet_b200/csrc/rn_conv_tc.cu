@@ -55,6 +55,7 @@ struct TcConvParams {
   int fuse_stats;                 // per-channel sum / sum of squares of the STORED bf16 output -> stat_partials[CTA][ncols][2]
   int fuse_add;                   // OUT = bf16(bf16(result) + residual): the residual tile arrives through r_map (warp 6)
   int ncols_total;
+  int oW, oH, oN;                 // output extents (rows of a tile that fall outside are not part of the tensor)
   float* stat_partials;
   CUtensorMap r_map;
   int8_t tap_map[TC_MAX_TAPS], tap_dw[TC_MAX_TAPS], tap_dh[TC_MAX_TAPS], tap_b[TC_MAX_TAPS];
@@ -63,7 +64,12 @@ struct TcConvParams {
 constexpr int TC_RES_SLOTS = 3;            // residual tiles in flight (16 KB each)
 constexpr int TC_THREADS_RES = TC_THREADS + 32;
 
-__global__ void __launch_bounds__(TC_THREADS_RES, 1) conv_tc_kernel(const __grid_constant__ TcConvParams p) {
+// FUSED = false compiles the plain epilogue only (fprop / dgrad without fusion keep their registers and schedule)
+template <bool FUSED>
+__global__ void __launch_bounds__(FUSED ? TC_THREADS_RES : TC_THREADS, 1)
+conv_tc_kernel(const __grid_constant__ TcConvParams p) {
+  const bool fuse_add = FUSED && p.fuse_add;
+  const bool fuse_stats = FUSED && p.fuse_stats;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base_u32 = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* smem = smem_raw + (base_u32 - smem_u32(smem_raw));
@@ -71,10 +77,10 @@ __global__ void __launch_bounds__(TC_THREADS_RES, 1) conv_tc_kernel(const __grid
   const int row_bytes_out = p.gw * 2;
   uint8_t* epi_buf = smem + (size_t)p.stages * stage_bytes;                  // 2 x 16 KB
   uint8_t* res_buf = epi_buf + 2 * 16384;                                     // TC_RES_SLOTS x 16 KB (fused add)
-  uint8_t* after_res = res_buf + (p.fuse_add ? TC_RES_SLOTS * 16384 : 0);
+  uint8_t* after_res = res_buf + (fuse_add ? TC_RES_SLOTS * 16384 : 0);
   float* cs = reinterpret_cast<float*>(after_res);                            // 2 x [4 warps][32 column pairs][4] (fused stats)
   float* pacc = cs + 1024;                                                    // [ncols_total][2]
-  uint8_t* after_stats = after_res + (p.fuse_stats ? 4096 + (size_t)p.ncols_total * 8 : 0);
+  uint8_t* after_stats = after_res + (fuse_stats ? 4096 + (size_t)p.ncols_total * 8 : 0);
   uint64_t* bars = reinterpret_cast<uint64_t*>(after_stats);
   uint64_t* full = bars;                  // [stages]
   uint64_t* empty = bars + p.stages;      // [stages]
@@ -93,13 +99,13 @@ __global__ void __launch_bounds__(TC_THREADS_RES, 1) conv_tc_kernel(const __grid
     tma_prefetch_desc(&p.a_map[0]);
     tma_prefetch_desc(&p.b_map);
     tma_prefetch_desc(&p.o_map);
-    if (p.fuse_add) tma_prefetch_desc(&p.r_map);
+    if (fuse_add) tma_prefetch_desc(&p.r_map);
   }
   if (warp == 1) {
     tmem_alloc(tmem_slot, p.tmem_cols);
     tmem_relinquish();
   }
-  if (p.fuse_stats && warp >= 2 && warp < 6)
+  if (fuse_stats && warp >= 2 && warp < 6)
     for (int i = threadIdx.x - 64; i < 2 * p.ncols_total; i += 128) pacc[i] = 0.f;
   tc_fence_before();
   __syncthreads();
@@ -248,6 +254,14 @@ __global__ void __launch_bounds__(TC_THREADS_RES, 1) conv_tc_kernel(const __grid
         mt /= p.tiles_w;
         const int h0 = (mt % p.tiles_h) * p.BH;
         const int n0 = (mt / p.tiles_h) * p.BN;
+        // rows of this warp whose output pixel exists: a k > 1 convolution produces non-zero values for
+        // pixels just outside the image (TMA clips them on store; the statistics must skip them too)
+        uint32_t row_mask = 0;
+        if (fuse_stats) {
+          const int bw = row % p.BW, bh = (row / p.BW) % p.BH, bn = row / (p.BW * p.BH);
+          const bool ok = row < box_rows && w0 + bw < p.oW && h0 + bh < p.oH && n0 + bn < p.oN;
+          row_mask = __ballot_sync(0xffffffffu, ok);
+        }
         for (int g = 0; g < groups; ++g) {
           const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) +
                                  (uint32_t)((acc * p.acc_m + j) * p.block_n + g * p.gw);
@@ -266,11 +280,11 @@ __global__ void __launch_bounds__(TC_THREADS_RES, 1) conv_tc_kernel(const __grid
           asm volatile("bar.sync 1, 128;" ::: "memory");
           uint8_t* sb = epi_buf + buf * 16384;
           if (p.gw == 64) {
-            if (p.fuse_stats && pend_col >= 0) combine(pend_col, csb ^ 1);
+            if (fuse_stats && pend_col >= 0) combine(pend_col, csb ^ 1);
             tmem_ld_wait();
             const uint32_t rbase = (uint32_t)row * 128u;
             const uint8_t* rb = res_buf + rslot * 16384;
-            if (p.fuse_add) mbar_wait(&rfull[rslot], rphase);
+            if (fuse_add) mbar_wait(&rfull[rslot], rphase);
 #pragma unroll
             for (int c = 0; c < 8; ++c) {
               uint32_t pk[4];
@@ -282,7 +296,7 @@ __global__ void __launch_bounds__(TC_THREADS_RES, 1) conv_tc_kernel(const __grid
                 pk[i] = *reinterpret_cast<uint32_t*>(&h);
               }
               const uint32_t so = swizzle_offset(rbase + 16u * c, 128);
-              if (p.fuse_add) {
+              if (fuse_add) {
                 // z = bf16(bf16(conv) + residual): the same two roundings as a stored conv output followed by the add
                 const uint4 rv = *reinterpret_cast<const uint4*>(rb + so);
                 const uint32_t rw[4] = {rv.x, rv.y, rv.z, rv.w};
@@ -296,20 +310,22 @@ __global__ void __launch_bounds__(TC_THREADS_RES, 1) conv_tc_kernel(const __grid
               }
               *reinterpret_cast<uint4*>(sb + so) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
             }
-            if (p.fuse_add) {
+            if (fuse_add) {
               __syncwarp();
               if (lane == 0) mbar_arrive(&rempty[rslot]);
               if (++rslot == TC_RES_SLOTS) { rslot = 0; rphase ^= 1; }
             }
-            if (p.fuse_stats) {
+            if (fuse_stats) {
               // first half: this warp re-reads the 32 rows it just wrote, one column pair per lane (a row is the
               // 32 lanes' 128 bytes: conflict-free under the swizzle), and sums value / value^2 of the STORED bf16
               __syncwarp();
               float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
-              const int nrow = min(32, box_rows - quad * 32);      // rows past the pixel box hold stale data
-              for (int r = 0; r < nrow; ++r) {
-                const uint32_t w = *reinterpret_cast<const uint32_t*>(
+#pragma unroll
+              for (int r = 0; r < 32; ++r) {
+                // all 32 loads independent; rows outside the tensor contribute +0 (they may hold anything)
+                uint32_t w = *reinterpret_cast<const uint32_t*>(
                     sb + swizzle_offset((uint32_t)(quad * 32 + r) * 128u + (uint32_t)lane * 4u, 128));
+                w = ((row_mask >> r) & 1u) ? w : 0u;
                 const float f0 = __uint_as_float(w << 16), f1 = __uint_as_float(w & 0xffff0000u);
                 s0 += f0; s1 += f1;
                 q0 = fmaf(f0, f0, q0); q1 = fmaf(f1, f1, q1);
@@ -354,7 +370,7 @@ __global__ void __launch_bounds__(TC_THREADS_RES, 1) conv_tc_kernel(const __grid
       if (lane == 0) mbar_arrive(&tempty[acc]);
       if (++acc == p.tstages) { acc = 0; acc_phase ^= 1; }
     }
-    if (p.fuse_stats) {
+    if (fuse_stats) {
       // last group's quarter sums, then this CTA's totals go to its row of the partial table (the finalize
       // kernel sums the <= 148 rows in fp64 in a fixed order)
       if (pend_col >= 0) combine(pend_col, csb ^ 1);      // ordered after the last group's second barrier
@@ -683,6 +699,12 @@ __global__ void weights_to_bf16_batched_kernel(const RelayoutJob* __restrict__ j
 // ------------------------------------------------------------------------------------------
 // host side: tensor maps and plans
 // ------------------------------------------------------------------------------------------
+static cudaError_t set_conv_tc_smem_attr() {
+  cudaError_t e = cudaFuncSetAttribute(conv_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024));
+  if (e != cudaSuccess) return e;
+  return cudaFuncSetAttribute(conv_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024));
+}
+
 typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                     const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
                                     CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -999,6 +1021,7 @@ static int create_sub(const rn_conv_desc* d, int kind, const void* a, const void
   p.fuse_add = residual != nullptr;
   p.fuse_stats = stat_partials != nullptr;
   p.ncols_total = ncols;
+  p.oW = oW; p.oH = oH; p.oN = d->N;
   p.stat_partials = stat_partials;
   const size_t fixed = 2 * 16384 + 1024 + 1024 + (p.fuse_add ? (size_t)TC_RES_SLOTS * 16384 : 0) +
                        (p.fuse_stats ? 4096 + (size_t)ncols * 8 : 0);
@@ -1071,7 +1094,7 @@ static int create_sub(const rn_conv_desc* d, int kind, const void* a, const void
 
 static int create_gemm_plan(const rn_conv_desc* d, int kind, const void* a, const void* b, void* out,
                             rn_convtc_plan* pl) {
-  cudaError_t e = cudaFuncSetAttribute(conv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024));
+  cudaError_t e = set_conv_tc_smem_attr();
   if (e != cudaSuccess) return fail(RN_ERR_CUDA, "convtc: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
   TapSpec taps[TC_MAX_TAPS];
   pl->clear_ptr = nullptr;
@@ -1191,7 +1214,7 @@ extern "C" int rn_convtc_plan_create_fused(const rn_conv_desc* d, const void* x,
   if (!rn_convtc_fused_supported(d)) return fail(RN_ERR_UNSUPPORTED, "convtc: fused epilogue not supported for this shape");
   RN_REQUIRE((((uintptr_t)x | (uintptr_t)w_bf16 | (uintptr_t)out | (uintptr_t)residual) & 15) == 0,
              "convtc: pointers must be 16-byte aligned");
-  cudaError_t e = cudaFuncSetAttribute(conv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024));
+  cudaError_t e = set_conv_tc_smem_attr();
   if (e != cudaSuccess) return fail(RN_ERR_CUDA, "convtc: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
   rn_convtc_plan* pl = new rn_convtc_plan();
   memset(pl, 0, sizeof(*pl));
@@ -1241,7 +1264,10 @@ extern "C" int rn_convtc_run(rn_convtc_plan* plan, float beta, void* stream) {
   for (int i = 0; i < plan->nsub; ++i) {
     TcConvParams p = plan->p[i];
     p.accumulate = beta != 0.f ? 1 : 0;
-    launch_pdl(conv_tc_kernel, plan->grid[i], p.fuse_add ? TC_THREADS_RES : TC_THREADS, plan->smem_sub[i], st, p);
+    if (p.fuse_add || p.fuse_stats)
+      launch_pdl(conv_tc_kernel<true>, plan->grid[i], p.fuse_add ? TC_THREADS_RES : TC_THREADS, plan->smem_sub[i], st, p);
+    else
+      launch_pdl(conv_tc_kernel<false>, plan->grid[i], TC_THREADS, plan->smem_sub[i], st, p);
     int rc = check_launch("conv_tc_kernel");
     if (rc) return rc;
   }
@@ -1549,7 +1575,7 @@ extern "C" int rn_stem_s2d_plan_create(const rn_conv_desc* d, int kind, const vo
   pl->kind = kind;
   int rc;
   if (kind == 0) {
-    cudaError_t e = cudaFuncSetAttribute(conv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024));
+    cudaError_t e = set_conv_tc_smem_attr();
     if (e != cudaSuccess) { delete pl; return fail(RN_ERR_CUDA, "stem_s2d: cudaFuncSetAttribute: %s", cudaGetErrorString(e)); }
     const uint64_t ostr[3] = {(uint64_t)d->Cout * 2, (uint64_t)d->Wo * d->Cout * 2, (uint64_t)d->Ho * d->Wo * d->Cout * 2};
     pl->nsub = 1;

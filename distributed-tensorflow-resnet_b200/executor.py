@@ -228,6 +228,44 @@ class Executor:
             return p
         return None
 
+    def _fusable_conv(self, t):
+        """The conv node producing tensor t if its tensor-core fprop can carry a fused epilogue."""
+        p = t.producer
+        if p is None or p.op != "conv2d" or hasattr(p, "fuse") or not self.use_tc or not self.bf16:
+            return None
+        d = self._desc(p)
+        if self._is_stem(p) or not lib.rn_convtc_fused_supported(C.byref(d)):
+            return None
+        return p
+
+    def _plan_epilogue_fusion(self):
+        """Decide which convolutions carry a fused epilogue (RN_NO_EPILOGUE_FUSION=1 disables it):
+          * a training-mode BN fed directly by a conv: the conv epilogue accumulates the per-channel sums, the
+            statistics pass over the tensor is replaced by rn_bn_finalize;
+          * a training-mode BN fed by `conv + shortcut` (the bottleneck's residual add): the conv epilogue adds
+            the shortcut tile, stores the sum and accumulates its statistics — the conv output itself is never
+            materialised (nothing in backward reads it)."""
+        if os.environ.get("RN_NO_EPILOGUE_FUSION"):
+            return
+        for n in self.g.nodes:
+            if n.op != "bn_act" or not n.attrs["is_training"]:
+                continue
+            x = n.inputs[0]
+            add = self._fused_add_for(n)
+            if add is not None:
+                for i in (0, 1):
+                    t, other = add.inputs[i], add.inputs[1 - i]
+                    cv = self._fusable_conv(t)
+                    if cv is not None and len(t.consumers) == 1 and t.shape == x.shape and other.shape == x.shape:
+                        cv.fuse = dict(out=x, residual=other, bn=n)
+                        n.stats_from = cv
+                        break
+            else:
+                cv = self._fusable_conv(x)
+                if cv is not None:
+                    cv.fuse = dict(out=x, residual=None, bn=n)
+                    n.stats_from = cv
+
     def _build_forward(self):
         fwd = []
         g = self.g
@@ -239,6 +277,7 @@ class Executor:
                 if a is not None:
                     fused_adds.add(id(a))
         self._fused_adds = fused_adds
+        self._plan_epilogue_fusion()
         for t in g.placeholders.values():
             src = getattr(t, "cast_from", None)
             if src is not None:
@@ -251,11 +290,19 @@ class Executor:
                 self._keep.append(src)
         for n in g.nodes:
             if n.op == "conv2d":
+                if getattr(n, "fuse", None) and n.fuse["residual"] is not None:
+                    continue            # launched where its add stood: the shortcut may be produced after this node
                 fwd.append(self._conv_fprop(n))
             elif n.op == "bn_act":
                 fwd.extend(self._bn_fwd(n))
             elif n.op == "add":
                 if id(n) in fused_adds:
+                    for t in n.inputs:
+                        cv = t.producer
+                        if cv is not None and getattr(cv, "fuse", None) and cv.fuse["out"] is n.outputs[0]:
+                            item = self._conv_fprop(cv)
+                            fwd.append(item)
+                            self.meta[item[0]] = dict(node=cv)
                     continue
                 a, b = n.inputs
                 y = n.outputs[0]
@@ -409,6 +456,21 @@ class Executor:
                       check(lib.rn_im2col(*a, s), "rn_im2col"))
             run = self._plan_raw(st["d1"], 0, st["cols"], st["wf"], y.buf)
             return ("conv_fprop_tc:" + y.name, lambda s, im2col=im2col, run=run: (im2col(s), run(s)))
+        if hasattr(n, "fuse"):
+            f = n.fuse
+            rows = lib.rn_convtc_stat_rows(C.byref(d))
+            f["partials"] = torch.zeros(rows, d.Cout, 2, dtype=torch.float32, device=self.dev)
+            nrows = C.c_int32(0)
+            plan = C.c_void_p()
+            check(lib.rn_convtc_plan_create_fused(C.byref(d), ptr(x.buf), self._wptr(kv, "Wb"), ptr(f["out"].buf),
+                                                  ptr(f["residual"].buf) if f["residual"] is not None else None,
+                                                  ptr(f["partials"]), C.byref(nrows), C.byref(plan)),
+                  "rn_convtc_plan_create_fused")
+            f["nrows"] = nrows.value
+            self._plans.append(plan)
+            if f["residual"] is not None:
+                y.buf = None            # conv + shortcut goes straight into the sum: the conv output is never materialised
+            return ("conv_fprop_tc:" + y.name, lambda s, p=plan: check(lib.rn_convtc_run(p, 0.0, s), "rn_convtc_run"))
         if self._conv_impl(n, 0) == "tc":
             return ("conv_fprop_tc:" + y.name, self._tc_plan(n, d, 0, x.buf, y.buf))
         w = self._wptr(kv, "Wb" if self.bf16 else "W")
@@ -453,9 +515,17 @@ class Executor:
             mm, mv = self._wptr(v["moving_mean"], "S"), self._wptr(v["moving_variance"], "S")
             if not self.train:
                 mm = mv = None       # forward-only with batch statistics: leave moving stats alone
-            out.append(("bn_stats:" + a["scope"],
-                        lambda s, args=(px, pa, pz, M, C_, self.rn_dt, a["eps"], a["decay"], int(a["unbiased"]), mean_p, rstd_p, mm, mv):
-                        check(lib.rn_bn_stats_fwd(*args, ptr(self.scratch), self.scratch_bytes, s), "rn_bn_stats_fwd")))
+            cv = getattr(n, "stats_from", None)
+            if cv is not None:
+                # the producing conv's epilogue already summed the stored tensor (and added the shortcut)
+                out.append(("bn_finalize:" + a["scope"],
+                            lambda s, args=(ptr(cv.fuse["partials"]), cv.fuse["nrows"], M, C_, a["eps"], a["decay"],
+                                            int(a["unbiased"]), mean_p, rstd_p, mm, mv):
+                            check(lib.rn_bn_finalize(*args, s), "rn_bn_finalize")))
+            else:
+                out.append(("bn_stats:" + a["scope"],
+                            lambda s, args=(px, pa, pz, M, C_, self.rn_dt, a["eps"], a["decay"], int(a["unbiased"]), mean_p, rstd_p, mm, mv):
+                            check(lib.rn_bn_stats_fwd(*args, ptr(self.scratch), self.scratch_bytes, s), "rn_bn_stats_fwd")))
             out.append(("bn_apply:" + a["scope"],
                         lambda s, args=(ptr(x.buf), ptr(y.buf), M, C_, self.rn_dt, self._wptr(v["gamma"]), self._wptr(v["beta"]), mean_p, rstd_p, 0, a["eps"], a["leak"]):
                         check(lib.rn_bn_apply_act_fwd(*args, s), "rn_bn_apply_act_fwd")))

@@ -269,6 +269,9 @@ FUSED_CASES = [
     (3, 9, 11, 64, 128, 1, 1, 0, (9, 11), True, False),        # add only, ragged everything
     (2, 56, 56, 64, 256, 1, 1, 0, (56, 56), True, True),       # C3 stage-1 shape
     (4, 16, 16, 64, 128, 3, 2, 1, (8, 8), False, True),        # stride 2
+    (2, 14, 14, 256, 256, 3, 1, 1, (14, 14), False, True),     # box 14x4x2: tile rows past the image bottom are non-zero for k = 3
+    (2, 28, 28, 256, 256, 3, 2, 1, (14, 14), False, True),
+    (3, 9, 11, 64, 64, 3, 1, 1, (9, 11), True, True),
 ]
 
 

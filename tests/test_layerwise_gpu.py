@@ -60,14 +60,19 @@ class Verifier:
             a = node.attrs
             net._given = {"w": self.weight(node).numpy()}
             out = net.conv2d(_var(x.buf), "w", a["k"], x.shape[3], y.shape[3], a["stride"], a["pad"], y.shape[1:3], None, "y")
-            self.check(name, y.buf, out.val)
+            f = getattr(node, "fuse", None)
+            if f is None:
+                self.check(name, y.buf, out.val)
+            else:       # fused epilogue: the launch wrote conv (+ shortcut) into the BN input, never y itself
+                want = out.val + (_d(f["residual"].buf) if f["residual"] is not None else 0.0)
+                self.check(name + "/fused", f["out"].buf, want)
         elif node.op == "bn_act":
             x, y = node.inputs[0], node.outputs[0]
             a, v = node.attrs, node.vars
             C = x.shape[-1]
             add = ex._fused_add_for(node)
-            if fam == "bn_stats":
-                if add is not None:
+            if fam in ("bn_stats", "bn_finalize"):
+                if add is not None and fam == "bn_stats":
                     z = _d(add.inputs[0].buf) + _d(add.inputs[1].buf)
                     self.check(name + "/z", x.buf, z)
                 x2 = _d(x.buf).reshape(-1, C)
