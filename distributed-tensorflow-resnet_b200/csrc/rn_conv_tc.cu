@@ -25,7 +25,10 @@
 namespace rn {
 using namespace tc;
 
-constexpr int TC_THREADS = 192;
+constexpr int TC_THREADS = 192;           // wgrad kernel: producer, MMA issuer, 4 epilogue warps
+constexpr int TC_EPI_WARPS = 8;           // fprop / dgrad kernel: two epilogue warps per TMEM lane quadrant (half a row each)
+constexpr int TC_EPI_THREADS = TC_EPI_WARPS * 32;
+constexpr int TC_CONV_THREADS = 64 + TC_EPI_THREADS;
 constexpr int TC_MAX_TAPS = 52;
 constexpr int TC_BLOCK_M = 128;
 
@@ -62,11 +65,11 @@ struct TcConvParams {
 };
 
 constexpr int TC_RES_SLOTS = 3;            // residual tiles in flight (16 KB each)
-constexpr int TC_THREADS_RES = TC_THREADS + 32;
+constexpr int TC_THREADS_RES = TC_CONV_THREADS + 32;
 
 // FUSED = false compiles the plain epilogue only (fprop / dgrad without fusion keep their registers and schedule)
 template <bool FUSED>
-__global__ void __launch_bounds__(FUSED ? TC_THREADS_RES : TC_THREADS, 1)
+__global__ void __launch_bounds__(FUSED ? TC_THREADS_RES : TC_CONV_THREADS, 1)
 conv_tc_kernel(const __grid_constant__ TcConvParams p) {
   const bool fuse_add = FUSED && p.fuse_add;
   const bool fuse_stats = FUSED && p.fuse_stats;
@@ -78,9 +81,9 @@ conv_tc_kernel(const __grid_constant__ TcConvParams p) {
   uint8_t* epi_buf = smem + (size_t)p.stages * stage_bytes;                  // 2 x 16 KB
   uint8_t* res_buf = epi_buf + 2 * 16384;                                     // TC_RES_SLOTS x 16 KB (fused add)
   uint8_t* after_res = res_buf + (fuse_add ? TC_RES_SLOTS * 16384 : 0);
-  float* cs = reinterpret_cast<float*>(after_res);                            // 2 x [4 warps][32 column pairs][4] (fused stats)
-  float* pacc = cs + 1024;                                                    // [ncols_total][2]
-  uint8_t* after_stats = after_res + (fuse_stats ? 4096 + (size_t)p.ncols_total * 8 : 0);
+  float* cs = reinterpret_cast<float*>(after_res);                            // 2 x [8 warps][32 column pairs][4] (fused stats)
+  float* pacc = cs + 2048;                                                    // [ncols_total][2]
+  uint8_t* after_stats = after_res + (fuse_stats ? 8192 + (size_t)p.ncols_total * 8 : 0);
   uint64_t* bars = reinterpret_cast<uint64_t*>(after_stats);
   uint64_t* full = bars;                  // [stages]
   uint64_t* empty = bars + p.stages;      // [stages]
@@ -93,8 +96,8 @@ conv_tc_kernel(const __grid_constant__ TcConvParams p) {
   const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
   if (warp == 0 && lane == 0) {
     for (int i = 0; i < p.stages; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], 4); }
-    for (int i = 0; i < TC_RES_SLOTS; ++i) { mbar_init(&rfull[i], 1); mbar_init(&rempty[i], 4); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], TC_EPI_WARPS); }
+    for (int i = 0; i < TC_RES_SLOTS; ++i) { mbar_init(&rfull[i], 1); mbar_init(&rempty[i], TC_EPI_WARPS); }
     fence_barrier_init();
     tma_prefetch_desc(&p.a_map[0]);
     tma_prefetch_desc(&p.b_map);
@@ -105,8 +108,8 @@ conv_tc_kernel(const __grid_constant__ TcConvParams p) {
     tmem_alloc(tmem_slot, p.tmem_cols);
     tmem_relinquish();
   }
-  if (fuse_stats && warp >= 2 && warp < 6)
-    for (int i = threadIdx.x - 64; i < 2 * p.ncols_total; i += 128) pacc[i] = 0.f;
+  if (fuse_stats && warp >= 2 && warp < 2 + TC_EPI_WARPS)
+    for (int i = threadIdx.x - 64; i < 2 * p.ncols_total; i += TC_EPI_THREADS) pacc[i] = 0.f;
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -217,11 +220,14 @@ conv_tc_kernel(const __grid_constant__ TcConvParams p) {
       }
       if (++acc == p.tstages) { acc = 0; acc_phase ^= 1; }
     }
-  } else if (warp < 6) {
-    // ===================== epilogue (warps 2..5) =====================
+  } else if (warp < 2 + TC_EPI_WARPS) {
+    // ===================== epilogue (warps 2..9) =====================
+    // Two warps per TMEM lane quadrant: a thread owns one pixel row and HALF of each 64-channel store group.
     const int quad = warp & 3;                      // TMEM lane quadrant this warp may access
+    const int half = (warp - 2) >> 2;               // which 32 channels of a 64-channel group
+    const int ew = warp - 2;                        // 0..7
     const int row = quad * 32 + lane;
-    const int te = threadIdx.x - 64;                // 0..127
+    const int te = threadIdx.x - 64;                // 0..255
     const int box_rows = p.BW * p.BH * p.BN;
     int acc = 0;
     uint32_t acc_phase = 0;
@@ -230,15 +236,16 @@ conv_tc_kernel(const __grid_constant__ TcConvParams p) {
     uint32_t rphase = 0;
     int csb = 0, pend_col = -1;                     // fused statistics: cs buffer in use, column base awaiting its combine
     const int groups = p.block_n / p.gw;
-    // Fused statistics, second half: add the four row-quarter sums of the PREVIOUS store group (written to
-    // cs[csb ^ 1] before that group's second barrier) into the CTA's running per-channel totals.  Thread te owns
-    // (column te & 63, statistic te >> 6); fixed quarter order.
+    // Fused statistics, second half: add the eight partial sums of the PREVIOUS store group (cs[csb ^ 1], written
+    // before this group's first barrier) into the CTA's running per-channel totals.  Thread te < 128 owns
+    // (column te & 63, statistic te >> 6); fixed order.
     auto combine = [&](int col0, int which) {
-      const float* c = cs + which * 512;
+      if (te >= 128) return;
+      const float* c = cs + which * 1024;
       const int col = te & 63, st = te >> 6;
       float v = 0.f;
 #pragma unroll
-      for (int q = 0; q < 4; ++q) v += c[(q * 32 + (col >> 1)) * 4 + st * 2 + (col & 1)];
+      for (int q = 0; q < TC_EPI_WARPS; ++q) v += c[(q * 32 + (col >> 1)) * 4 + st * 2 + (col & 1)];
       pacc[(col0 + col) * 2 + st] += v;
     };
     for (int t = blockIdx.x; t < total; t += gridDim.x) {
@@ -254,7 +261,7 @@ conv_tc_kernel(const __grid_constant__ TcConvParams p) {
         mt /= p.tiles_w;
         const int h0 = (mt % p.tiles_h) * p.BH;
         const int n0 = (mt / p.tiles_h) * p.BN;
-        // rows of this warp whose output pixel exists: a k > 1 convolution produces non-zero values for
+        // rows of this quadrant whose output pixel exists: a k > 1 convolution produces non-zero values for
         // pixels just outside the image (TMA clips them on store; the statistics must skip them too)
         uint32_t row_mask = 0;
         if (fuse_stats) {
@@ -265,34 +272,29 @@ conv_tc_kernel(const __grid_constant__ TcConvParams p) {
         for (int g = 0; g < groups; ++g) {
           const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) +
                                  (uint32_t)((acc * p.acc_m + j) * p.block_n + g * p.gw);
-          // 64-column groups: both 32-column TMEM loads are issued before waiting for the staging buffer, so
-          // their latency overlaps the barrier; then one wait, 8 x (4 cvt + one 128-bit shared store)
-          uint32_t va[32], vb[32];
-          if (p.gw == 64) {
-            tmem_ld_32x32(taddr, va);
-            tmem_ld_32x32(taddr + 32, vb);
-          }
+          // 64-column groups: the TMEM load is issued before waiting for the staging buffer, so its latency
+          // overlaps the barrier; then one wait, 4 x (4 cvt + one 128-bit shared store)
+          uint32_t va[32];
+          if (p.gw == 64) tmem_ld_32x32(taddr + half * 32, va);
           // the TMA store that last read this staging buffer must have finished reading it
           if (warp == 2) {
             if (elect_one()) tma_store_wait_read<1>();
             __syncwarp();
           }
-          asm volatile("bar.sync 1, 128;" ::: "memory");
+          asm volatile("bar.sync 1, 256;" ::: "memory");
           uint8_t* sb = epi_buf + buf * 16384;
           if (p.gw == 64) {
             if (fuse_stats && pend_col >= 0) combine(pend_col, csb ^ 1);
             tmem_ld_wait();
-            const uint32_t rbase = (uint32_t)row * 128u;
+            const uint32_t rbase = (uint32_t)row * 128u + (uint32_t)half * 64u;
             const uint8_t* rb = res_buf + rslot * 16384;
             if (fuse_add) mbar_wait(&rfull[rslot], rphase);
 #pragma unroll
-            for (int c = 0; c < 8; ++c) {
+            for (int c = 0; c < 4; ++c) {
               uint32_t pk[4];
 #pragma unroll
               for (int i = 0; i < 4; ++i) {
-                const uint32_t lo = c < 4 ? va[8 * c + 2 * i] : vb[8 * (c - 4) + 2 * i];
-                const uint32_t hi = c < 4 ? va[8 * c + 2 * i + 1] : vb[8 * (c - 4) + 2 * i + 1];
-                __nv_bfloat162 h = __floats2bfloat162_rn(__uint_as_float(lo), __uint_as_float(hi));
+                __nv_bfloat162 h = __floats2bfloat162_rn(__uint_as_float(va[8 * c + 2 * i]), __uint_as_float(va[8 * c + 2 * i + 1]));
                 pk[i] = *reinterpret_cast<uint32_t*>(&h);
               }
               const uint32_t so = swizzle_offset(rbase + 16u * c, 128);
@@ -315,43 +317,25 @@ conv_tc_kernel(const __grid_constant__ TcConvParams p) {
               if (lane == 0) mbar_arrive(&rempty[rslot]);
               if (++rslot == TC_RES_SLOTS) { rslot = 0; rphase ^= 1; }
             }
-            if (fuse_stats) {
-              // first half: this warp re-reads the 32 rows it just wrote, one column pair per lane (a row is the
-              // 32 lanes' 128 bytes: conflict-free under the swizzle), and sums value / value^2 of the STORED bf16
-              __syncwarp();
-              float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
+          } else if (half == 0) {
+            for (int c0 = 0; c0 < p.gw; c0 += 16) {
+              uint32_t v[16];
+              tmem_ld_32x16(taddr + c0, v);
+              tmem_ld_wait();
+              uint32_t pk[8];
 #pragma unroll
-              for (int r = 0; r < 32; ++r) {
-                // all 32 loads independent; rows outside the tensor contribute +0 (they may hold anything)
-                uint32_t w = *reinterpret_cast<const uint32_t*>(
-                    sb + swizzle_offset((uint32_t)(quad * 32 + r) * 128u + (uint32_t)lane * 4u, 128));
-                w = ((row_mask >> r) & 1u) ? w : 0u;
-                const float f0 = __uint_as_float(w << 16), f1 = __uint_as_float(w & 0xffff0000u);
-                s0 += f0; s1 += f1;
-                q0 = fmaf(f0, f0, q0); q1 = fmaf(f1, f1, q1);
+              for (int i = 0; i < 8; ++i) {
+                __nv_bfloat162 h = __floats2bfloat162_rn(__uint_as_float(v[2 * i]), __uint_as_float(v[2 * i + 1]));
+                pk[i] = *reinterpret_cast<uint32_t*>(&h);
               }
-              *reinterpret_cast<float4*>(cs + csb * 512 + (quad * 32 + lane) * 4) = make_float4(s0, s1, q0, q1);
-              pend_col = nt * p.block_n + g * 64;
-              csb ^= 1;
+              // 16 channels = two 16-byte chunks of this row, XOR-swizzled like the TMA store expects
+              const uint32_t off0 = (uint32_t)row * row_bytes_out + (uint32_t)c0 * 2;
+              *reinterpret_cast<uint4*>(sb + swizzle_offset(off0, row_bytes_out)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+              *reinterpret_cast<uint4*>(sb + swizzle_offset(off0 + 16, row_bytes_out)) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
             }
-          } else
-          for (int c0 = 0; c0 < p.gw; c0 += 16) {
-            uint32_t v[16];
-            tmem_ld_32x16(taddr + c0, v);
-            tmem_ld_wait();
-            uint32_t pk[8];
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-              __nv_bfloat162 h = __floats2bfloat162_rn(__uint_as_float(v[2 * i]), __uint_as_float(v[2 * i + 1]));
-              pk[i] = *reinterpret_cast<uint32_t*>(&h);
-            }
-            // 16 channels = two 16-byte chunks of this row, XOR-swizzled like the TMA store expects
-            const uint32_t off0 = (uint32_t)row * row_bytes_out + (uint32_t)c0 * 2;
-            *reinterpret_cast<uint4*>(sb + swizzle_offset(off0, row_bytes_out)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-            *reinterpret_cast<uint4*>(sb + swizzle_offset(off0 + 16, row_bytes_out)) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
           }
           fence_proxy_async();
-          asm volatile("bar.sync 1, 128;" ::: "memory");
+          asm volatile("bar.sync 1, 256;" ::: "memory");
           if (warp == 2) {
             // the same (deterministically elected) lane issues, commits and later waits on the bulk stores
             if (elect_one()) {
@@ -360,6 +344,26 @@ conv_tc_kernel(const __grid_constant__ TcConvParams p) {
               tma_store_commit();
             }
             __syncwarp();
+          }
+          if (fuse_stats && p.gw == 64) {
+            // first half of the fused statistics: the staged group is complete (barrier above); this warp sums 16 of
+            // its quadrant's rows, one column pair per lane (a row is the 32 lanes' 128 bytes: conflict-free under
+            // the swizzle), value and value^2 of the STORED bf16.  All loads independent; rows outside the tensor
+            // contribute +0 (they may hold anything).
+            float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
+#pragma unroll
+            for (int r = 0; r < 16; ++r) {
+              const int rr = half * 16 + r;
+              uint32_t w = *reinterpret_cast<const uint32_t*>(
+                  sb + swizzle_offset((uint32_t)(quad * 32 + rr) * 128u + (uint32_t)lane * 4u, 128));
+              w = ((row_mask >> rr) & 1u) ? w : 0u;
+              const float f0 = __uint_as_float(w << 16), f1 = __uint_as_float(w & 0xffff0000u);
+              s0 += f0; s1 += f1;
+              q0 = fmaf(f0, f0, q0); q1 = fmaf(f1, f1, q1);
+            }
+            *reinterpret_cast<float4*>(cs + csb * 1024 + (ew * 32 + lane) * 4) = make_float4(s0, s1, q0, q1);
+            pend_col = nt * p.block_n + g * 64;
+            csb ^= 1;
           }
           buf ^= 1;
         }
@@ -371,19 +375,20 @@ conv_tc_kernel(const __grid_constant__ TcConvParams p) {
       if (++acc == p.tstages) { acc = 0; acc_phase ^= 1; }
     }
     if (fuse_stats) {
-      // last group's quarter sums, then this CTA's totals go to its row of the partial table (the finalize
+      // last group's partial sums, then this CTA's totals go to its row of the partial table (the finalize
       // kernel sums the <= 148 rows in fp64 in a fixed order)
-      if (pend_col >= 0) combine(pend_col, csb ^ 1);      // ordered after the last group's second barrier
-      asm volatile("bar.sync 1, 128;" ::: "memory");
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      if (pend_col >= 0) combine(pend_col, csb ^ 1);
+      asm volatile("bar.sync 1, 256;" ::: "memory");
       float* dst = p.stat_partials + (size_t)blockIdx.x * 2 * p.ncols_total;
-      for (int i = te; i < 2 * p.ncols_total; i += 128) dst[i] = pacc[i];
+      for (int i = te; i < 2 * p.ncols_total; i += TC_EPI_THREADS) dst[i] = pacc[i];
     }
     if (warp == 2) {
       if (elect_one()) tma_store_wait<0>();
       __syncwarp();
     }
   } else {
-    // ===================== residual-tile producer (warp 6; only launched with the fused add) =====================
+    // ===================== residual-tile producer (warp 10; only launched with the fused add) =====================
     const uint32_t rtx = (uint32_t)(p.BW * p.BH * p.BN) * 128u;
     const int groups = p.block_n / 64;
     int rslot = 0;
@@ -1024,7 +1029,7 @@ static int create_sub(const rn_conv_desc* d, int kind, const void* a, const void
   p.oW = oW; p.oH = oH; p.oN = d->N;
   p.stat_partials = stat_partials;
   const size_t fixed = 2 * 16384 + 1024 + 1024 + (p.fuse_add ? (size_t)TC_RES_SLOTS * 16384 : 0) +
-                       (p.fuse_stats ? 4096 + (size_t)ncols * 8 : 0);
+                       (p.fuse_stats ? 8192 + (size_t)ncols * 8 : 0);
   const size_t budget = 227 * 1024;
   int acc_m = 1;
   {
@@ -1265,9 +1270,9 @@ extern "C" int rn_convtc_run(rn_convtc_plan* plan, float beta, void* stream) {
     TcConvParams p = plan->p[i];
     p.accumulate = beta != 0.f ? 1 : 0;
     if (p.fuse_add || p.fuse_stats)
-      launch_pdl(conv_tc_kernel<true>, plan->grid[i], p.fuse_add ? TC_THREADS_RES : TC_THREADS, plan->smem_sub[i], st, p);
+      launch_pdl(conv_tc_kernel<true>, plan->grid[i], p.fuse_add ? TC_THREADS_RES : TC_CONV_THREADS, plan->smem_sub[i], st, p);
     else
-      launch_pdl(conv_tc_kernel<false>, plan->grid[i], TC_THREADS, plan->smem_sub[i], st, p);
+      launch_pdl(conv_tc_kernel<false>, plan->grid[i], TC_CONV_THREADS, plan->smem_sub[i], st, p);
     int rc = check_launch("conv_tc_kernel");
     if (rc) return rc;
   }
