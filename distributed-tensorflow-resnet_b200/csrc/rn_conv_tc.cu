@@ -454,7 +454,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_wgrad_tc_kernel(const __gr
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base_u32 = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* smem = smem_raw + (base_u32 - smem_u32(smem_raw));
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + (size_t)p.stages * p.stage_bytes);
+  uint8_t* epi_slab = smem + (size_t)p.stages * p.stage_bytes;                 // 4 epilogue warps x 4 KB
+  uint64_t* bars = reinterpret_cast<uint64_t*>(epi_slab + 16384);
   uint64_t* full = bars;
   uint64_t* empty = bars + p.stages;
   uint64_t* tfull = bars + 2 * p.stages;
@@ -587,7 +588,33 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_wgrad_tc_kernel(const __gr
         const int64_t grow = (int64_t)tap * p.Cin + cb * p.bwA + (row % p.bwA);
         float* dst = p.partial + ((int64_t)z * rows_total + grow) * p.Cout + (int64_t)nt * p.block_n;
         const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(a * p.block_n);
-        for (int c0 = 0; c0 < p.block_n; c0 += 16) {
+        // A thread holds one ROW of the accumulator; storing it directly would make every store instruction touch
+        // 32 different rows (32 half-used sectors).  The warp transposes 32 rows x 32 columns through its own 4 KB
+        // slab of shared memory (16-byte chunks XOR-swizzled by row) so that each store instruction writes four
+        // complete 128-byte lines.
+        uint8_t* slab = epi_slab + (warp - 2) * 4096;
+        const unsigned long long dst_u = reinterpret_cast<unsigned long long>(dst);
+        int c0 = 0;
+        for (; c0 + 32 <= p.block_n; c0 += 32) {
+          uint32_t v[32];
+          tmem_ld_32x32(taddr + c0, v);
+          tmem_ld_wait();
+          __syncwarp();                                  // the slab's previous contents have been read
+#pragma unroll
+          for (int c = 0; c < 8; ++c)
+            *reinterpret_cast<uint4*>(slab + lane * 128 + ((c ^ (lane & 7)) << 4)) =
+                make_uint4(v[4 * c], v[4 * c + 1], v[4 * c + 2], v[4 * c + 3]);
+          __syncwarp();
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const int r = i * 4 + (lane >> 3), c = lane & 7;
+            const uint4 val = *reinterpret_cast<const uint4*>(slab + r * 128 + ((c ^ (r & 7)) << 4));
+            const unsigned long long d = __shfl_sync(0xffffffffu, dst_u, r);
+            const int okr = __shfl_sync(0xffffffffu, (int)ok, r);
+            if (okr) *reinterpret_cast<uint4*>(reinterpret_cast<float*>(d) + c0 + 4 * c) = val;
+          }
+        }
+        for (; c0 < p.block_n; c0 += 16) {               // column tail (BLOCK_N a multiple of 16 only)
           uint32_t v[16];
           tmem_ld_32x16(taddr + c0, v);
           tmem_ld_wait();
@@ -905,7 +932,7 @@ static bool wgrad_shape(const rn_conv_desc* d, WgradShape* w) {
       const uint32_t abox = (uint32_t)kp * w->bwA * 2, bbox = (uint32_t)kp * w->bwB * 2;
       if (abox % 1024 || bbox % 1024) continue;            // swizzle atoms must stay 1024-byte aligned
       const size_t stage = (size_t)rbpc * abox + (size_t)nb * bbox;
-      const int stages = (int)((220 * 1024) / stage);
+      const int stages = (int)((204 * 1024) / stage);    // 227 KB - epilogue transpose slabs, barriers, alignment
       if (stages < 3) continue;
       const double ops = (double)rbpc / run + 1.0;
       const double macs = (double)acc * kp * w->block_n;
@@ -920,7 +947,7 @@ static bool wgrad_shape(const rn_conv_desc* d, WgradShape* w) {
   }
   if (!found) return false;
   w->row_groups = (w->RB + w->blocksA * w->acc - 1) / (w->blocksA * w->acc);
-  w->smem = (size_t)w->stages * w->stage_bytes + 2048;
+  w->smem = (size_t)w->stages * w->stage_bytes + 16384 + 2048;
   uint32_t cols = 32;
   while (cols < (uint32_t)(w->acc * w->block_n)) cols <<= 1;
   w->tmem_cols = cols;
