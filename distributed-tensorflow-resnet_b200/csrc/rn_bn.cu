@@ -690,7 +690,9 @@ static int bn_apply_launch(const void* x, void* y, int64_t M, int C, const float
                            const float* mean, const float* rstd, int moving, float eps, float leak, cudaStream_t st) {
   int rc = check_bn_args<T>(M, C);
   if (rc) return rc;
-  BnLayout L = bn_layout<T>(M, C, 8, bn_apply_cw(), 16384);
+  static int awaves = -1;
+  if (awaves < 0) { const char* e = getenv("RN_BN_APPLY_WAVES"); awaves = e ? atoi(e) : 8; }
+  BnLayout L = bn_layout<T>(M, C, awaves, bn_apply_cw(), 16384);
   launch_pdl(bn_apply_kernel<T>, dim3(L.G, L.gridY), BN_THREADS, 0, st, (const T*)x, (T*)y, M, C, L, gamma, beta, mean,
              rstd, moving, eps, leak);
   return check_launch("bn_apply_kernel");
@@ -763,7 +765,10 @@ static int bn_bwd_apply_launch(const void* dy, const void* x, void* dx, const vo
                                const float* dgamma, const float* dbeta, float leak, cudaStream_t st) {
   int rc = check_bn_args<T>(M, C);
   if (rc) return rc;
-  BnLayout L = bn_layout<T>(M, C, 8, bn_apply_cw(), 16384);
+  static int bwaves = -1, bkb = -1;
+  if (bwaves < 0) { const char* e = getenv("RN_BN_BWD_APPLY_WAVES"); bwaves = e ? atoi(e) : 3; }   // 80 registers: 3 resident CTAs per SM = one full wave
+  if (bkb < 0) { const char* e = getenv("RN_BN_BWD_APPLY_KB"); bkb = e ? atoi(e) : 16; }
+  BnLayout L = bn_layout<T>(M, C, bwaves, bn_apply_cw(), (int64_t)bkb * 1024);
   dim3 grid(L.G, L.gridY);
   if (addend)
     launch_pdl(bn_bwd_apply_kernel<T, true>, grid, BN_THREADS, 0, st, (const T*)dy, (const T*)x, (T*)dx,
