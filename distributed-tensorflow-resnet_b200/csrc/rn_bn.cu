@@ -691,7 +691,7 @@ static int bn_apply_launch(const void* x, void* y, int64_t M, int C, const float
   int rc = check_bn_args<T>(M, C);
   if (rc) return rc;
   static int awaves = -1;
-  if (awaves < 0) { const char* e = getenv("RN_BN_APPLY_WAVES"); awaves = e ? atoi(e) : 8; }
+  if (awaves < 0) { const char* e = getenv("RN_BN_APPLY_WAVES"); awaves = e ? atoi(e) : 4; }   // 56 registers: 4 resident CTAs per SM
   BnLayout L = bn_layout<T>(M, C, awaves, bn_apply_cw(), 16384);
   launch_pdl(bn_apply_kernel<T>, dim3(L.G, L.gridY), BN_THREADS, 0, st, (const T*)x, (T*)y, M, C, L, gamma, beta, mean,
              rstd, moving, eps, leak);
