@@ -610,39 +610,46 @@ using namespace rn;
 
 // Finalisation of statistics whose per-CTA sums were produced by a convolution epilogue
 // (rn_convtc_plan_create_fused): partials[nparts][C][2] = (sum, sum of squares) per channel.
-// A CTA handles 32 channels with 8 thread slices over the partial rows (fixed order, fp64).
+// A CTA handles 8 channels with 32 thread slices over the partial rows: every thread issues its <= 5 loads
+// (148 rows / 32 slices) at once, so the kernel is one memory round trip; slices are then combined in a fixed
+// order in fp64.
 namespace rn {
+constexpr int FIN_CH = 8, FIN_SLICES = 32;
 __global__ void __launch_bounds__(256)
 bn_finalize_kernel(const float* __restrict__ partials, int nparts, int64_t M, int C, float eps, float decay, int unbiased,
                    float* __restrict__ mean_out, float* __restrict__ rstd_out, float* moving_mean, float* moving_var) {
   pdl_trigger();
   pdl_wait();
-  __shared__ double sh[2][8][32];
-  const int cl = threadIdx.x % 32, slice = threadIdx.x / 32;
-  const int c = blockIdx.x * 32 + cl;
+  __shared__ double sh[2][FIN_SLICES][FIN_CH];
+  const int cl = threadIdx.x % FIN_CH, slice = threadIdx.x / FIN_CH;
+  const int c = blockIdx.x * FIN_CH + cl;
   double s = 0.0, q = 0.0;
   if (c < C) {
     const float2* p = reinterpret_cast<const float2*>(partials) + c;
     int z = slice;
-    for (; z + 24 < nparts; z += 32) {
-      const float2 a = __ldcg(p + (size_t)z * C), b = __ldcg(p + (size_t)(z + 8) * C);
-      const float2 d = __ldcg(p + (size_t)(z + 16) * C), e = __ldcg(p + (size_t)(z + 24) * C);
+    for (; z + 3 * FIN_SLICES < nparts; z += 4 * FIN_SLICES) {
+      const float2 a = __ldcg(p + (size_t)z * C), b = __ldcg(p + (size_t)(z + FIN_SLICES) * C);
+      const float2 d = __ldcg(p + (size_t)(z + 2 * FIN_SLICES) * C), e = __ldcg(p + (size_t)(z + 3 * FIN_SLICES) * C);
       s += (double)a.x; q += (double)a.y;
       s += (double)b.x; q += (double)b.y;
       s += (double)d.x; q += (double)d.y;
       s += (double)e.x; q += (double)e.y;
     }
-    for (; z < nparts; z += 8) {
-      const float2 a = __ldcg(p + (size_t)z * C);
-      s += (double)a.x; q += (double)a.y;
+    float2 t[3];
+#pragma unroll
+    for (int u = 0; u < 3; ++u) {
+      const int zz = z + u * FIN_SLICES;
+      t[u] = zz < nparts ? __ldcg(p + (size_t)zz * C) : make_float2(0.f, 0.f);
     }
+#pragma unroll
+    for (int u = 0; u < 3; ++u) { s += (double)t[u].x; q += (double)t[u].y; }
   }
   sh[0][slice][cl] = s;
   sh[1][slice][cl] = q;
   __syncthreads();
   if (slice == 0 && c < C) {
     double S = 0.0, Q = 0.0;
-    for (int j = 0; j < 8; ++j) { S += sh[0][j][cl]; Q += sh[1][j][cl]; }
+    for (int j = 0; j < FIN_SLICES; ++j) { S += sh[0][j][cl]; Q += sh[1][j][cl]; }
     const double mean = S / (double)M;
     double var = Q / (double)M - mean * mean;
     if (var < 0.0) var = 0.0;
@@ -664,7 +671,7 @@ extern "C" int rn_bn_finalize(const float* partials, int32_t nparts, int64_t M, 
   RN_REQUIRE(partials && mean && rstd && nparts > 0 && M > 0 && C > 0, "bn_finalize: bad arguments");
   RN_REQUIRE((moving_mean == nullptr) == (moving_var == nullptr), "bn_finalize: moving_mean/var must both be set or NULL");
   RN_REQUIRE(((uintptr_t)partials & 7) == 0, "bn_finalize: partials must be 8-byte aligned");
-  launch_pdl(rn::bn_finalize_kernel, (C + 31) / 32, 256, 0, rn::as_stream(stream), partials, (int)nparts, M, (int)C, eps,
+  launch_pdl(rn::bn_finalize_kernel, (C + rn::FIN_CH - 1) / rn::FIN_CH, 256, 0, rn::as_stream(stream), partials, (int)nparts, M, (int)C, eps,
              decay, (int)unbiased, mean, rstd, moving_mean, moving_var);
   return rn::check_launch("bn_finalize_kernel");
 }

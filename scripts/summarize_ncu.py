@@ -1,31 +1,62 @@
 """Summarise ncu outputs brought back in gpurun_out/ into small tracked files under profiles/.
 usage: python scripts/summarize_ncu.py <round tag> [launches.csv] [report.ncu-rep]"""
-import csv, subprocess, sys, collections, io, re
+import csv, subprocess, sys, collections, io, re, json
 tag = sys.argv[1]
 launches = sys.argv[2] if len(sys.argv) > 2 else "gpurun_out/launches.csv"
 rep = sys.argv[3] if len(sys.argv) > 3 else None
 rows = [r for r in csv.reader(l for l in open(launches) if not l.startswith("=="))]
 hdr = rows[0]
-ki, vi = hdr.index("Kernel Name"), hdr.index("Metric Value")
-agg = collections.OrderedDict()
+ii, ki, mi, vi = hdr.index("ID"), hdr.index("Kernel Name"), hdr.index("Metric Name"), hdr.index("Metric Value")
+ui = hdr.index("Metric Unit")
+# one record per launch ID: duration (ns) and, when collected, DRAM bytes
+launch = collections.OrderedDict()
 for r in rows[1:]:
     if len(r) <= vi:
         continue
     name = re.sub(r"\(.*", "", r[ki]).replace("void ", "").replace("rn::", "")
     name = re.sub(r"<.*", "", name)
-    t = float(r[vi].replace(",", ""))
-    a = agg.setdefault(name, [0, 0.0])
-    a[0] += 1; a[1] += t
+    rec = launch.setdefault(r[ii], dict(name=name, t=0.0, rd=0.0, wr=0.0))
+    v = float(r[vi].replace(",", ""))
+    scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "ns": 1.0, "us": 1e3, "ms": 1e6}.get(r[ui], 1.0)
+    if r[mi].startswith("gpu__time_duration"):
+        rec["t"] = v * scale
+    elif r[mi].startswith("dram__bytes_read"):
+        rec["rd"] = v * scale
+    elif r[mi].startswith("dram__bytes_write"):
+        rec["wr"] = v * scale
+seq = list(launch.values())
+# keep ONE training step: the launches between the last two optimizer kernels
+opt = [i for i, r in enumerate(seq) if r["name"].startswith("sgd_momentum")]
+if len(opt) >= 2:
+    seq = seq[opt[-2] + 1:opt[-1] + 1]
+agg = collections.OrderedDict()
+for r in seq:
+    a = agg.setdefault(r["name"], [0, 0.0, 0.0, 0.0])
+    a[0] += 1; a[1] += r["t"]; a[2] += r["rd"]; a[3] += r["wr"]
 tot = sum(a[1] for a in agg.values())
-unit = rows[1][hdr.index("Metric Unit")]
 with open("profiles/%s_launch_summary.md" % tag, "w") as f:
-    f.write("# %s: kernel launch list of one profiled window (ncu --metrics gpu__time_duration.sum --clock-control none)\n\n" % tag)
+    f.write("# %s: kernel launches of ONE training step (ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,"
+            "dram__bytes_write.sum --clock-control none, un-captured launch list)\n\n" % tag)
     f.write("Per-launch times under ncu are cold-cache and serialised: compare SHARES, not absolutes.\n\n")
-    f.write("| kernel | launches | total %s | share |\n|---|---:|---:|---:|\n" % unit)
-    for k, (c, t) in sorted(agg.items(), key=lambda kv: -kv[1][1]):
-        f.write("| %s | %d | %.1f | %.1f%% |\n" % (k, c, t, 100 * t / tot))
-    f.write("| **total** | %d | %.1f | 100%% |\n" % (sum(a[0] for a in agg.values()), tot))
+    f.write("| kernel | launches | total us | share | DRAM read MB / launch | DRAM write MB / launch |\n|---|---:|---:|---:|---:|---:|\n")
+    for k, (c, t, rd, wr) in sorted(agg.items(), key=lambda kv: -kv[1][1]):
+        f.write("| %s | %d | %.1f | %.1f%% | %.1f | %.1f |\n" % (k, c, t / 1e3, 100 * t / tot, rd / c / 1e6, wr / c / 1e6))
+    f.write("| **total** | %d | %.1f | 100%% | | |\n" % (sum(a[0] for a in agg.values()), tot / 1e3))
 print(open("profiles/%s_launch_summary.md" % tag).read())
+# DRAM bytes per launch by bench.py family name (roofline.traffic)
+fam = {"conv_wgrad_tc_kernel": "conv_wgrad_tc", "bn_bwd_reduce_kernel": "bn_bwd_reduce", "bn_bwd_apply_kernel": "bn_bwd_apply",
+       "bn_apply_kernel": "bn_apply", "bn_stats_kernel": "bn_stats", "sgd_momentum_kernel": "sgd_momentum_fused"}
+import json
+traffic = {}
+for k, (c, t, rd, wr) in agg.items():
+    if k in fam and rd + wr > 0:
+        traffic[fam[k]] = round((rd + wr) / c)
+if "conv_wgrad_tc" in traffic and "wgrad_reduce_kernel" in agg:      # the family's launch = GEMM + partial reduction
+    a = agg["wgrad_reduce_kernel"]
+    traffic["conv_wgrad_tc"] += round((a[2] + a[3]) / agg["conv_wgrad_tc_kernel"][0])
+if traffic:
+    json.dump(traffic, open("profiles/traffic.json", "w"), indent=1)
+    print("traffic.json", traffic)
 if rep:
     out = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
     rr = list(csv.reader(io.StringIO(out)))
