@@ -98,14 +98,15 @@ __device__ __forceinline__ float act_fn(float v, float leak) { return v < 0.f ? 
 // Contract: a kernel launched through launch_pdl() calls pdl_wait() before its first access to global
 // memory (it returns once the preceding kernel has completed and its writes are visible) and
 // pdl_trigger() as early as it likes.  Kernels launched the ordinary way are unaffected (a normal launch
-// still waits for full completion of everything before it).  Off by default: RN_PDL=1 turns the attribute on
-// (measured on B200 inside the captured step graph: no gain, 11.34 vs 11.38 ms).
+// still waits for full completion of everything before it).  RN_PDL=0 turns the attribute off.
+// Measured on B200 inside the captured step graph: ResNet-50 / ImageNet 10.16 -> 10.03 ms, ResNet-50 / CIFAR
+// (432 small kernels) 2.93 -> 2.68 ms.
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
 inline bool pdl_enabled() {
   static int v = -1;
-  if (v < 0) { const char* e = getenv("RN_PDL"); v = e ? (atoi(e) != 0) : 0; }
+  if (v < 0) { const char* e = getenv("RN_PDL"); v = e ? (atoi(e) != 0) : 1; }
   return v != 0;
 }
 
