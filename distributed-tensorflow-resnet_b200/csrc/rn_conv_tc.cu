@@ -299,15 +299,17 @@ conv_tc_kernel(const __grid_constant__ TcConvParams p) {
               }
               const uint32_t so = swizzle_offset(rbase + 16u * c, 128);
               if (fuse_add) {
-                // z = bf16(bf16(conv) + residual): the same two roundings as a stored conv output followed by the add
+                // z = bf16(bf16(conv) + residual): the same two roundings as a stored conv output followed by the
+                // add.  One packed bf16x2 add per channel pair: the sum of two bf16 values rounded once to bf16
+                // equals their fp32 sum rounded to bf16 (the fp32 add is exact unless one addend is below
+                // 2^-16 of the other, where both round to the larger one).
                 const uint4 rv = *reinterpret_cast<const uint4*>(rb + so);
                 const uint32_t rw[4] = {rv.x, rv.y, rv.z, rv.w};
 #pragma unroll
                 for (int i = 0; i < 4; ++i) {
-                  const float z0 = __uint_as_float(pk[i] << 16) + __uint_as_float(rw[i] << 16);
-                  const float z1 = __uint_as_float(pk[i] & 0xffff0000u) + __uint_as_float(rw[i] & 0xffff0000u);
-                  __nv_bfloat162 h = __floats2bfloat162_rn(z0, z1);
-                  pk[i] = *reinterpret_cast<uint32_t*>(&h);
+                  const __nv_bfloat162 h = __hadd2(*reinterpret_cast<const __nv_bfloat162*>(&pk[i]),
+                                                   *reinterpret_cast<const __nv_bfloat162*>(&rw[i]));
+                  pk[i] = *reinterpret_cast<const uint32_t*>(&h);
                 }
               }
               *reinterpret_cast<uint4*>(sb + so) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
@@ -350,17 +352,29 @@ conv_tc_kernel(const __grid_constant__ TcConvParams p) {
             // its quadrant's rows, one column pair per lane (a row is the 32 lanes' 128 bytes: conflict-free under
             // the swizzle), value and value^2 of the STORED bf16.  All loads independent; rows outside the tensor
             // contribute +0 (they may hold anything).
-            float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
+            float2 sv = make_float2(0.f, 0.f), qv = make_float2(0.f, 0.f);     // packed fp32x2 accumulators
+            const uint32_t hmask = (row_mask >> (half * 16)) & 0xffffu;
+            if (hmask == 0xffffu) {                                            // warp-uniform: all 16 rows exist
 #pragma unroll
-            for (int r = 0; r < 16; ++r) {
-              const int rr = half * 16 + r;
-              uint32_t w = *reinterpret_cast<const uint32_t*>(
-                  sb + swizzle_offset((uint32_t)(quad * 32 + rr) * 128u + (uint32_t)lane * 4u, 128));
-              w = ((row_mask >> rr) & 1u) ? w : 0u;
-              const float f0 = __uint_as_float(w << 16), f1 = __uint_as_float(w & 0xffff0000u);
-              s0 += f0; s1 += f1;
-              q0 = fmaf(f0, f0, q0); q1 = fmaf(f1, f1, q1);
+              for (int r = 0; r < 16; ++r) {
+                const uint32_t w = *reinterpret_cast<const uint32_t*>(
+                    sb + swizzle_offset((uint32_t)(quad * 32 + half * 16 + r) * 128u + (uint32_t)lane * 4u, 128));
+                const float2 f = make_float2(__uint_as_float(w << 16), __uint_as_float(w & 0xffff0000u));
+                sv = __fadd2_rn(sv, f);
+                qv = __ffma2_rn(f, f, qv);
+              }
+            } else {
+#pragma unroll
+              for (int r = 0; r < 16; ++r) {
+                uint32_t w = *reinterpret_cast<const uint32_t*>(
+                    sb + swizzle_offset((uint32_t)(quad * 32 + half * 16 + r) * 128u + (uint32_t)lane * 4u, 128));
+                w = ((hmask >> r) & 1u) ? w : 0u;
+                const float2 f = make_float2(__uint_as_float(w << 16), __uint_as_float(w & 0xffff0000u));
+                sv = __fadd2_rn(sv, f);
+                qv = __ffma2_rn(f, f, qv);
+              }
             }
+            const float s0 = sv.x, s1 = sv.y, q0 = qv.x, q1 = qv.y;
             *reinterpret_cast<float4*>(cs + csb * 1024 + (ew * 32 + lane) * 4) = make_float4(s0, s1, q0, q1);
             pend_col = nt * p.block_n + g * 64;
             csb ^= 1;
