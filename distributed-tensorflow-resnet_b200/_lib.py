@@ -56,6 +56,10 @@ SIGNATURES = {
     "rn_convtc_stat_rows": (C.c_int, [pdesc]),
     "rn_convtc_plan_create_fused": (C.c_int, [pdesc, vp, vp, vp, vp, vp, C.POINTER(i32), C.POINTER(vp)]),
     "rn_bn_finalize": (C.c_int, [vp, i32, C.c_int64, i32, f32, f32, i32, vp, vp, vp, vp, vp]),
+    "rn_convtc_fused_dgrad_supported": (C.c_int, [pdesc]),
+    "rn_convtc_plan_create_fused_dgrad": (C.c_int, [pdesc, vp, vp, vp, vp, vp, vp, vp, vp, f32, vp, C.POINTER(i32),
+                                                    C.POINTER(vp)]),
+    "rn_bn_bwd_finalize": (C.c_int, [vp, i32, i32, vp, vp, vp]),
     "rn_convtc_run": (C.c_int, [vp, f32, vp]),
     "rn_convtc_plan_destroy": (C.c_int, [vp]),
     "rn_weights_to_bf16": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, vp, vp, vp]),

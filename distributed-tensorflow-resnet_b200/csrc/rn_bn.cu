@@ -676,6 +676,52 @@ extern "C" int rn_bn_finalize(const float* partials, int32_t nparts, int64_t M, 
   return rn::check_launch("bn_finalize_kernel");
 }
 
+// dgamma / dbeta from the per-CTA sums a fused dgrad epilogue produced (rn_convtc_plan_create_fused_dgrad):
+// partials[nparts][C][2] = (sum g, sum g * xhat).  Same shape of work as bn_finalize_kernel.
+namespace rn {
+__global__ void __launch_bounds__(256)
+bn_bwd_finalize_kernel(const float* __restrict__ partials, int nparts, int C, float* __restrict__ dgamma,
+                       float* __restrict__ dbeta) {
+  pdl_trigger();
+  pdl_wait();
+  __shared__ double sh[2][FIN_SLICES][FIN_CH];
+  const int cl = threadIdx.x % FIN_CH, slice = threadIdx.x / FIN_CH;
+  const int c = blockIdx.x * FIN_CH + cl;
+  double s = 0.0, q = 0.0;
+  if (c < C) {
+    const float2* p = reinterpret_cast<const float2*>(partials) + c;
+    for (int z0 = slice; z0 < nparts; z0 += 4 * FIN_SLICES) {
+      float2 t[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int zz = z0 + u * FIN_SLICES;
+        t[u] = zz < nparts ? __ldcg(p + (size_t)zz * C) : make_float2(0.f, 0.f);
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) { s += (double)t[u].x; q += (double)t[u].y; }
+    }
+  }
+  sh[0][slice][cl] = s;
+  sh[1][slice][cl] = q;
+  __syncthreads();
+  if (slice == 0 && c < C) {
+    double S = 0.0, Q = 0.0;
+    for (int j = 0; j < FIN_SLICES; ++j) { S += sh[0][j][cl]; Q += sh[1][j][cl]; }
+    dbeta[c] = (float)S;
+    dgamma[c] = (float)Q;
+  }
+}
+}  // namespace rn
+
+extern "C" int rn_bn_bwd_finalize(const float* partials, int32_t nparts, int32_t C, float* dgamma, float* dbeta,
+                                  void* stream) {
+  RN_REQUIRE(partials && dgamma && dbeta && nparts > 0 && C > 0, "bn_bwd_finalize: bad arguments");
+  RN_REQUIRE(((uintptr_t)partials & 7) == 0, "bn_bwd_finalize: partials must be 8-byte aligned");
+  launch_pdl(rn::bn_bwd_finalize_kernel, (C + rn::FIN_CH - 1) / rn::FIN_CH, 256, 0, rn::as_stream(stream), partials,
+             (int)nparts, (int)C, dgamma, dbeta);
+  return rn::check_launch("bn_bwd_finalize_kernel");
+}
+
 extern "C" size_t rn_bn_scratch_bytes(int64_t M, int32_t C) { return bn_scratch_bytes(M, C); }
 
 extern "C" int rn_bn_stats_fwd(const void* x, const void* addend, void* sum_out, int64_t M, int32_t C, int32_t dtype,

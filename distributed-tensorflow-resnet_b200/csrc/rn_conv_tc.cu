@@ -57,6 +57,10 @@ struct TcConvParams {
   // fused epilogue (fprop, 64-channel store groups only)
   int fuse_stats;                 // per-channel sum / sum of squares of the STORED bf16 output -> stat_partials[CTA][ncols][2]
   int fuse_add;                   // OUT = bf16(bf16(result) + residual): the residual tile arrives through r_map (warp 6)
+  int fuse_bnbwd;                 // dgrad: the output is dy of a BN+ReLU whose input x arrives through r_map; the epilogue
+                                  // accumulates that BN's backward reductions (sum g, sum g*xhat; g = dy masked by the ReLU)
+  const float *bn_gamma, *bn_beta, *bn_mean, *bn_rstd;
+  float bn_leak;
   int ncols_total;
   int oW, oH, oN;                 // output extents (rows of a tile that fall outside are not part of the tensor)
   float* stat_partials;
@@ -72,7 +76,9 @@ template <bool FUSED>
 __global__ void __launch_bounds__(FUSED ? TC_THREADS_RES : TC_CONV_THREADS, 1)
 conv_tc_kernel(const __grid_constant__ TcConvParams p) {
   const bool fuse_add = FUSED && p.fuse_add;
-  const bool fuse_stats = FUSED && p.fuse_stats;
+  const bool fuse_bnbwd = FUSED && p.fuse_bnbwd;
+  const bool fuse_stats = FUSED && (p.fuse_stats || p.fuse_bnbwd);      // both keep per-channel running sums
+  const bool use_ring = fuse_add || fuse_bnbwd;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base_u32 = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* smem = smem_raw + (base_u32 - smem_u32(smem_raw));
@@ -80,10 +86,12 @@ conv_tc_kernel(const __grid_constant__ TcConvParams p) {
   const int row_bytes_out = p.gw * 2;
   uint8_t* epi_buf = smem + (size_t)p.stages * stage_bytes;                  // 2 x 16 KB
   uint8_t* res_buf = epi_buf + 2 * 16384;                                     // TC_RES_SLOTS x 16 KB (fused add)
-  uint8_t* after_res = res_buf + (fuse_add ? TC_RES_SLOTS * 16384 : 0);
+  uint8_t* after_res = res_buf + (use_ring ? TC_RES_SLOTS * 16384 : 0);
   float* cs = reinterpret_cast<float*>(after_res);                            // 2 x [8 warps][32 column pairs][4] (fused stats)
   float* pacc = cs + 2048;                                                    // [ncols_total][2]
-  uint8_t* after_stats = after_res + (fuse_stats ? 8192 + (size_t)p.ncols_total * 8 : 0);
+  float* ctab = pacc + 2 * p.ncols_total;                                     // [ncols_total][4] = a, b, mean, rstd (fused BN backward)
+  uint8_t* after_stats = after_res + (fuse_stats ? 8192 + (size_t)p.ncols_total * 8 : 0) +
+                         (fuse_bnbwd ? (size_t)p.ncols_total * 16 : 0);
   uint64_t* bars = reinterpret_cast<uint64_t*>(after_stats);
   uint64_t* full = bars;                  // [stages]
   uint64_t* empty = bars + p.stages;      // [stages]
@@ -102,7 +110,7 @@ conv_tc_kernel(const __grid_constant__ TcConvParams p) {
     tma_prefetch_desc(&p.a_map[0]);
     tma_prefetch_desc(&p.b_map);
     tma_prefetch_desc(&p.o_map);
-    if (fuse_add) tma_prefetch_desc(&p.r_map);
+    if (use_ring) tma_prefetch_desc(&p.r_map);
   }
   if (warp == 1) {
     tmem_alloc(tmem_slot, p.tmem_cols);
@@ -117,6 +125,15 @@ conv_tc_kernel(const __grid_constant__ TcConvParams p) {
   // everything above (barriers, TMEM, descriptor prefetch) overlapped the previous kernel's tail
   pdl_trigger();
   pdl_wait();
+  if (fuse_bnbwd && warp >= 2 && warp < 2 + TC_EPI_WARPS) {
+    // per-channel constants of the BN whose backward sums this dgrad accumulates (read by the epilogue warps only,
+    // ordered by their first named barrier)
+    for (int c = threadIdx.x - 64; c < p.ncols_total; c += TC_EPI_THREADS) {
+      const float rs = p.bn_rstd[c], mu = p.bn_mean[c];
+      const float a = p.bn_gamma[c] * rs;
+      *reinterpret_cast<float4*>(ctab + 4 * c) = make_float4(a, p.bn_beta[c] - mu * a, mu, rs);
+    }
+  }
 
   // work item = (group of acc_m consecutive pixel tiles, column tile); the acc_m tiles share each B tile
   const int m_tiles = p.tiles_w * p.tiles_h * p.tiles_n;
@@ -347,7 +364,39 @@ conv_tc_kernel(const __grid_constant__ TcConvParams p) {
             }
             __syncwarp();
           }
-          if (fuse_stats && p.gw == 64) {
+          if (fuse_bnbwd && p.gw == 64) {
+            // BN backward reductions of the staged dy group (barrier above): g = dy where the forward pre-activation
+            // a*x + b was >= 0, leak*dy elsewhere; sums of g and g*xhat over this warp's 16 rows, one channel pair
+            // per lane.  x comes from the tile ring (same swizzled layout as the staging buffer).
+            mbar_wait(&rfull[rslot], rphase);
+            const uint8_t* rb = res_buf + rslot * 16384;
+            const int cpair = nt * p.block_n + g * 64 + 2 * lane;
+            const float4 k0 = *reinterpret_cast<const float4*>(ctab + 4 * cpair);
+            const float4 k1 = *reinterpret_cast<const float4*>(ctab + 4 * cpair + 4);
+            const uint32_t hmask = (row_mask >> (half * 16)) & 0xffffu;
+            float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
+#pragma unroll
+            for (int r = 0; r < 16; ++r) {
+              const uint32_t so = swizzle_offset((uint32_t)(quad * 32 + half * 16 + r) * 128u + (uint32_t)lane * 4u, 128);
+              uint32_t wg = *reinterpret_cast<const uint32_t*>(sb + so);
+              uint32_t wx = *reinterpret_cast<const uint32_t*>(rb + so);
+              wg = ((hmask >> r) & 1u) ? wg : 0u;                  // rows outside the tensor contribute +0
+              wx = ((hmask >> r) & 1u) ? wx : 0u;                  // (rows past the pixel box are stale smem: 0 * NaN)
+              const float g0 = __uint_as_float(wg << 16), g1 = __uint_as_float(wg & 0xffff0000u);
+              const float x0 = __uint_as_float(wx << 16), x1 = __uint_as_float(wx & 0xffff0000u);
+              const float m0 = fmaf(x0, k0.x, k0.y) < 0.f ? p.bn_leak * g0 : g0;
+              const float m1 = fmaf(x1, k1.x, k1.y) < 0.f ? p.bn_leak * g1 : g1;
+              s0 += m0; s1 += m1;
+              q0 = fmaf(m0, (x0 - k0.z) * k0.w, q0);
+              q1 = fmaf(m1, (x1 - k1.z) * k1.w, q1);
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&rempty[rslot]);
+            if (++rslot == TC_RES_SLOTS) { rslot = 0; rphase ^= 1; }
+            *reinterpret_cast<float4*>(cs + csb * 1024 + (ew * 32 + lane) * 4) = make_float4(s0, s1, q0, q1);
+            pend_col = nt * p.block_n + g * 64;
+            csb ^= 1;
+          } else if (fuse_stats && p.gw == 64) {
             // first half of the fused statistics: the staged group is complete (barrier above); this warp sums 16 of
             // its quadrant's rows, one column pair per lane (a row is the 32 lanes' 128 bytes: conflict-free under
             // the swizzle), value and value^2 of the STORED bf16.  All loads independent; rows outside the tensor
@@ -1028,11 +1077,13 @@ extern "C" size_t rn_convtc_scratch_bytes(const rn_conv_desc* d, int kind) {
 // One GEMM sub-problem.  `oW,oH` and `ostr` describe the (possibly strided) view of the output that this
 // sub-problem writes; taps[] lists (map, dw, dh, weight tap).
 struct TapSpec { int8_t map, dw, dh, b; };
+// dgrad whose output is the dy of a BN+ReLU: the epilogue accumulates that BN's backward reductions
+struct BnBwdOpts { const void* x; const float *gamma, *beta, *mean, *rstd; float leak; };
 
 static int create_sub(const rn_conv_desc* d, int kind, const void* a, const void* b, const void* out_base,
                       int oW, int oH, const uint64_t* ostr, const TapSpec* taps, int ntaps, TcConvParams* pp,
                       int* grid, size_t* smem_bytes, const ActView* view = nullptr, int b_taps = 0,
-                      const void* residual = nullptr, float* stat_partials = nullptr) {
+                      const void* residual = nullptr, float* stat_partials = nullptr, const BnBwdOpts* bnbwd = nullptr) {
   TcConvParams& p = *pp;
   memset(&p, 0, sizeof(p));
   const int cred = kind == 0 ? d->Cin : d->Cout;
@@ -1062,15 +1113,24 @@ static int create_sub(const rn_conv_desc* d, int kind, const void* a, const void
   const long m_tiles = (long)p.tiles_w * p.tiles_h * p.tiles_n;
   // epilogue staging, barriers, alignment slack; fused epilogue: residual tile ring, statistics scratch
   const bool want_fused = residual != nullptr || stat_partials != nullptr;
-  if (want_fused && (kind != 0 || p.gw != 64))
-    return fail(RN_ERR_UNSUPPORTED, "convtc: the fused epilogue needs fprop and output channels in multiples of 64");
+  if (want_fused && p.gw != 64)
+    return fail(RN_ERR_UNSUPPORTED, "convtc: the fused epilogue needs output channels in multiples of 64");
+  if (bnbwd ? (kind != 1 || stat_partials == nullptr || residual != nullptr) : (want_fused && kind != 0))
+    return fail(RN_ERR_UNSUPPORTED, "convtc: fused add / statistics belong to fprop, fused BN backward sums to dgrad");
   p.fuse_add = residual != nullptr;
-  p.fuse_stats = stat_partials != nullptr;
+  p.fuse_bnbwd = bnbwd != nullptr;
+  p.fuse_stats = stat_partials != nullptr && !bnbwd;
+  if (bnbwd) {
+    residual = bnbwd->x;                     // the BN input rides the residual-tile ring
+    p.bn_gamma = bnbwd->gamma; p.bn_beta = bnbwd->beta; p.bn_mean = bnbwd->mean; p.bn_rstd = bnbwd->rstd;
+    p.bn_leak = bnbwd->leak;
+  }
   p.ncols_total = ncols;
   p.oW = oW; p.oH = oH; p.oN = d->N;
   p.stat_partials = stat_partials;
-  const size_t fixed = 2 * 16384 + 1024 + 1024 + (p.fuse_add ? (size_t)TC_RES_SLOTS * 16384 : 0) +
-                       (p.fuse_stats ? 8192 + (size_t)ncols * 8 : 0);
+  const size_t fixed = 2 * 16384 + 1024 + 1024 + ((p.fuse_add || p.fuse_bnbwd) ? (size_t)TC_RES_SLOTS * 16384 : 0) +
+                       ((p.fuse_stats || p.fuse_bnbwd) ? 8192 + (size_t)ncols * 8 : 0) +
+                       (p.fuse_bnbwd ? (size_t)ncols * 16 : 0);
   const size_t budget = 227 * 1024;
   int acc_m = 1;
   {
@@ -1128,7 +1188,7 @@ static int create_sub(const rn_conv_desc* d, int kind, const void* a, const void
     const uint32_t box[4] = {(uint32_t)p.gw, (uint32_t)p.BW, (uint32_t)p.BH, (uint32_t)p.BN};
     rc = encode_map(&p.o_map, out_base, 4, dims, ostr, box, p.gw * 2, "output");
     if (rc) return rc;
-    if (p.fuse_add) {
+    if (p.fuse_add || p.fuse_bnbwd) {
       rc = encode_map(&p.r_map, residual, 4, dims, ostr, box, p.gw * 2, "residual");
       if (rc) return rc;
     }
@@ -1282,6 +1342,45 @@ extern "C" int rn_convtc_plan_create_fused(const rn_conv_desc* d, const void* x,
   return RN_OK;
 }
 
+extern "C" int rn_convtc_fused_dgrad_supported(const rn_conv_desc* d) {
+  if (!rn_convtc_supported(d, 1) || d->stride != 1) return 0;
+  const int bn_ = choose_block_n(d->Cin);
+  return (bn_ % 64 == 0 && d->Cin <= 1024) ? 1 : 0;
+}
+
+extern "C" int rn_convtc_plan_create_fused_dgrad(const rn_conv_desc* d, const void* dy, const void* w_bf16, void* dx,
+                                                 const void* bn_x, const float* gamma, const float* beta,
+                                                 const float* mean, const float* rstd, float leak,
+                                                 float* sum_partials, int32_t* rows, rn_convtc_plan** plan) {
+  RN_REQUIRE(d && dy && w_bf16 && dx && bn_x && gamma && beta && mean && rstd && sum_partials && plan,
+             "convtc_plan_create_fused_dgrad: NULL pointer");
+  if (!rn_convtc_fused_dgrad_supported(d))
+    return fail(RN_ERR_UNSUPPORTED, "convtc: fused BN-backward dgrad not supported for this shape");
+  RN_REQUIRE((((uintptr_t)dy | (uintptr_t)w_bf16 | (uintptr_t)dx | (uintptr_t)bn_x) & 15) == 0,
+             "convtc: pointers must be 16-byte aligned");
+  cudaError_t e = set_conv_tc_smem_attr();
+  if (e != cudaSuccess) return fail(RN_ERR_CUDA, "convtc: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+  rn_convtc_plan* pl = new rn_convtc_plan();
+  memset(pl, 0, sizeof(*pl));
+  pl->kind = 1;
+  pl->nsub = 1;
+  TapSpec taps[TC_MAX_TAPS];
+  for (int r = 0; r < d->k; ++r)
+    for (int s = 0; s < d->k; ++s) {
+      TapSpec& t = taps[r * d->k + s];
+      t.b = (int8_t)(r * d->k + s);
+      t.map = 0; t.dw = (int8_t)(d->pad - s); t.dh = (int8_t)(d->pad - r);
+    }
+  const uint64_t ostr[3] = {(uint64_t)d->Cin * 2, (uint64_t)d->W * d->Cin * 2, (uint64_t)d->H * d->W * d->Cin * 2};
+  const BnBwdOpts o = {bn_x, gamma, beta, mean, rstd, leak};
+  const int rc = create_sub(d, 1, dy, w_bf16, dx, d->W, d->H, ostr, taps, d->k * d->k, &pl->p[0], &pl->grid[0],
+                            &pl->smem_sub[0], nullptr, 0, nullptr, sum_partials, &o);
+  if (rc) { delete pl; return rc; }
+  if (rows) *rows = pl->grid[0];
+  *plan = pl;
+  return RN_OK;
+}
+
 extern "C" int rn_convtc_run(rn_convtc_plan* plan, float beta, void* stream) {
   RN_REQUIRE(plan, "convtc_run: NULL plan");
   RN_REQUIRE(beta == 0.f || beta == 1.f, "convtc_run: beta must be 0 or 1");
@@ -1301,7 +1400,7 @@ extern "C" int rn_convtc_run(rn_convtc_plan* plan, float beta, void* stream) {
     }
     return rc;
   }
-  if (beta != 0.f && (plan->p[0].fuse_add || plan->p[0].fuse_stats))
+  if (beta != 0.f && (plan->p[0].fuse_add || plan->p[0].fuse_stats || plan->p[0].fuse_bnbwd))
     return fail(RN_ERR_UNSUPPORTED, "convtc_run: a plan with a fused epilogue overwrites its output (beta must be 0)");
   if (beta == 0.f && plan->clear_ptr) {
     cudaError_t e = cudaMemsetAsync(plan->clear_ptr, 0, plan->clear_bytes, st);
@@ -1310,8 +1409,9 @@ extern "C" int rn_convtc_run(rn_convtc_plan* plan, float beta, void* stream) {
   for (int i = 0; i < plan->nsub; ++i) {
     TcConvParams p = plan->p[i];
     p.accumulate = beta != 0.f ? 1 : 0;
-    if (p.fuse_add || p.fuse_stats)
-      launch_pdl(conv_tc_kernel<true>, plan->grid[i], p.fuse_add ? TC_THREADS_RES : TC_CONV_THREADS, plan->smem_sub[i], st, p);
+    if (p.fuse_add || p.fuse_stats || p.fuse_bnbwd)
+      launch_pdl(conv_tc_kernel<true>, plan->grid[i], (p.fuse_add || p.fuse_bnbwd) ? TC_THREADS_RES : TC_CONV_THREADS,
+                 plan->smem_sub[i], st, p);
     else
       launch_pdl(conv_tc_kernel<false>, plan->grid[i], TC_CONV_THREADS, plan->smem_sub[i], st, p);
     int rc = check_launch("conv_tc_kernel");

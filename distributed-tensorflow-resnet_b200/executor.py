@@ -679,10 +679,16 @@ class Executor:
             mean_p, rstd_p = n.saved[0].data_ptr(), n.saved[1].data_ptr()
             gp, bp = self._wptr(v["gamma"]), self._wptr(v["beta"])
             dgp, dbp = self._wptr(v["gamma"], "G"), self._wptr(v["beta"], "G")
-            self._emit(bwd, "bn_bwd_reduce:" + a["scope"],
-                       lambda s, args=(ptr(dy), ptr(x.buf), M, C_, self.rn_dt, gp, bp, mean_p, rstd_p, a["leak"], dgp, dbp):
-                       check(lib.rn_bn_act_bwd_reduce(*args, ptr(self.scratch), self.scratch_bytes, s), "rn_bn_act_bwd_reduce"),
-                       node=n, dy=dy)
+            bf = getattr(n, "bwd_from", None)
+            if bf is not None:
+                self._emit(bwd, "bn_bwd_finalize:" + a["scope"],
+                           lambda s, args=(ptr(bf["partials"]), bf["nrows"], C_, dgp, dbp):
+                           check(lib.rn_bn_bwd_finalize(*args, s), "rn_bn_bwd_finalize"), node=n, dy=dy)
+            else:
+                self._emit(bwd, "bn_bwd_reduce:" + a["scope"],
+                           lambda s, args=(ptr(dy), ptr(x.buf), M, C_, self.rn_dt, gp, bp, mean_p, rstd_p, a["leak"], dgp, dbp):
+                           check(lib.rn_bn_act_bwd_reduce(*args, ptr(self.scratch), self.scratch_bytes, s), "rn_bn_act_bwd_reduce"),
+                           node=n, dy=dy)
             if x.requires_grad:
                 dxb, beta = self._target(x, done, bwd)
                 addp = ptr(dxb) if beta != 0.0 else None
@@ -696,7 +702,28 @@ class Executor:
             kv = n.vars["kernel"]
             if x.requires_grad:
                 dxb, beta = self._target(x, done, bwd)
-                if self._conv_impl(n, 1) == "tc":
+                bn = x.producer
+                if (beta == 0.0 and self.bf16 and self._conv_impl(n, 1) == "tc" and bn is not None and bn.op == "bn_act"
+                        and bn.attrs["is_training"] and len(x.consumers) == 1 and hasattr(bn, "saved")
+                        and not os.environ.get("RN_NO_BNBWD_FUSION")
+                        and lib.rn_convtc_fused_dgrad_supported(C.byref(d))):
+                    # this dgrad produces the complete incoming gradient of a BN+ReLU: its epilogue also accumulates
+                    # that BN's backward reductions, so the BN needs no pass over (dy, x) before its dx kernel
+                    rows = lib.rn_convtc_stat_rows(C.byref(d))
+                    part = torch.zeros(rows, d.Cin, 2, dtype=torch.float32, device=self.dev)
+                    nrows = C.c_int32(0)
+                    plan = C.c_void_p()
+                    bv = bn.vars
+                    check(lib.rn_convtc_plan_create_fused_dgrad(
+                        C.byref(d), ptr(dy), self._wptr(kv, "Wb"), ptr(dxb), ptr(bn.inputs[0].buf),
+                        self._wptr(bv["gamma"]), self._wptr(bv["beta"]), bn.saved[0].data_ptr(), bn.saved[1].data_ptr(),
+                        bn.attrs["leak"], ptr(part), C.byref(nrows), C.byref(plan)), "rn_convtc_plan_create_fused_dgrad")
+                    self._plans.append(plan)
+                    bn.bwd_from = dict(partials=part, nrows=nrows.value)
+                    self._emit(bwd, "conv_dgrad_tc:" + y.name,
+                               lambda s, p=plan: check(lib.rn_convtc_run(p, 0.0, s), "rn_convtc_run"),
+                               node=n, dy=dy, dx=dxb, beta=0.0)
+                elif self._conv_impl(n, 1) == "tc":
                     run = self._tc_plan(n, d, 1, dy, dxb)
                     self._emit(bwd, "conv_dgrad_tc:" + y.name, lambda s, run=run, beta=beta: run(s, beta=beta),
                                node=n, dy=dy, dx=dxb, beta=beta)

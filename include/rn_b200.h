@@ -100,6 +100,16 @@ int rn_convtc_stat_rows(const rn_conv_desc* d);
 int rn_convtc_plan_create_fused(const rn_conv_desc* d, const void* x, const void* w_bf16, void* out,
                                 const void* residual, float* stat_partials, int32_t* stat_rows,
                                 rn_convtc_plan** plan);
+/* dgrad whose output dx is the incoming gradient of a batch_norm_relu (resnet_model_official.py:41-50) that is
+ * read by this convolution only (stride 1, Cin a multiple of 64, <= 1024; beta must be 0 at run time): the
+ * epilogue also accumulates that BN's backward reductions — sum(g) and sum(g * xhat) with g = dx masked by the
+ * ReLU, xhat from bn_x / mean / rstd — one row [Cin][2] per CTA in sum_partials (rn_convtc_stat_rows bounds the
+ * rows); rn_bn_bwd_finalize turns them into dbeta / dgamma, replacing rn_bn_act_bwd_reduce's pass over dy and x. */
+int rn_convtc_fused_dgrad_supported(const rn_conv_desc* d);
+int rn_convtc_plan_create_fused_dgrad(const rn_conv_desc* d, const void* dy, const void* w_bf16, void* dx,
+                                      const void* bn_x, const float* gamma, const float* beta, const float* mean,
+                                      const float* rstd, float leak, float* sum_partials, int32_t* rows,
+                                      rn_convtc_plan** plan);
 int rn_convtc_run(rn_convtc_plan* plan, float beta, void* stream);
 int rn_convtc_plan_destroy(rn_convtc_plan* plan);
 /* Re-layout of the fp32 HWIO master weights into the two bf16 operand layouts above
@@ -153,6 +163,7 @@ size_t rn_bn_scratch_bytes(int64_t M, int32_t C);
  * (rn_convtc_plan_create_fused): same outputs and moving-average update as rn_bn_stats_fwd. */
 int rn_bn_finalize(const float* partials, int32_t nparts, int64_t M, int32_t C, float eps, float decay,
                    int32_t unbiased, float* mean, float* rstd, float* moving_mean, float* moving_var, void* stream);
+int rn_bn_bwd_finalize(const float* partials, int32_t nparts, int32_t C, float* dgamma, float* dbeta, void* stream);
 /* Training statistics.  If `addend` != NULL the statistics are of z = x + addend and z is written
  * to `sum_out` (the residual add fused into the statistics pass).  Writes mean[C], rstd[C]
  * (= 1/sqrt(biased_var + eps)) and, if moving_mean != NULL, updates

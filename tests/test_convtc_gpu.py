@@ -328,3 +328,72 @@ def test_convtc_fused_epilogue(case):
         assert rel_err(rstd.cpu().double(), 1.0 / torch.sqrt(v_ref + 1e-5)) < 1e-5
         assert rel_err(mm.cpu().double(), 0.1 * m_ref) < 1e-4
         assert rel_err(mv.cpu().double(), 0.9 + 0.1 * v_ref * M / (M - 1)) < 1e-5
+
+
+FUSED_DGRAD_CASES = [
+    # N, H, W, Cin, Cout, k, pad  (stride 1; dx has Cin channels = the BN's channels)
+    (4, 16, 16, 64, 64, 3, 1),
+    (8, 14, 14, 256, 256, 3, 1),
+    (2, 14, 14, 256, 64, 3, 1),        # pixel box 14x4x2: tile rows below the image are non-zero for k = 3
+    (4, 28, 28, 512, 128, 1, 0),       # dgrad of a bottleneck conv1: wide dx (two column tiles), short reduction
+    (3, 9, 11, 64, 128, 1, 0),         # ragged
+    (6, 7, 7, 1024, 256, 1, 0),        # four column tiles
+]
+
+
+@pytest.mark.parametrize("leak", [0.0, 0.1])
+@pytest.mark.parametrize("case", FUSED_DGRAD_CASES)
+def test_convtc_fused_dgrad_bn_backward_sums(case, leak):
+    """dgrad with the following batch-norm's backward reductions fused into the epilogue
+    (rn_convtc_plan_create_fused_dgrad + rn_bn_bwd_finalize): dx must be bit-identical to the plain dgrad,
+    dgamma / dbeta must match rn_bn_act_bwd_reduce run on that dx, and the oracle's BN backward."""
+    N, H, W, Cin, Cout, k, pad = case
+    g = torch.Generator().manual_seed(sum(case) + 11)
+    w = (torch.randn(k, k, Cin, Cout, generator=g) / (k * k * Cin) ** 0.5).to(BF)
+    dy = torch.randn(N, H, W, Cout, generator=g).to(BF)
+    xbn = torch.randn(N, H, W, Cin, generator=g).to(BF)            # the BN's input (its output fed this conv)
+    gamma = (1.0 + 0.1 * torch.randn(Cin, generator=g)).float()
+    beta = (0.1 * torch.randn(Cin, generator=g)).float()
+    M = N * H * W
+    x2 = xbn.double().reshape(M, Cin)
+    mean = x2.mean(0).float()
+    rstd = (1.0 / torch.sqrt(x2.var(0, unbiased=False) + 1e-5)).float()
+    d = ConvDesc(N, H, W, Cin, H, W, Cout, k, 1, pad, RN_BF16)
+    assert lib.rn_convtc_fused_dgrad_supported(C.byref(d)) == 1
+    DY, WB, XB = dev(dy), dev(w), dev(xbn)
+    G_, B_, MU, RS = dev(gamma), dev(beta), dev(mean), dev(rstd)
+    DX0 = torch.empty(N, H, W, Cin, dtype=BF, device="cuda")
+    plan = C.c_void_p()
+    check(lib.rn_convtc_plan_create(C.byref(d), 1, ptr(DY), ptr(WB), ptr(DX0), None, 0, C.byref(plan)), "plan")
+    check(lib.rn_convtc_run(plan, 0.0, stream()), "run")
+    lib.rn_convtc_plan_destroy(plan)
+    nb = lib.rn_bn_scratch_bytes(M, Cin)
+    sc = torch.zeros(nb, dtype=torch.uint8, device="cuda")
+    DG0, DB0 = torch.empty(Cin, device="cuda"), torch.empty(Cin, device="cuda")
+    check(lib.rn_bn_act_bwd_reduce(ptr(DX0), ptr(XB), M, Cin, RN_BF16, ptr(G_), ptr(B_), ptr(MU), ptr(RS), leak,
+                                   ptr(DG0), ptr(DB0), ptr(sc), nb, stream()), "reduce")
+    rows_cap = lib.rn_convtc_stat_rows(C.byref(d))
+    PART = torch.full((rows_cap, Cin, 2), float("nan"), dtype=torch.float32, device="cuda")
+    DX = torch.full((N, H, W, Cin), float("nan"), dtype=BF, device="cuda")
+    nrows = C.c_int32(0)
+    check(lib.rn_convtc_plan_create_fused_dgrad(C.byref(d), ptr(DY), ptr(WB), ptr(DX), ptr(XB), ptr(G_), ptr(B_), ptr(MU),
+                                                ptr(RS), leak, ptr(PART), C.byref(nrows), C.byref(plan)), "plan fused")
+    for _ in range(2):
+        check(lib.rn_convtc_run(plan, 0.0, stream()), "run fused")
+    DG, DB = torch.empty(Cin, device="cuda"), torch.empty(Cin, device="cuda")
+    check(lib.rn_bn_bwd_finalize(ptr(PART), nrows.value, Cin, ptr(DG), ptr(DB), stream()), "finalize")
+    torch.cuda.synchronize()
+    assert lib.rn_convtc_run(plan, 1.0, stream()) != 0
+    lib.rn_convtc_plan_destroy(plan)
+    assert torch.equal(DX, DX0)
+    # against the separate reduction kernel (same inputs, different summation order)
+    gd = DX0.double().reshape(M, Cin).cpu()
+    pre = torch.addcmul((beta - mean * (gamma * rstd)).float(), xbn.float().reshape(M, Cin), (gamma * rstd).float()).double()
+    gm = torch.where(pre < 0, leak * gd, gd)
+    xhat = (x2 - mean.double()) * rstd.double()
+    sb_ref, sg_ref = gm.sum(0), (gm * xhat).sum(0)
+    scale_b = max(float(gm.abs().sum(0).max()), 1e-30)
+    scale_g = max(float((gm * xhat).abs().sum(0).max()), 1e-30)
+    assert (DB.cpu().double() - sb_ref).abs().max().item() / scale_b < 1e-5
+    assert (DG.cpu().double() - sg_ref).abs().max().item() / scale_g < 1e-5
+    assert (DB - DB0).abs().max().item() / scale_b < 1e-5 and (DG - DG0).abs().max().item() / scale_g < 1e-5

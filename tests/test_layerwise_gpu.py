@@ -147,7 +147,7 @@ class Verifier:
                 # fp32 accumulation over up to 1.6 M pixels of products of (bf16) values
                 self.check(name, ex.var_view(node.vars["kernel"].name, "G"), net.param_grads["w"],
                            1e-4 if not self.bf16 else 2e-3)
-        elif fam in ("bn_bwd_reduce", "bn_bwd_apply"):
+        elif fam in ("bn_bwd_reduce", "bn_bwd_finalize", "bn_bwd_apply"):
             x, y = node.inputs[0], node.outputs[0]
             a, v = node.attrs, node.vars
             C = x.shape[-1]
@@ -163,7 +163,7 @@ class Verifier:
             g = dy.reshape(M, C)
             g = torch.where(pre < 0, a["leak"] * g, g)
             dbeta, dgamma = g.sum(0), (g * xhat).sum(0)
-            if fam == "bn_bwd_reduce":
+            if fam in ("bn_bwd_reduce", "bn_bwd_finalize"):
                 scale = max(float(g.abs().sum(0).max()), 1e-30)     # conditioning: sums of signed terms
                 e1 = (_d(ex.var_view(v["beta"].name, "G")) - dbeta).abs().max().item() / scale
                 e2 = (_d(ex.var_view(v["gamma"].name, "G")) - dgamma).abs().max().item() / max(float((g * xhat).abs().sum(0).max()), 1e-30)
