@@ -40,6 +40,34 @@ def test_cabi_argument_errors_without_gpu():
     assert lib.rn_sgd_momentum_fused(1, 1, 1, None, 100, None, 1, 1.0, 0.0, 0.9, 1, None, None, 0, None) == -1
 
 
+def test_fusion_support_predicates_on_the_c3_shapes():
+    """Which convolutions of ResNet-50 / 224x224 may carry a fused epilogue is pure host logic (no CUDA call):
+    fprop fusion needs 64-channel store groups, dgrad fusion additionally stride 1 and <= 1024 channels, the
+    space-to-depth stem a stride-2 conv over <= 4 channels with a 7x7 or 8x8 kernel."""
+    from distributed_tensorflow_resnet_b200._lib import lib, ConvDesc, RN_BF16, RN_F32
+    B = ctypes.byref
+
+    def desc(h, cin, cout, k, s, dt=RN_BF16):
+        ho = h // s
+        return ConvDesc(128, h, h, cin, ho, ho, cout, k, s, (k - 1) // 2, dt)
+    assert lib.rn_convtc_fused_supported(B(desc(56, 64, 256, 1, 1))) == 1         # conv3 + shortcut + statistics
+    assert lib.rn_convtc_fused_supported(B(desc(56, 64, 64, 3, 1))) == 1
+    assert lib.rn_convtc_fused_supported(B(desc(28, 256, 128, 3, 2))) == 1
+    assert lib.rn_convtc_fused_supported(B(desc(32, 16, 16, 3, 1))) == 0           # CIFAR width: 16-channel store groups
+    assert lib.rn_convtc_fused_supported(B(desc(56, 64, 64, 3, 1, RN_F32))) == 0   # fp32 verification mode: no tensor cores
+    assert lib.rn_convtc_fused_dgrad_supported(B(desc(56, 256, 64, 1, 1))) == 1    # dx = gradient of a 256-channel BN
+    assert lib.rn_convtc_fused_dgrad_supported(B(desc(14, 1024, 256, 1, 1))) == 1
+    assert lib.rn_convtc_fused_dgrad_supported(B(desc(7, 2048, 512, 1, 1))) == 0   # constants table would not fit
+    assert lib.rn_convtc_fused_dgrad_supported(B(desc(56, 128, 128, 3, 2))) == 0   # stride-2 dgrad: four sub-GEMMs
+    stem = ConvDesc(128, 224, 224, 3, 112, 112, 64, 7, 2, 3, RN_BF16)
+    assert lib.rn_stem_s2d_supported(B(stem)) == 1
+    h2, w2, t = ctypes.c_int32(), ctypes.c_int32(), ctypes.c_int32()
+    assert lib.rn_stem_s2d_geometry(B(stem), B(h2), B(w2), B(t)) == 0 and (h2.value, w2.value, t.value) == (115, 115, 4)
+    assert lib.rn_stem_s2d_supported(B(ConvDesc(128, 32, 32, 3, 32, 32, 16, 3, 1, 1, RN_BF16))) == 0   # CIFAR stem: unfold path
+    assert lib.rn_convtc_stat_rows(B(stem)) == 148
+    assert lib.rn_dense_bwd_scratch_bytes(128, 2048, 1001) > 0 and lib.rn_dense_bwd_scratch_bytes(8, 64, 10) == 0
+
+
 def _build(dataset, size, shape, classes):
     from distributed_tensorflow_resnet_b200 import graph as G, resnet_model_official as off
     g = G.reset_default_graph()
