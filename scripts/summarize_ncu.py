@@ -51,6 +51,18 @@ traffic = {}
 for k, (c, t, rd, wr) in agg.items():
     if k in fam and rd + wr > 0:
         traffic[fam[k]] = round((rd + wr) / c)
+# conv_tc_kernel serves fprop (before the loss kernel) and dgrad (after it); bench.py counts one launch per LAYER
+# (a stride-2 dgrad is four kernel launches), so divide the family's bytes by bench.py's launch count
+cut = next((i for i, r in enumerate(seq) if r["name"].startswith("softmax_xent")), None)
+if cut is not None:
+    try:
+        per_step = {k["kernel"]: k["launches"] for k in json.load(open("profiles/%s_bench_n1.json" % tag))["kernels"]}
+    except Exception:
+        per_step = {}
+    for famname, part in (("conv_fprop_tc", seq[:cut]), ("conv_dgrad_tc", seq[cut:])):
+        rs = [r for r in part if r["name"] == "conv_tc_kernel"]
+        if rs:
+            traffic[famname] = round(sum(r["rd"] + r["wr"] for r in rs) / per_step.get(famname, len(rs)))
 if "conv_wgrad_tc" in traffic and "wgrad_reduce_kernel" in agg:      # the family's launch = GEMM + partial reduction
     a = agg["wgrad_reduce_kernel"]
     traffic["conv_wgrad_tc"] += round((a[2] + a[3]) / agg["conv_wgrad_tc_kernel"][0])
