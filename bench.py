@@ -2,7 +2,7 @@
 """Benchmark of the synchronous data-parallel ResNet training step (BASELINE.json metric:
 ResNet-50 train images/sec at 1/2/4/8 B200; conv tensor-pipe utilisation).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload imagenet50|cifar50]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload imagenet50|cifar50|cifar20|wrn28_10]
 
 N > 1 is launched by the driver under torchrun (one rank per GPU, NCCL).  One "step" is one
 full training step (forward, backward, gradient all-reduce, fused update) on synthetic data.
@@ -26,6 +26,14 @@ WORKLOADS = {
                        desc="ResNet-50 v2 bottleneck [3,4,6,3], ImageNet-shape 224x224, 128 images/GPU (C3)"),
     "cifar50": dict(dataset="cifar10", size=32, classes=10, batch=128, wd=2e-4,
                     desc="cifar10_resnet_v2_generator(50) basic blocks, 32x32, 128 images/GPU (C2 net)"),
+    # upstream-style builders (HParams.num_residual_units given), SURVEY section 8 configs C1 and C4
+    "cifar20": dict(dataset="cifar10", size=32, classes=10, batch=128, wd=2e-4,
+                    upstream=dict(num_residual_units=3, use_bottleneck=False, relu_leakiness=0.1), filters=None,
+                    desc="upstream ResNet-20 (_residual units 3x3, filters 16/16/32/64), CIFAR-10, 128 images/GPU (C1)"),
+    "wrn28_10": dict(dataset="cifar100", size=32, classes=100, batch=128, wd=5e-4,
+                     upstream=dict(num_residual_units=4, use_bottleneck=False, relu_leakiness=0.1),
+                     filters=[16, 160, 320, 640],
+                     desc="upstream WRN-28-10 (filters 16/160/320/640), CIFAR-100, 128 images/GPU (C4)"),
 }
 # derived images/s from the reference README: ImageNet ResNet-50, 128/worker
 PUBLISHED = {("imagenet50", 1): 123.0, ("imagenet50", 8): 952.0, ("cifar50", 1): 1784.0}
@@ -186,7 +194,10 @@ def cpu_reference_step(workload, batch, steps, warmup, threads=None):
     g = torch.Generator().manual_seed(1000)
     x = torch.randn(batch, wl["size"], wl["size"], 3, generator=g)
     y = torch.eye(wl["classes"])[torch.randint(0, wl["classes"], (batch,), generator=g)]
-    net = ro.OfficialResNetV2(wl["dataset"], 50, wl["classes"], dtype=torch.float32, seed=0)
+    if wl.get("upstream"):
+        net = ro.UpstreamResNet(wl["classes"], filters=wl["filters"], dtype=torch.float32, seed=0, **wl["upstream"])
+    else:
+        net = ro.OfficialResNetV2(wl["dataset"], 50, wl["classes"], dtype=torch.float32, seed=0)
     tr = ro.Trainer(net, wl["wd"], "mom")
     times = []
     for i in range(warmup + steps):
@@ -249,8 +260,13 @@ def run_ours(args):
     labels = torch.empty(B, wl["classes"], dtype=torch.float32, device=dev)
     images.copy_(host_img)
     labels.copy_(host_lab)
-    hps = resnet_model.HParams(num_classes=wl["classes"], lrn_rate=0.1, weight_decay_rate=wl["wd"], optimizer='mom')
+    hkw = dict(num_classes=wl["classes"], lrn_rate=0.1, weight_decay_rate=wl["wd"], optimizer='mom')
+    if wl.get("upstream"):
+        hkw.update(batch_size=B, min_lrn_rate=1e-4, **wl["upstream"])
+    hps = resnet_model.HParams(**hkw)
     model = resnet_model.ResNet(hps, images, labels, 'train')
+    if wl.get("filters"):
+        model.filters = wl["filters"]
     model.build_graph()
     ex = model.executor
     model.lrn_rate = 0.1

@@ -964,10 +964,12 @@ static int box_width(int c) { return c % 64 == 0 ? 64 : (c % 32 == 0 ? 32 : (c %
 
 static bool wgrad_shape(const rn_conv_desc* d, WgradShape* w) {
   w->bwA = box_width(d->Cin);
-  w->bwB = box_width(d->Cout);
-  if (!w->bwA || !w->bwB) return false;
   w->block_n = choose_block_n(d->Cout);
-  if (w->block_n == 0 || w->block_n % w->bwB) return false;
+  if (w->block_n == 0) return false;
+  // dY boxes must tile one BLOCK_N column tile exactly: 320 / 640 output channels (WRN-28-10) run as BLOCK_N = 160
+  // = five 32-channel boxes, although the tensor itself would allow 64-channel boxes
+  w->bwB = box_width(w->block_n);
+  if (!w->bwA || !w->bwB || d->Cout % w->bwB) return false;
   w->n_tiles = d->Cout / w->block_n;
   w->blocksA = 128 / w->bwA;
   w->cin_blocks = d->Cin / w->bwA;

@@ -96,6 +96,8 @@ WGRAD_CASES = CASES[0:3] + CASES[3:7] + [CASES[11]] + [
     (8, 16, 16, 16, 32, 1, 1, 0),                # mixed box widths A=16, B=32
     (4, 32, 32, 160, 160, 3, 1, 1),              # WRN-28-10 width: 32-channel boxes, N = 160
     (4, 16, 16, 32, 64, 3, 1, 1),
+    (4, 16, 16, 160, 320, 3, 1, 1),              # WRN-28-10 stage 2: BLOCK_N = 160 of 320 columns, 32-channel dY boxes
+    (2, 8, 8, 640, 640, 3, 1, 1),                # WRN-28-10 stage 3
 ]
 
 
