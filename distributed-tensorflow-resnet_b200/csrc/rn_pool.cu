@@ -228,6 +228,49 @@ __global__ void avgpool_bwd_kernel(const TO* __restrict__ dy, TI* dx, int N, int
   }
 }
 
+// 8 output channels per thread (bf16 x; C / Cout / cb multiples of 8, so a group is either all padding or all data)
+template <typename TO>
+__global__ void avgpool_fwd_vec_kernel(const __nv_bfloat16* __restrict__ x, TO* __restrict__ y, int N, int H, int W, int C,
+                                       int k, int s, int Ho, int Wo, int Cout, int cb) {
+  const int CV = Cout / 8;
+  const int64_t total = (int64_t)N * Ho * Wo * CV;
+  const float inv = 1.f / (float)(k * k);
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int cg = (int)(i % CV);
+    int64_t p = i / CV;
+    const int wo = (int)(p % Wo);
+    p /= Wo;
+    const int ho = (int)(p % Ho);
+    const int n = (int)(p / Ho);
+    const int c = cg * 8 - cb;
+    float acc[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+    if (c >= 0 && c < C) {
+      for (int r = 0; r < k; ++r)
+        for (int q = 0; q < k; ++q) {
+          Vec<__nv_bfloat16> v;
+          float f[8];
+          v.load(x + (((int64_t)n * H + ho * s + r) * W + wo * s + q) * C + c);
+          v.unpack(f);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) acc[j] += f[j];
+        }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[j] *= inv;
+    }
+    if (sizeof(TO) == 4) {
+      float4* o = reinterpret_cast<float4*>(y + i * 8);
+      o[0] = make_float4(acc[0], acc[1], acc[2], acc[3]);
+      o[1] = make_float4(acc[4], acc[5], acc[6], acc[7]);
+    } else {
+      Vec<__nv_bfloat16> o;
+      o.pack(acc);
+      o.store(reinterpret_cast<__nv_bfloat16*>(y) + i * 8);
+    }
+  }
+}
+
 // 8 channels per thread (bf16 dx, C / Cout / cb multiples of 8): one 128-bit store per pixel x channel group
 template <typename TO>
 __global__ void avgpool_bwd_vec_kernel(const TO* __restrict__ dy, __nv_bfloat16* dx, int N, int H, int W, int C, int k,
@@ -333,6 +376,16 @@ extern "C" int rn_avgpool_fwd(const void* x, void* y, int32_t N, int32_t H, int3
   const int Ho = (H - k) / s + 1, Wo = (W - k) / s + 1;
   const int g = grid_for((int64_t)N * Ho * Wo * Cout, 256);
   cudaStream_t st = as_stream(stream);
+  if (idt == RN_BF16 && C % 8 == 0 && Cout % 8 == 0 && cb % 8 == 0 && (((uintptr_t)x | (uintptr_t)y) & 15) == 0 &&
+      (odt == RN_F32 || odt == RN_BF16)) {
+    const int gv = grid_for((int64_t)N * Ho * Wo * (Cout / 8), 256);
+    if (odt == RN_F32)
+      avgpool_fwd_vec_kernel<float><<<gv, 256, 0, st>>>((const __nv_bfloat16*)x, (float*)y, N, H, W, C, k, s, Ho, Wo, Cout, cb);
+    else
+      avgpool_fwd_vec_kernel<__nv_bfloat16><<<gv, 256, 0, st>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)y, N, H, W, C, k, s,
+                                                                Ho, Wo, Cout, cb);
+    return check_launch("avgpool_fwd_vec_kernel");
+  }
   if (idt == RN_F32 && odt == RN_F32)
     avgpool_fwd_kernel<float, float><<<g, 256, 0, st>>>((const float*)x, (float*)y, N, H, W, C, k, s, Ho, Wo, Cout, cb);
   else if (idt == RN_BF16 && odt == RN_F32)
