@@ -2,7 +2,11 @@
 """Benchmark of the synchronous data-parallel ResNet training step (BASELINE.json metric:
 ResNet-50 train images/sec at 1/2/4/8 B200; conv tensor-pipe utilisation).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload imagenet50|cifar50|cifar20|wrn28_10]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+                    [--workload imagenet50|cifar50|cifar20|wrn28_10] [--global-batch G] [--sustained-steps S]
+
+`--global-batch G` fixes the GLOBAL batch (per-GPU batch = G / N, "scaling": "strong") — BASELINE config 2, the
+reference's headline experiment: the CIFAR ResNet-50 at global batch 128 over 1/2/4/8 workers.
 
 N > 1 is launched by the driver under torchrun (one rank per GPU, NCCL).  One "step" is one
 full training step (forward, backward, gradient all-reduce, fused update) on synthetic data.
@@ -85,6 +89,15 @@ class ClockSampler(threading.Thread):
                 "reasons": reasons, "samples": len(self.samples)}
 
 
+def sources_digest():
+    """Digest of csrc/ + the header (what build.py stamps): ties an ncu-derived profiles/traffic.json to the code."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("_rn_build", os.path.join(ROOT, "distributed-tensorflow-resnet_b200", "build.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod.digest()
+
+
 def conv_flops(graph):
     """Algorithmic FLOPs: 2*N*Ho*Wo*Cout*k^2*Cin per GEMM; dgrad skipped where the
     input needs no gradient (the stem)."""
@@ -117,6 +130,11 @@ def hbm_bytes(name, ex, graph):
         return (4 if len(slot.members) > 1 else 3) * E * s
     if fam == "sgd_momentum_fused":
         return ex.n_flat * (20 + (2 if ex.bf16 else 0))
+    if fam == "cifar_decode":
+        # record bytes read + image (fp32 12,288 B / bf16 6,144 B) + one-hot (4*classes) written, per image
+        pipe = ex._bench_pipe
+        return pipe.B * (pipe.record_bytes + 3072 * (2 if pipe.images.dtype == __import__("torch").bfloat16 else 4)
+                         + 4 * pipe.classes)
     return None
 
 
@@ -124,6 +142,9 @@ def profile_step(ex, graph, iters=3):
     """Per-launch CUDA-event timing of the un-captured launch list (same stream the kernels run on)."""
     import torch
     lists = [("fwd", ex.fwd), ("bwd", ex.bwd), ("upd", ex.update)]
+    pipe = getattr(ex, "_bench_pipe", None)
+    if pipe is not None:       # the record decode runs once per step in front of the captured graph
+        lists.insert(0, ("input", [("cifar_decode:batch", lambda st_: pipe.next_batch())]))
     st = torch.cuda.current_stream()
     acc = {}
     for it in range(iters + 1):
@@ -143,7 +164,7 @@ def profile_step(ex, graph, iters=3):
     return {k: sum(v) / len(v) for k, v in acc.items()}
 
 
-def roofline_report(ex, graph, per_launch_ms, pk):
+def roofline_report(ex, graph, per_launch_ms, pk, clocks=None):
     cf = conv_flops(graph)
     fams = {}
     for name, ms in per_launch_ms.items():
@@ -172,15 +193,117 @@ def roofline_report(ex, graph, per_launch_ms, pk):
     top = next((r for r in table if "bound" in r), None)
     roof = None
     traffic = None
-    tp = os.path.join(ROOT, "profiles", "traffic.json")     # dram bytes per launch from the last ncu --set full capture
+    tensor_pipe = None
+    stale = None
+    tp = os.path.join(ROOT, "profiles", "traffic.json")     # per-launch DRAM bytes / tensor-pipe % from the ncu captures
     if top and os.path.exists(tp):
-        traffic = json.load(open(tp)).get(top["kernel"])
+        tj = json.load(open(tp))
+        if tj.get("sources_sha256") == sources_digest():
+            traffic = tj.get("dram_bytes_per_launch", {}).get(top["kernel"])
+            tensor_pipe = tj.get("tensor_pipe_pct")
+        else:
+            stale = "profiles/traffic.json was captured from other sources (digest mismatch): traffic not reported"
     if top:
-        roof = dict(kernel=top["kernel"], bound=top["bound"], achieved=top["achieved"],
-                    peak=pk["tf_sust"] if top["bound"] == "tensor" else pk["hbm"], unit=top["unit"], frac=top["frac"],
-                    traffic=traffic, peak_source=pk["src"] + (" sustained bf16" if top["bound"] == "tensor" else " copy"),
+        tensor = top["bound"] == "tensor"
+        # The per-launch times come from a short un-captured burst; which measured peak applies depends on the
+        # clock the GPU actually held (MEASURED_PEAKS: burst figure at max clock, sustained under a long load).
+        at_max = bool(clocks and clocks.get("sm_mhz") and clocks.get("sm_max_mhz") and
+                      clocks["sm_mhz"] >= 0.97 * clocks["sm_max_mhz"])
+        peak = (pk["tf_burst"] if at_max else pk["tf_sust"]) if tensor else pk["hbm"]
+        roof = dict(kernel=top["kernel"], bound=top["bound"], achieved=top["achieved"], peak=peak, unit=top["unit"],
+                    frac=round(top["achieved"] / peak, 4), traffic=traffic,
+                    peak_source=pk["src"] + ((" burst bf16 (SM clock at max during the timed region)" if at_max
+                                              else " sustained bf16") if tensor else " copy"),
                     share_of_step=top["share"], launches_per_step=top["launches"])
+        if tensor:
+            roof["frac_of_burst_peak"] = round(top["achieved"] / pk["tf_burst"], 4)
+            roof["frac_of_sustained_peak"] = round(top["achieved"] / pk["tf_sust"], 4)
+        if tensor_pipe:
+            roof["tensor_pipe_pct"] = tensor_pipe
+        if stale:
+            roof["traffic_note"] = stale
     return roof, table, total
+
+
+def ddp_check(ex, model, world, rank, dev):
+    """Values, not just speed, at N > 1: (1) after the timed steps every rank holds bit-identical
+    weights, momentum and BN moving statistics... of the replicas that must agree: W and Mom (BN statistics are
+    rank-local by design, the reference has no sync-BN); (2) two steps of a tiny net (CIFAR ResNet-8, fp32) equal
+    the CPU oracle's step on the MEAN of the R per-replica gradients (SyncReplicasOptimizer / Horovod semantics,
+    models/resnet_model.py:104-120), on both the eager and the segmented-CUDA-graph path; (3) a checkpoint written
+    by the chief and resumed on every rank leaves all ranks on identical weights and the same global_step."""
+    import tempfile
+    import torch
+    import torch.distributed as dist
+    from distributed_tensorflow_resnet_b200 import resnet_model, FLAGS, train_utils
+    out = {}
+
+    def same_everywhere(t):
+        h = torch.stack([t.view(torch.int32).to(torch.int64).sum(), t.double().abs().sum().view(torch.int64)])
+        g = [torch.empty_like(h) for _ in range(world)]
+        dist.all_gather(g, h)
+        return all(torch.equal(g[0], x) for x in g)
+
+    out["ranks_identical"] = bool(same_everywhere(ex.W) and same_everywhere(ex.Mom))
+    saved = dict(FLAGS.__dict__)
+    worst = 0.0
+    try:
+        B = 8
+        g = torch.Generator().manual_seed(5)
+        x = torch.randn(world * B, 32, 32, 3, generator=g)
+        y = torch.eye(10)[torch.arange(world * B) % 10]
+        for use_graph in (False, True):
+            FLAGS.reset()
+            FLAGS.update(compute_dtype="f32", use_cuda_graph=use_graph, dataset="cifar10", resnet_size=8, seed=3,
+                         job_name="worker", sync_replicas=True, replicas_to_aggregate=world, task_index=rank)
+            X = x[rank * B:(rank + 1) * B].to(dev).contiguous()
+            Y = y[rank * B:(rank + 1) * B].to(dev).contiguous()
+            hps = resnet_model.HParams(num_classes=10, lrn_rate=0.1, weight_decay_rate=2e-4, optimizer='mom')
+            m = resnet_model.ResNet(hps, X, Y, 'train')
+            m.build_graph()
+            e2 = m.executor
+            params = {k: v for k, v in e2.state_dict().items() if not k.endswith("/Momentum") and k != "global_step"}
+            for _ in range(2):
+                m.train_op()
+            torch.cuda.synchronize()
+            out["ranks_identical"] = bool(out["ranks_identical"] and same_everywhere(e2.W) and same_everywhere(e2.Mom))
+            if rank == 0:
+                from oracle import resnet_oracle as ro           # the checker (test infrastructure), rank 0 only
+                net = ro.OfficialResNetV2("cifar10", 8, 10, dtype=torch.float64, params=params)
+                tr = ro.Trainer(net, 2e-4, "mom")
+                for _ in range(2):
+                    tr.step([(x[r * B:(r + 1) * B].double(), y[r * B:(r + 1) * B].double()) for r in range(world)], 0.1)
+                for v in m.graph.trainable_variables():
+                    got = e2.var_view(v.name).double().cpu()
+                    want = net.params[v.name]
+                    worst = max(worst, float((got - want).abs().max() / (want.abs().max() + 1e-30)))
+            if use_graph:
+                # (3) chief saves, every rank builds a DIFFERENTLY seeded model and resumes
+                d = [tempfile.mkdtemp() if rank == 0 else None]
+                dist.broadcast_object_list(d, src=0)
+                if rank == 0:
+                    train_utils.save_checkpoint(m, d[0], m.global_step)
+                dist.barrier()
+                FLAGS.update(seed=100 + rank)
+                m2 = resnet_model.ResNet(hps, X, Y, 'train')
+                m2.build_graph()
+                train_utils.resume(m2, d[0])
+                steps = torch.tensor([m2.global_step], device=dev)
+                gs = [torch.empty_like(steps) for _ in range(world)]
+                dist.all_gather(gs, steps)
+                out["resume_ranks_identical"] = bool(same_everywhere(m2.executor.W) and same_everywhere(m2.executor.Mom)
+                                                     and same_everywhere(m2.executor.S)
+                                                     and torch.equal(m2.executor.W, e2.W)
+                                                     and all(int(s_.item()) == m.global_step for s_ in gs))
+                m2.executor.close()
+            e2.close()
+    finally:
+        FLAGS.__dict__.clear()
+        FLAGS.__dict__.update(saved)
+    out["oracle_rel_err"] = worst if rank == 0 else None
+    out["what"] = ("W / Mom checksums all-gathered after the timed steps; 2 steps of CIFAR ResNet-8 fp32 vs the CPU oracle's "
+                   "mean-of-%d-replicas step (eager and CUDA-graph paths); chief checkpoint resumed on all ranks" % world)
+    return out
 
 
 def cpu_reference_step(workload, batch, steps, warmup, threads=None):
@@ -214,7 +337,7 @@ def run_reference(args):
     if rank != 0:
         return
     wl = WORKLOADS[args.workload]
-    batch = 8 if args.workload == "imagenet50" else 64
+    batch = 32 if args.workload == "imagenet50" else 128      # a bounded sample: seconds per step on the host cores
     steps = max(1, min(args.steps, 5))
     warm = 1
     ips, dt, threads = cpu_reference_step(args.workload, batch, steps, warm)
@@ -245,21 +368,37 @@ def run_ours(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     if world != args.gpus and rank == 0:
         sys.stderr.write("warning: --gpus %d but WORLD_SIZE %d\n" % (args.gpus, world))
-    B = args.batch or wl["batch"]
+    strong = args.global_batch > 0
+    if strong:
+        if args.global_batch % world:
+            raise SystemExit("--global-batch %d is not divisible by %d ranks" % (args.global_batch, world))
+        B = args.global_batch // world
+    else:
+        B = args.batch or wl["batch"]
     dev = torch.device("cuda", local)
     dt = torch.bfloat16 if args.dtype == "bf16" else torch.float32
     FLAGS.reset()
     FLAGS.update(dataset=wl["dataset"], compute_dtype=args.dtype, use_cuda_graph=not args.no_graph, resnet_size=50,
                  seed=0, sync_replicas=True, job_name="worker" if world > 1 else None, replicas_to_aggregate=world)
-    gen = torch.Generator().manual_seed(1000 + rank)
-    host_img = torch.randn(B, wl["size"], wl["size"], 3, generator=gen).pin_memory()        # fp32, as tf.data yields
-    lab = torch.randint(0, wl["classes"], (B,), generator=gen)
-    host_lab = torch.zeros(B, wl["classes"]).pin_memory()
-    host_lab[torch.arange(B), lab] = 1.0
-    images = torch.empty(B, wl["size"], wl["size"], 3, dtype=torch.float32, device=dev)   # model casts to bf16 itself
-    labels = torch.empty(B, wl["classes"], dtype=torch.float32, device=dev)
-    images.copy_(host_img)
-    labels.copy_(host_lab)
+    cifar = wl["dataset"] in ("cifar10", "cifar100")
+    pipe = None
+    if cifar:
+        # the reference's input path: binary CIFAR records -> rn_cifar_decode (crop / flip / standardise) every step;
+        # synthetic records, resident in HBM for `value`, in pinned host memory for `e2e`
+        from distributed_tensorflow_resnet_b200 import cifar_input
+        images, labels = cifar_input.input_fn(True, "synthetic:50000", B, dataset=wl["dataset"], seed=0)
+        pipe = images._rn_pipeline
+        host_records = torch.from_numpy(cifar_input.synthetic_records(50000, wl["dataset"], 0)).pin_memory()
+    else:
+        gen = torch.Generator().manual_seed(1000 + rank)
+        host_img = torch.randn(B, wl["size"], wl["size"], 3, generator=gen).pin_memory()        # fp32, as tf.data yields
+        lab = torch.randint(0, wl["classes"], (B,), generator=gen)
+        host_lab = torch.zeros(B, wl["classes"]).pin_memory()
+        host_lab[torch.arange(B), lab] = 1.0
+        images = torch.empty(B, wl["size"], wl["size"], 3, dtype=torch.float32, device=dev)   # model casts to bf16 itself
+        labels = torch.empty(B, wl["classes"], dtype=torch.float32, device=dev)
+        images.copy_(host_img)
+        labels.copy_(host_lab)
     hkw = dict(num_classes=wl["classes"], lrn_rate=0.1, weight_decay_rate=wl["wd"], optimizer='mom')
     if wl.get("upstream"):
         hkw.update(batch_size=B, min_lrn_rate=1e-4, **wl["upstream"])
@@ -269,6 +408,7 @@ def run_ours(args):
         model.filters = wl["filters"]
     model.build_graph()
     ex = model.executor
+    ex._bench_pipe = pipe
     model.lrn_rate = 0.1
     pk = peaks()
 
@@ -301,34 +441,69 @@ def run_ours(args):
     ms = t.item()
     value = world * B * args.steps / (ms / 1e3)
 
-    # ---- end to end through the public API with host buffers ------------------------------
-    copy_stream = torch.cuda.Stream()
-    stage_i = [torch.empty_like(images) for _ in range(2)]
-    stage_l = [torch.empty_like(labels) for _ in range(2)]
-    ready = [torch.cuda.Event() for _ in range(2)]
-    consumed = [torch.cuda.Event() for _ in range(2)]
-    out_host = torch.zeros(2, dtype=torch.float32).pin_memory()
-
-    def e2e_steps(k):
-        cur = torch.cuda.current_stream()
-        for i in range(k):
-            sl = i % 2
-            with torch.cuda.stream(copy_stream):
-                copy_stream.wait_event(consumed[sl])
-                stage_i[sl].copy_(host_img, non_blocking=True)          # H2D from pinned host memory
-                stage_l[sl].copy_(host_lab, non_blocking=True)
-                ready[sl].record(copy_stream)
-            cur.wait_event(ready[sl])
-            images.copy_(stage_i[sl], non_blocking=True)
-            labels.copy_(stage_l[sl], non_blocking=True)
-            consumed[sl].record(cur)
+    # ---- sustained leg: seconds of back-to-back steps with the clock sampler running ------------
+    sustained = None
+    if args.sustained_steps > 0:
+        sampler = ClockSampler(local) if rank == 0 else None
+        if sampler:
+            sampler.start()
+        barrier()
+        e0.record()
+        for _ in range(args.sustained_steps):
             model.train_op()
-            out_host.copy_(model._loss[1].buf, non_blocking=True)      # D2H of the step's loss / precision
-        torch.cuda.current_stream().synchronize()
-        return float(out_host[0])
+        e1.record()
+        barrier()
+        t = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        sclk = sampler.stop() if sampler else None
+        sustained = {"steps": args.sustained_steps, "seconds": round(t.item() / 1e3, 3),
+                     "ms_per_step": round(t.item() / args.sustained_steps, 4),
+                     "value": round(world * B * args.sustained_steps / (t.item() / 1e3), 2), "unit": "images/s",
+                     "clocks": sclk}
 
-    for ev in consumed:
-        ev.record(torch.cuda.current_stream())
+    # ---- end to end through the public API with host buffers ------------------------------
+    out_host = torch.zeros(2, dtype=torch.float32).pin_memory()
+    if cifar:
+        # the record file stays in pinned HOST memory: every step gathers its B records on the host, copies them
+        # H2D (plus the B int32 record indices) and decodes them on the GPU in front of the training step
+        pipe.set_resident(False)
+
+        def e2e_steps(k):
+            for i in range(k):
+                model.train_op()
+                out_host.copy_(model._loss[1].buf, non_blocking=True)      # D2H of the step's loss / precision
+            torch.cuda.current_stream().synchronize()
+            return float(out_host[0])
+        h2d = B * pipe.record_bytes + B * 4
+    else:
+        copy_stream = torch.cuda.Stream()
+        stage_i = [torch.empty_like(images) for _ in range(2)]
+        stage_l = [torch.empty_like(labels) for _ in range(2)]
+        ready = [torch.cuda.Event() for _ in range(2)]
+        consumed = [torch.cuda.Event() for _ in range(2)]
+
+        def e2e_steps(k):
+            cur = torch.cuda.current_stream()
+            for i in range(k):
+                sl = i % 2
+                with torch.cuda.stream(copy_stream):
+                    copy_stream.wait_event(consumed[sl])
+                    stage_i[sl].copy_(host_img, non_blocking=True)          # H2D from pinned host memory
+                    stage_l[sl].copy_(host_lab, non_blocking=True)
+                    ready[sl].record(copy_stream)
+                cur.wait_event(ready[sl])
+                images.copy_(stage_i[sl], non_blocking=True)
+                labels.copy_(stage_l[sl], non_blocking=True)
+                consumed[sl].record(cur)
+                model.train_op()
+                out_host.copy_(model._loss[1].buf, non_blocking=True)      # D2H of the step's loss / precision
+            torch.cuda.current_stream().synchronize()
+            return float(out_host[0])
+
+        for ev in consumed:
+            ev.record(torch.cuda.current_stream())
+        h2d = host_img.numel() * 4 + host_lab.numel() * 4
     e2e_steps(2)
     barrier()
     e0.record()
@@ -340,8 +515,9 @@ def run_ours(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     e2e_ms = t.item()
     e2e_value = world * B * args.steps / (e2e_ms / 1e3)
-    h2d = host_img.numel() * 4 + host_lab.numel() * 4
     d2h = 8
+    if cifar:
+        pipe.set_resident(True)
 
     # ---- gradient aggregation alone (C5): all-reduce of the flat fp32 fusion buffer, bus bandwidth
     allreduce = None
@@ -363,6 +539,8 @@ def run_ours(args):
                      "buckets_in_step": len(ex.buckets)}
         ex.Gd.zero_()
 
+    ddp = ddp_check(ex, model, world, rank, dev) if world > 1 else None
+
     line = None
     if rank == 0:
         # ---- per-kernel roofline (un-captured launch list, CUDA events per launch) ------------
@@ -382,9 +560,9 @@ def run_ours(args):
                         if b_:
                             extra = " %8.1f GB/s" % (b_ / ms_ / 1e6)
                     f.write("%-44s %9.4f ms%s\n" % (name, ms_, extra))
-        roof, table, prof_total = roofline_report(ex, model.graph, per_launch, pk)
+        roof, table, prof_total = roofline_report(ex, model.graph, per_launch, pk, clocks)
         cpu = None
-        if not args.no_cpu_baseline:
+        if not args.no_cpu_baseline and world == 1:      # rank 0 at N = 1 only: at N > 1 the other ranks' GPUs would idle
             cb = 8 if args.workload == "imagenet50" else 64
             ips, cdt, threads = cpu_reference_step(args.workload, cb, 2, 1)
             cpu = {"value": round(ips, 3), "unit": "images/s", "cores": threads, "kind": "port",
@@ -395,15 +573,19 @@ def run_ours(args):
         line = {
             "metric": "train images/sec", "value": round(value, 2), "unit": "images/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms / args.steps, 4),
-            "higher_is_better": True, "scaling": "weak",
+            "higher_is_better": True, "scaling": "strong" if strong else "weak",
             "vs_baseline": (round(value / PUBLISHED[(args.workload, world)], 3)
-                            if (args.workload, world) in PUBLISHED and B == wl["batch"] else None),
+                            if (args.workload, world) in PUBLISHED and B == wl["batch"] and not strong else None),
             "dtype": args.dtype, "data": "synthetic",
             "config": {"workload": args.workload, "description": wl["desc"], "per_gpu_batch": B,
                        "global_batch": B * world, "parallelism": "dp%d" % world,
                        "optimizer": "momentum 0.9 + L2 wd %g, lr 0.1" % wl["wd"],
                        "cuda_graph": not args.no_graph,
-                       "cache": "working set (activations + gradients, GBs) far exceeds the 126 MB L2; no explicit flush",
+                       "cache": "working set (activations + gradients, GBs) far exceeds the 126 MB L2; no explicit flush"
+                                if not cifar else "working set %d MB per step vs 126 MB L2; no explicit flush (steady-state training loop)"
+                                % (sum(t_.buf.numel() * t_.buf.element_size() for t_ in model.graph.tensors.values() if t_.buf is not None) >> 20),
+                       "input": ("synthetic CIFAR records through rn_cifar_decode every step (HBM-resident for value, "
+                                 "pinned host memory for e2e)") if cifar else "synthetic standard-normal images",
                        "conv_impl": sorted({family(n) for n, _ in ex.fwd + ex.bwd if n.startswith("conv_")})},
             "e2e": {"value": round(e2e_value, 2), "unit": "images/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": round(e2e_ms / args.steps, 4), "last_loss": last_loss},
@@ -412,6 +594,8 @@ def run_ours(args):
             "clocks": clocks,
             "roofline": roof,
             "allreduce": allreduce,
+            "ddp_check": ddp,
+            "sustained": sustained,
             "conv": {"tflops_all_conv_kernels": round(conv_fl / conv_ms / 1e9, 2) if conv_ms else None,
                      "frac_of_sustained_peak": round(conv_fl / conv_ms / 1e9 / pk["tf_sust"], 4) if conv_ms else None,
                      "gflop_per_step": round(conv_fl / 1e9, 2)},
@@ -436,12 +620,18 @@ def main():
     ap.add_argument("--workload", default="imagenet50", choices=sorted(WORKLOADS))
     ap.add_argument("--dtype", default="bf16", choices=["bf16", "f32"])
     ap.add_argument("--batch", type=int, default=0, help="per-GPU batch (default: the workload's)")
+    ap.add_argument("--global-batch", type=int, default=0,
+                    help="fixed GLOBAL batch split over the ranks (strong scaling; BASELINE config 2 uses 128)")
+    ap.add_argument("--sustained-steps", type=int, default=-1,
+                    help="extra timed leg of this many back-to-back steps (default: ~3 s worth; 0 disables)")
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--dump-layers", default="", help="write the per-launch timing table to this file")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":
         args.warmup = 3
+    if args.sustained_steps < 0:
+        args.sustained_steps = 300 if args.workload in ("imagenet50", "wrn28_10") else 1000
     if args.impl == "reference":
         run_reference(args)
     else:

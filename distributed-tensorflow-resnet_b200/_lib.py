@@ -22,17 +22,44 @@ class ConvDesc(C.Structure):
                 ("N", "H", "W", "Cin", "Ho", "Wo", "Cout", "k", "stride", "pad", "dtype")]
 
 
+ABI_VERSION = 4           # must equal RN_ABI_VERSION of include/rn_b200.h the .so was compiled from
+
+
 def _load():
-    if not os.path.exists(SO_PATH):
-        # build in-tree (needs nvcc); raises if impossible
-        import importlib.util
-        spec = importlib.util.spec_from_file_location("_rn_build", os.path.join(HERE, "build.py"))
-        mod = importlib.util.module_from_spec(spec)
-        spec.loader.exec_module(mod)
-        mod.build(verbose=False)
+    """Build (a digest compare of csrc/ + the header when nothing changed) and load the library.
+    One process builds at a time: ranks started together by torchrun serialise on a lock file, the
+    first one compiles, the others find the stamp up to date."""
+    import fcntl
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("_rn_build", os.path.join(HERE, "build.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    try:
+        lock = open(os.path.join(HERE, ".build.lock"), "w")
+    except OSError:
+        lock = None                       # read-only tree: use what is there
+    try:
+        if lock is not None:
+            fcntl.flock(lock, fcntl.LOCK_EX)
+        try:
+            mod.build(verbose=False)      # raises if sources changed and nvcc is missing / fails
+        except Exception as e:
+            if not os.path.exists(SO_PATH):
+                raise RnError("librn_b200.so is missing and could not be built (%s); there is no CPU fallback" % e)
+            raise
+    finally:
+        if lock is not None:
+            fcntl.flock(lock, fcntl.LOCK_UN)
+            lock.close()
     if not os.path.exists(SO_PATH):
         raise RnError("librn_b200.so is missing and could not be built; there is no CPU fallback")
-    return C.CDLL(SO_PATH)
+    so = C.CDLL(SO_PATH)
+    so.rn_abi_version.restype = C.c_int
+    got = so.rn_abi_version()
+    if got != ABI_VERSION:
+        raise RnError("librn_b200.so reports ABI version %d, these bindings expect %d: rebuild with "
+                      "`python distributed-tensorflow-resnet_b200/build.py --force`" % (got, ABI_VERSION))
+    return so
 
 
 _so = _load()
@@ -92,11 +119,12 @@ SIGNATURES = {
     "rn_optimizer_scratch_bytes": (sz, [i64]),
     "rn_sgd_momentum_fused": (C.c_int, [vp, vp, vp, vp, i64, vp, vp, f32, f32, f32, i32, vp, vp, sz, vp]),
     "rn_l2_sumsq": (C.c_int, [vp, i64, vp, vp, vp, sz, vp]),
-    "rn_cifar_decode": (C.c_int, [vp, i64, i32, i32, i32, vp, i32, i32, i32, u32, u32, u32, vp, vp, i32, vp, vp, vp, vp]),
+    "rn_cifar_decode": (C.c_int, [vp, i64, i32, i32, i32, vp, i32, i32, i32, u32, u32, u32, vp, i32, vp, i32, vp, vp, vp, vp]),
     "rn_cast": (C.c_int, [vp, vp, i64, i32, i32, vp]),
     "rn_add_inplace": (C.c_int, [vp, vp, i64, i32, vp]),
     "rn_add": (C.c_int, [vp, vp, vp, i64, i32, vp]),
     "rn_pad_channels": (C.c_int, [vp, vp, i64, i32, i32, i32, i32, vp]),
+    "rn_crc32c": (u32, [vp, sz, u32]),
 }
 
 for _name, (_res, _args) in SIGNATURES.items():

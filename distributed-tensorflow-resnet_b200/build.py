@@ -27,7 +27,9 @@ def digest():
     files = sorted(os.path.join(CSRC, f) for f in os.listdir(CSRC)) + \
         [os.path.join(os.path.dirname(HERE), "include", "rn_b200.h"), os.path.abspath(__file__)]
     for f in files:
-        h.update(f.encode())
+        if os.path.isdir(f):
+            continue
+        h.update(os.path.basename(f).encode())     # names, not absolute paths: the GPU box unpacks the tree elsewhere
         h.update(open(f, "rb").read())
     return h.hexdigest()
 

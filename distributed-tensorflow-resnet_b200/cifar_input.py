@@ -61,7 +61,7 @@ class RecordPipeline(object):
     """Owns the device-resident records and the two output tensors."""
 
     def __init__(self, dataset, data_path, batch_size, train, pad, *, seed=0, dtype=None, device=None,
-                 rank=0, world=1, shuffle=True):
+                 rank=0, world=1, shuffle=True, resident=True):
         if dataset == 'cifar10':
             self.label_offset, self.classes = 0, 10
         elif dataset == 'cifar100':
@@ -78,7 +78,15 @@ class RecordPipeline(object):
         dev = torch.device(device if device is not None else "cuda:%d" % torch.cuda.current_device())
         host = _load_records(dataset, data_path, self.record_bytes, seed)
         self.n = host.shape[0]
-        self.records = torch.from_numpy(host).to(dev)
+        # resident: the whole record file lives in HBM (CIFAR: 154 MB).  Otherwise it stays in pinned host
+        # memory and every batch's records are gathered on the host and copied H2D in front of the decode.
+        self.resident = bool(resident)
+        self.records = torch.from_numpy(host).to(dev) if self.resident else None
+        self.host_records = None if self.resident else torch.from_numpy(host).pin_memory()
+        self._stage_host = [torch.zeros(self.B, self.record_bytes, dtype=torch.uint8).pin_memory() for _ in range(4)]
+        self._stage_dev = [torch.zeros(self.B, self.record_bytes, dtype=torch.uint8, device=dev) for _ in range(4)]
+        self._stage_evt = [None] * 4
+        self._stage = 0
         if dtype is None:
             dtype = torch.bfloat16 if FLAGS.compute_dtype == "bf16" else torch.float32
         self.images = torch.zeros(self.B, 32, 32, 3, dtype=dtype, device=dev)
@@ -117,6 +125,17 @@ class RecordPipeline(object):
                 self._cursor = 0
         return out
 
+    def seek(self, batches):
+        """Position the stream as if `batches` batches had been consumed and decode the next one
+        (checkpoint resume: the record order is a pure function of (seed, epoch), so replaying the
+        index stream on the host reproduces exactly what the interrupted run would have read)."""
+        self.epoch = 0
+        self._cursor = 0
+        self._order = self._epoch_order(0)
+        for _ in range(int(batches)):
+            self.next_indices()
+        return self.next_batch()
+
     def next_batch(self, indices=None, draws=None):
         """Decode the next batch into self.images / self.labels (one H2D of B int32 + one launch)."""
         idx = self.next_indices() if indices is None else np.asarray(indices, dtype=np.int32)
@@ -135,12 +154,37 @@ class RecordPipeline(object):
             self._draws_in = torch.as_tensor(np.asarray(draws, dtype=np.int32)).to(self.records.device)
             din = ptr(self._draws_in)
         odt = RN_BF16 if self.images.dtype == torch.bfloat16 else RN_F32
-        check(lib.rn_cifar_decode(ptr(self.records), self.n, self.record_bytes, self.label_offset, self.classes,
+        if self.resident:
+            rec, nrec, staged = self.records, self.n, 0
+        else:
+            k = self._stage
+            self._stage = (k + 1) % len(self._stage_host)
+            if self._stage_evt[k] is not None:
+                self._stage_evt[k].synchronize()     # only blocks if the GPU is 4 batches behind the host
+            torch.index_select(self.host_records, 0, torch.from_numpy(idx.astype(np.int64)), out=self._stage_host[k])
+            self._stage_dev[k].copy_(self._stage_host[k], non_blocking=True)        # H2D, B x record_bytes
+            self._stage_evt[k] = torch.cuda.Event()
+            self._stage_evt[k].record(st)
+            rec, nrec, staged = self._stage_dev[k], self.B, 1
+        check(lib.rn_cifar_decode(ptr(rec), nrec, self.record_bytes, self.label_offset, self.classes,
                                   ptr(self.indices), self.B, int(self.train), self.pad,
                                   self.seed & 0xFFFFFFFF, (self.seed >> 32) & 0xFFFFFFFF, epoch & 0xFFFFFFFF, din,
-                                  ptr(self.images), odt, ptr(self.labels), ptr(self.label_ids), ptr(self.draws),
+                                  staged, ptr(self.images), odt, ptr(self.labels), ptr(self.label_ids), ptr(self.draws),
                                   st.cuda_stream), "rn_cifar_decode")
         return self.images, self.labels
+
+    def set_resident(self, resident):
+        """Move the record file between HBM and pinned host memory (same batches, same draws either way)."""
+        resident = bool(resident)
+        if resident == self.resident:
+            return
+        if resident:
+            self.records = self.host_records.to(self.images.device)
+            self.host_records = None
+        else:
+            self.host_records = self.records.cpu().pin_memory()
+            self.records = None
+        self.resident = resident
 
 
 def _dist():

@@ -728,6 +728,7 @@ extern "C" int rn_bn_stats_fwd(const void* x, const void* addend, void* sum_out,
                                float eps, float decay, int32_t unbiased, float* mean, float* rstd, float* moving_mean,
                                float* moving_var, void* scratch, size_t scratch_bytes, void* stream) {
   RN_REQUIRE(x && mean && rstd, "bn_stats: NULL pointer");
+  RN_REQUIRE((((uintptr_t)x | (uintptr_t)addend | (uintptr_t)sum_out) & 15) == 0, "bn_stats: x / addend / sum_out must be 16-byte aligned");
   RN_REQUIRE((moving_mean == nullptr) == (moving_var == nullptr), "bn_stats: moving_mean/var must both be set or NULL");
   if (dtype == RN_F32)
     return bn_stats_launch<float>(x, addend, sum_out, M, C, eps, decay, unbiased, mean, rstd, moving_mean, moving_var,
@@ -755,6 +756,7 @@ extern "C" int rn_bn_apply_act_fwd(const void* x, void* y, int64_t M, int32_t C,
                                    const float* beta, const float* mean, const float* rstd, int32_t stats_are_moving,
                                    float eps, float leak, void* stream) {
   RN_REQUIRE(x && y && gamma && beta && mean && rstd, "bn_apply: NULL pointer");
+  RN_REQUIRE((((uintptr_t)x | (uintptr_t)y) & 15) == 0, "bn_apply: x / y must be 16-byte aligned");
   if (dtype == RN_F32)
     return bn_apply_launch<float>(x, y, M, C, gamma, beta, mean, rstd, stats_are_moving, eps, leak, as_stream(stream));
   if (dtype == RN_BF16)
@@ -803,6 +805,7 @@ extern "C" int rn_bn_act_bwd_reduce(const void* dy, const void* x, int64_t M, in
                                     float leak, float* dgamma, float* dbeta, void* scratch, size_t scratch_bytes,
                                     void* stream) {
   RN_REQUIRE(dy && x && gamma && beta && mean && rstd && dgamma && dbeta, "bn_bwd_reduce: NULL pointer");
+  RN_REQUIRE((((uintptr_t)dy | (uintptr_t)x) & 15) == 0, "bn_bwd_reduce: dy / x must be 16-byte aligned");
   if (dtype == RN_F32)
     return bn_bwd_reduce_launch<float>(dy, x, M, C, gamma, beta, mean, rstd, leak, dgamma, dbeta, scratch,
                                        scratch_bytes, as_stream(stream));
@@ -837,6 +840,8 @@ extern "C" int rn_bn_act_bwd_apply(const void* dy, const void* x, void* dx, cons
                                    const float* rstd, const float* dgamma, const float* dbeta, float leak,
                                    void* stream) {
   RN_REQUIRE(dy && x && dx && gamma && beta && mean && rstd && dgamma && dbeta, "bn_bwd_apply: NULL pointer");
+  RN_REQUIRE((((uintptr_t)dy | (uintptr_t)x | (uintptr_t)dx | (uintptr_t)dx_addend) & 15) == 0,
+             "bn_bwd_apply: dy / x / dx / dx_addend must be 16-byte aligned");
   if (dtype == RN_F32)
     return bn_bwd_apply_launch<float>(dy, x, dx, dx_addend, M, C, gamma, beta, mean, rstd, dgamma, dbeta, leak,
                                       as_stream(stream));
@@ -859,7 +864,8 @@ extern "C" int rn_bn_act_bwd_apply(const void* dy, const void* x, void* dx, cons
 //
 // The array's name is only a host-side handle; its device address is looked up once per device
 // (with that device current) through cudaGetSymbolAddress on the FIRST call made on that device —
-// make that first call during set-up, before any stream capture is begun.  The entry point calls
+// make that first call during set-up, before any stream capture is begun.  On EVERY call the device
+// that owns `stream` must be the current device: the array used is the current device's.  The entry point calls
 // no cudaMalloc / cudaFree and no allocating library routine.
 //
 // All calls on a device share the one array and it keeps whatever the previous call left behind:
@@ -934,6 +940,8 @@ extern "C" int rn_bn_stats_fwd_noalloc(const void* x, const void* addend, void* 
                                        int32_t dtype, float eps, float decay, int32_t unbiased, float* mean,
                                        float* rstd, float* moving_mean, float* moving_var, void* stream) {
   RN_REQUIRE(x && mean && rstd, "bn_stats_noalloc: NULL pointer");
+  RN_REQUIRE((((uintptr_t)x | (uintptr_t)addend | (uintptr_t)sum_out) & 15) == 0,
+             "bn_stats_noalloc: x / addend / sum_out must be 16-byte aligned");
   RN_REQUIRE((moving_mean == nullptr) == (moving_var == nullptr),
              "bn_stats_noalloc: moving_mean/var must both be set or NULL");
   RN_REQUIRE(addend == nullptr || sum_out != nullptr, "bn_stats_noalloc: addend given but sum_out is NULL");

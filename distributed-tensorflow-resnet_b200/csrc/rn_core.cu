@@ -1,5 +1,6 @@
 // Library state (error string, launch counter) and small element-wise utilities.
 #include "rn_common.cuh"
+#include <string.h>
 
 namespace rn {
 thread_local char g_err[512] = "";
@@ -64,7 +65,7 @@ __global__ void pad_channels_kernel(const S* __restrict__ src, D* __restrict__ d
 using namespace rn;
 
 extern "C" const char* rn_last_error(void) { return g_err; }
-extern "C" int rn_abi_version(void) { return 3; }
+extern "C" int rn_abi_version(void) { return RN_ABI_VERSION; }
 extern "C" uint64_t rn_launch_count(void) { return g_launches.load(); }
 
 extern "C" int rn_cast(const void* src, void* dst, int64_t n, int32_t sd, int32_t dd, void* stream) {
@@ -137,4 +138,44 @@ extern "C" int rn_pad_channels(const void* src, void* dst, int64_t pixels, int32
   else
     return fail(RN_ERR_INVALID, "pad_channels: bad dtypes %d -> %d", sd, dd);
   return check_launch("pad_channels_kernel");
+}
+
+// ------------------------------------------------------------------------------------------
+// CRC-32C (Castagnoli, reflected polynomial 0x82F63B78), slicing-by-8, host code: the checksum of
+// TensorFlow's checkpoint bundles (tensor data and index-table blocks), used by tf_io.py.
+// ------------------------------------------------------------------------------------------
+namespace rn {
+static uint32_t g_crc_tab[8][256];
+static std::atomic<int> g_crc_ready{0};
+static void crc32c_init() {
+  if (g_crc_ready.load(std::memory_order_acquire)) return;
+  uint32_t t[8][256];
+  for (uint32_t i = 0; i < 256; ++i) {
+    uint32_t c = i;
+    for (int k = 0; k < 8; ++k) c = (c & 1u) ? (c >> 1) ^ 0x82F63B78u : c >> 1;
+    t[0][i] = c;
+  }
+  for (uint32_t i = 0; i < 256; ++i)
+    for (int s = 1; s < 8; ++s) t[s][i] = (t[s - 1][i] >> 8) ^ t[0][t[s - 1][i] & 0xffu];
+  memcpy(g_crc_tab, t, sizeof(t));          // idempotent: concurrent initialisers write identical bytes
+  g_crc_ready.store(1, std::memory_order_release);
+}
+}  // namespace rn
+
+extern "C" uint32_t rn_crc32c(const void* data, size_t n, uint32_t crc) {
+  rn::crc32c_init();
+  const uint8_t* p = (const uint8_t*)data;
+  uint32_t c = ~crc;
+  while (n && ((uintptr_t)p & 7)) { c = rn::g_crc_tab[0][(c ^ *p++) & 0xffu] ^ (c >> 8); --n; }
+  while (n >= 8) {
+    uint64_t w;
+    memcpy(&w, p, 8);
+    w ^= c;
+    c = rn::g_crc_tab[7][w & 0xff] ^ rn::g_crc_tab[6][(w >> 8) & 0xff] ^ rn::g_crc_tab[5][(w >> 16) & 0xff] ^
+        rn::g_crc_tab[4][(w >> 24) & 0xff] ^ rn::g_crc_tab[3][(w >> 32) & 0xff] ^ rn::g_crc_tab[2][(w >> 40) & 0xff] ^
+        rn::g_crc_tab[1][(w >> 48) & 0xff] ^ rn::g_crc_tab[0][(w >> 56) & 0xff];
+    p += 8; n -= 8;
+  }
+  while (n--) c = rn::g_crc_tab[0][(c ^ *p++) & 0xffu] ^ (c >> 8);
+  return ~c;
 }

@@ -28,15 +28,17 @@ template <typename T>
 __global__ void __launch_bounds__(DEC_THREADS)
 cifar_decode_kernel(const uint8_t* __restrict__ records, int64_t n_records, int record_bytes, int label_offset,
                     int classes, const int32_t* __restrict__ indices, int train, int pad, uint32_t seed_lo,
-                    uint32_t seed_hi, uint32_t epoch, const int32_t* __restrict__ draws_in, T* __restrict__ out_img,
-                    float* __restrict__ out_onehot, int32_t* __restrict__ out_labels, int32_t* __restrict__ draws_out) {
+                    uint32_t seed_hi, uint32_t epoch, const int32_t* __restrict__ draws_in, int staged,
+                    T* __restrict__ out_img, float* __restrict__ out_onehot, int32_t* __restrict__ out_labels,
+                    int32_t* __restrict__ draws_out) {
   __shared__ uint8_t px[3072];
   __shared__ int red[2][DEC_THREADS / 32];
   __shared__ float s_scale;
   __shared__ int s_sum;
   const int b = blockIdx.x;
   const int64_t rec = indices ? (int64_t)indices[b] : (int64_t)b;
-  const uint8_t* base = records + rec * record_bytes;
+  // staged: `records` holds just this batch (row b), copied from host memory; `rec` still keys the random draws
+  const uint8_t* base = records + (staged ? (int64_t)b : rec) * record_bytes;
   int oy = pad, ox = pad, flip = 0;  // identity window when not training
   if (train) {
     if (draws_in) {
@@ -108,23 +110,24 @@ using namespace rn;
 extern "C" int rn_cifar_decode(const uint8_t* records, int64_t n_records, int32_t record_bytes, int32_t label_offset,
                                int32_t classes, const int32_t* indices, int32_t B, int32_t train, int32_t pad,
                                uint32_t seed_lo, uint32_t seed_hi, uint32_t epoch, const int32_t* draws_in,
-                               void* out_img, int32_t out_dtype, float* out_onehot, int32_t* out_labels,
-                               int32_t* draws_out, void* stream) {
+                               int32_t staged, void* out_img, int32_t out_dtype, float* out_onehot,
+                               int32_t* out_labels, int32_t* draws_out, void* stream) {
   RN_REQUIRE(records && out_img && B >= 0 && n_records > 0, "cifar_decode: bad arguments");
   RN_REQUIRE(record_bytes == 1 + label_offset + 3072 && (label_offset == 0 || label_offset == 1),
              "cifar_decode: record_bytes=%d label_offset=%d is not a CIFAR record", record_bytes, label_offset);
   RN_REQUIRE(pad >= 0 && pad <= 16 && classes > 0, "cifar_decode: bad pad/classes");
   RN_REQUIRE(indices != nullptr || B <= n_records, "cifar_decode: B > n_records without indices");
+  RN_REQUIRE(!staged || B <= n_records, "cifar_decode: a staged batch must hold B records");
   if (B == 0) return RN_OK;
   cudaStream_t st = as_stream(stream);
   if (out_dtype == RN_F32)
     cifar_decode_kernel<float><<<B, DEC_THREADS, 0, st>>>(records, n_records, record_bytes, label_offset, classes,
                                                          indices, train, pad, seed_lo, seed_hi, epoch, draws_in,
-                                                         (float*)out_img, out_onehot, out_labels, draws_out);
+                                                         staged, (float*)out_img, out_onehot, out_labels, draws_out);
   else if (out_dtype == RN_BF16)
     cifar_decode_kernel<__nv_bfloat16><<<B, DEC_THREADS, 0, st>>>(records, n_records, record_bytes, label_offset,
                                                                  classes, indices, train, pad, seed_lo, seed_hi, epoch,
-                                                                 draws_in, (__nv_bfloat16*)out_img, out_onehot,
+                                                                 draws_in, staged, (__nv_bfloat16*)out_img, out_onehot,
                                                                  out_labels, draws_out);
   else
     return fail(RN_ERR_INVALID, "cifar_decode: bad out_dtype %d", out_dtype);

@@ -148,7 +148,6 @@ class Executor:
         self.all_decay = bool(mask.all())
         self.mask = None if self.all_decay else torch.from_numpy(mask).to(dev)
         self.hyper = torch.zeros(4, dtype=torch.float32, device=dev)
-        self._hyper_host = torch.zeros(4, dtype=torch.float32).pin_memory()
         self.sumsq = torch.zeros(1, dtype=torch.float32, device=dev)
         nbytes = max(lib.rn_bn_scratch_bytes(1, 8), lib.rn_optimizer_scratch_bytes(self.n_flat))
         self.scratch = torch.zeros(nbytes, dtype=torch.uint8, device=dev)     # ticket counters start at 0
@@ -799,14 +798,26 @@ class Executor:
 
     def set_lr(self, lr):
         """The reference feeds the learning rate every step (resnet_cifar_train.py:297-299); here
-        it lives in device memory and is only re-uploaded when the value changes."""
+        it lives in device memory and is re-uploaded when the value changes: one async H2D copy from
+        a ring of pinned staging words, so a schedule that changes the rate on every step (the
+        ImageNet warm-up, resnet_imagenet_train.py:236-260) never stalls the host on the stream."""
         lr = float(lr)
         if getattr(self, "lrn_rate", None) == lr:
             return
         self.lrn_rate = lr
-        torch.cuda.current_stream().synchronize()   # the pinned staging word may still be in flight
-        self._hyper_host[0] = lr
-        self.hyper.copy_(self._hyper_host, non_blocking=True)
+        ring = getattr(self, "_hyper_ring", None)
+        if ring is None:
+            ring = self._hyper_ring = [[torch.zeros(4, dtype=torch.float32).pin_memory(), None] for _ in range(32)]
+            self._hyper_slot = 0
+        slot = ring[self._hyper_slot]
+        self._hyper_slot = (self._hyper_slot + 1) % len(ring)
+        if slot[1] is not None:
+            slot[1].synchronize()           # only blocks if the GPU is 32 rate changes behind the host
+        slot[0][0] = lr
+        st = torch.cuda.current_stream()
+        self.hyper.copy_(slot[0], non_blocking=True)
+        slot[1] = torch.cuda.Event()
+        slot[1].record(st)
 
     def broadcast_from_rank0(self):
         """hvd.BroadcastGlobalVariablesHook(0) (resnet_cifar_train_horovod.py:313): weights, BN

@@ -10,7 +10,6 @@ exits at once (there are no parameter servers), and gradients are aggregated by 
         --batch_size 128 --train_steps 200
 """
 import argparse
-import json
 import os
 import sys
 import time
@@ -60,6 +59,9 @@ def define_flags(parser):
     a('--use_cuda_graph', type=str2bool, default=True)
     a('--resnet_size', type=int, default=50)
     a('--seed', type=int, default=0)
+    a('--save_checkpoint_steps', type=int, default=1000, help='chief checkpoint cadence (reference: 1000)')
+    a('--checkpoint_format', default='npz', choices=['npz', 'tf'],
+      help="npz = one numpy archive per checkpoint; tf = TF-V2 bundle (.index/.data) under the reference's tensor names")
 
 
 def cifar_learning_rate(train_step):
@@ -83,69 +85,69 @@ def init_distributed():
     return (dist.get_rank(), dist.get_world_size()) if dist.is_initialized() else (0, 1)
 
 
-def save_checkpoint(model, train_dir, step):
-    os.makedirs(train_dir, exist_ok=True)
-    path = os.path.join(train_dir, "model.ckpt-%d.npz" % step)
-    np.savez(path, **model.executor.state_dict())
-    with open(os.path.join(train_dir, "checkpoint"), "w") as f:
-        f.write('model_checkpoint_path: "%s"\n' % os.path.basename(path))
-    return path
+from .train_utils import save_checkpoint, restore_latest, resume, SummaryWriter  # noqa: E402,F401
 
 
-def restore_latest(model, train_dir):
-    ck = os.path.join(train_dir, "checkpoint")
-    if not os.path.exists(ck):
-        return None
-    name = open(ck).read().split('"')[1]
-    z = np.load(os.path.join(train_dir, name))
-    model.executor.load_state_dict({k: z[k] for k in z.files})
-    model.global_step = model.executor.global_step
-    return name
-
-
-def train(hps, lr_fn=cifar_learning_rate, log_every=20, out=sys.stdout):
-    """Training loop (reference :251-344): logging every 20 iterations {step, loss, precision,
-    lr}, summaries every 100 steps, LR set from the global step fetched by the previous run,
-    checkpoint every 1000 steps on the chief, stop at train_steps."""
-    rank, world = init_distributed()
+def run_training_loop(model, lr_begin, lr_fn, world, out, log_every=20, summary_every=100, checkpoint_every=None):
+    """The body of `with MonitoredTrainingSession(...) as mon_sess: while not mon_sess.should_stop():
+    mon_sess.run(model.train_op)` with the reference's hooks (resnet_cifar_train.py:275-344):
+    LoggingTensorHook every 20 iterations {step, loss, precision, lr}; SummarySaverHook every 100
+    steps on the chief (cross_entropy, cost, learning_rate, Precision -> TensorBoard events in
+    --log_dir); _LearningRateSetterHook (rate for the NEXT run from the step this run returned);
+    CheckpointSaverHook every 1000 steps and at the end on the chief; StopAtStepHook(train_steps).
+    A run started on a --train_dir that already holds a checkpoint resumes from it on every rank."""
+    import torch.distributed as dist
+    rank = dist.get_rank() if dist.is_available() and dist.is_initialized() else 0
     is_chief = rank == 0
-    images, labels = cifar_input.input_fn(True, FLAGS.train_data_path, FLAGS.batch_size, num_epochs=1000,
-                                          dataset=FLAGS.dataset, seed=FLAGS.seed)
-    model = resnet_model.ResNet(hps, images, labels, FLAGS.mode)
-    model.build_graph()
-    if FLAGS.train_dir and is_chief:
-        restored = restore_latest(model, FLAGS.train_dir)
-        if restored:
-            out.write("restored %s\n" % restored)
-    lrn_rate = 0.1                       # _LearningRateSetterHook.begin
-    summaries = None
-    if FLAGS.log_dir and is_chief:
-        os.makedirs(FLAGS.log_dir, exist_ok=True)
-        summaries = open(os.path.join(FLAGS.log_dir, "summaries.jsonl"), "a")
+    restored = resume(model, FLAGS.train_dir) if FLAGS.train_dir else None
+    if restored and is_chief:
+        out.write("restored %s (global_step %d)\n" % (restored, model.global_step))
+    lrn_rate = lr_fn(model.global_step) if restored else lr_begin     # _LearningRateSetterHook.begin
+    writer = SummaryWriter(FLAGS.log_dir) if (FLAGS.log_dir and is_chief) else None
+    fmt = getattr(FLAGS, "checkpoint_format", "npz")
+    if checkpoint_every is None:
+        checkpoint_every = int(getattr(FLAGS, "save_checkpoint_steps", 1000) or 1000)
     t0 = time.time()
     it = 0
+    last_saved = model.global_step if restored else -1
     while model.global_step < FLAGS.train_steps:
         model.lrn_rate = lrn_rate
         model.train_op()
         it += 1
         step = model.global_step
-        if it % log_every == 0 or step >= FLAGS.train_steps:
+        want_log = it % log_every == 0 or step >= FLAGS.train_steps
+        want_summ = writer is not None and (it == 1 or step % summary_every == 0)
+        if want_log or want_summ:
             xent, prec, cost = model.executor.scalars()
-            dt = time.time() - t0
-            out.write("step = %d, loss = %.6f, precision = %.4f, lr = %g (%.1f images/sec)\n" %
-                      (step, cost, prec, lrn_rate, it * FLAGS.batch_size * world / max(dt, 1e-9)))
-            out.flush()
-            if summaries is not None and step % 100 < log_every:
-                summaries.write(json.dumps({"step": step, "cross_entropy": xent, "cost": cost,
-                                            "learning_rate": lrn_rate, "Precision": prec}) + "\n")
-                summaries.flush()
+            if want_log:
+                dt = time.time() - t0
+                out.write("step = %d, loss = %.6f, precision = %.4f, lr = %g (%.1f images/sec)\n" %
+                          (step, cost, prec, lrn_rate, it * FLAGS.batch_size * world / max(dt, 1e-9)))
+                out.flush()
+            if want_summ:
+                writer.add_scalars(step, {"cross_entropy": xent, "cost": cost, "learning_rate": lrn_rate,
+                                          "Precision": prec})
+                writer.flush()
         lrn_rate = lr_fn(step)
-        if FLAGS.train_dir and is_chief and step % 1000 == 0:
-            save_checkpoint(model, FLAGS.train_dir, step)
+        if FLAGS.train_dir and is_chief and step % checkpoint_every == 0:
+            save_checkpoint(model, FLAGS.train_dir, step, fmt)
+            last_saved = step
     torch.cuda.synchronize()
-    if FLAGS.train_dir and is_chief:
-        save_checkpoint(model, FLAGS.train_dir, model.global_step)
+    if FLAGS.train_dir and is_chief and last_saved != model.global_step:
+        save_checkpoint(model, FLAGS.train_dir, model.global_step, fmt)
+    if writer is not None:
+        writer.close()
     return model
+
+
+def train(hps, lr_fn=cifar_learning_rate, log_every=20, out=sys.stdout):
+    """Training loop (reference :251-344)."""
+    rank, world = init_distributed()
+    images, labels = cifar_input.input_fn(True, FLAGS.train_data_path, FLAGS.batch_size, num_epochs=1000,
+                                          dataset=FLAGS.dataset, seed=FLAGS.seed)
+    model = resnet_model.ResNet(hps, images, labels, FLAGS.mode)
+    model.build_graph()
+    return run_training_loop(model, 0.1, lr_fn, world, out, log_every=log_every)
 
 
 def main(argv=None):
@@ -174,7 +176,10 @@ def main(argv=None):
     hps = resnet_model.HParams(num_classes=num_classes, lrn_rate=0.1, weight_decay_rate=_WEIGHT_DECAY, optimizer='mom')
     if FLAGS.mode == 'train':
         return train(hps)
-    raise ValueError("this build implements --mode=train only")
+    if FLAGS.mode == 'eval':
+        from . import resnet_cifar_eval
+        return resnet_cifar_eval.evaluate(hps)
+    raise ValueError("--mode must be train or eval")
 
 
 if __name__ == '__main__':

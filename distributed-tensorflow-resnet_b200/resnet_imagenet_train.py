@@ -9,7 +9,6 @@ synthetic standard-normal 224x224x3 images resident on the device.
 import argparse
 import os
 import sys
-import time
 
 import torch
 
@@ -52,23 +51,8 @@ def train(hps, out=sys.stdout, log_every=40):
     images, labels = synthetic_batch(FLAGS.batch_size, FLAGS.image_size, hps.num_classes, rank, dt, dev)
     model = resnet_model.ResNet(hps, images, labels, FLAGS.mode)
     model.build_graph()
-    lrn_rate = 0.4                        # _LearningRateSetterHook.begin (reference :241)
-    t0 = time.time()
-    it = 0
-    while model.global_step < FLAGS.train_steps:
-        model.lrn_rate = lrn_rate
-        model.train_op()
-        it += 1
-        step = model.global_step
-        if it % log_every == 0 or step >= FLAGS.train_steps:
-            xent, prec, cost = model.executor.scalars()
-            el = time.time() - t0
-            out.write("step = %d, loss = %.6f, precision = %.4f, lr = %g (%.1f images/sec)\n" %
-                      (step, cost, prec, lrn_rate, it * FLAGS.batch_size * world / max(el, 1e-9)))
-            out.flush()
-        lrn_rate = imagenet_learning_rate(step)
-    torch.cuda.synchronize()
-    return model
+    # _LearningRateSetterHook.begin sets 0.4 for the first run (reference :241); hooks as the CIFAR trainer
+    return _cifar.run_training_loop(model, 0.4, imagenet_learning_rate, world, out, log_every=log_every)
 
 
 def main(argv=None):

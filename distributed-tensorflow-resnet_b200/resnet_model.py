@@ -216,14 +216,25 @@ class ResNet(object):
         exactly R gradients per step, R = number of ranks (reference :104-120; main() overwrites
         replicas_to_aggregate with the worker count, resnet_cifar_train.py:375-376)."""
         import torch.distributed as dist
-        if dist.is_available() and dist.is_initialized() and (FLAGS.sync_replicas or FLAGS.use_horovod):
-            world = dist.get_world_size()
-            R = FLAGS.replicas_to_aggregate
-            if R is not None and int(R) != world:
-                raise ValueError("replicas_to_aggregate=%s must equal the number of ranks (%d): the reference "
-                                 "always sets it to the worker count" % (R, world))
-            return world, dist.get_rank()
-        return 1, 0
+        if not (dist.is_available() and dist.is_initialized()):
+            return 1, 0
+        world = dist.get_world_size()
+        if not (FLAGS.sync_replicas or FLAGS.use_horovod):
+            if world > 1:
+                # the reference's asynchronous PS mode is not carried over; R independent, silently
+                # diverging replicas would be the result of honouring the flags literally
+                raise ValueError("a process group with %d ranks is initialised but gradient aggregation is off "
+                                 "(sync_replicas=False and use_horovod=False): set FLAGS.sync_replicas=True (or "
+                                 "use_horovod=True), or run one process" % world)
+            return 1, 0
+        R = FLAGS.replicas_to_aggregate
+        if R is not None and int(R) != world:
+            raise ValueError("replicas_to_aggregate=%s must equal the number of ranks (%d): the reference always "
+                             "sets it to the worker count (resnet_cifar_train.py:375-376).  To aggregate over "
+                             "k < %d replicas launch k processes (torchrun --nproc-per-node k): the communicator, "
+                             "and with it the 1/k of the mean, is the set of ranks that exist"
+                             % (R, world, world))
+        return world, dist.get_rank()
 
     def _make_executor(self, train):
         world, rank = self._world()
@@ -260,6 +271,29 @@ class ResNet(object):
             pipe.next_batch()           # the dequeue that train_op depends on in the reference graph
         self._pulled_first = True
         self.executor.step()
+        self.global_step = self.executor.global_step
+
+    # ------------------------------------------------------------------ reference artefacts
+    def load_frozen_graph(self, path):
+        """Weights and BN moving statistics from a frozen GraphDef written by the reference
+        (resnet_cifar_frozen_model.py; consumed by resnet_cifar_predict_from_pd.py:66-103 through
+        import_graph_def), matched by TF variable name.  Before build_graph() the values become the
+        initial values; afterwards they are loaded into the running executor.  Returns the names."""
+        from . import tf_io
+        w = tf_io.read_frozen_graph(path)
+        if self.executor is None:
+            self.init_values = dict(getattr(self, "init_values", None) or {}, **w)
+        else:
+            missing = [v.name for v in self.graph.variables.values() if v.name not in w]
+            if missing:
+                raise KeyError("%s lacks %d variables of this model, e.g. %s" % (path, len(missing), missing[:3]))
+            self.executor.load_state_dict(w)
+        return sorted(w)
+
+    def load_checkpoint(self, path):
+        """`saver.restore(sess, path)`: an .npz of this build, a TF-V2 bundle prefix, or a frozen .pb."""
+        from .train_utils import load_checkpoint_file
+        self.executor.load_state_dict(load_checkpoint_file(path))
         self.global_step = self.executor.global_step
 
     # ------------------------------------------------------------------ fetchable values

@@ -39,7 +39,9 @@ typedef enum {
 } rn_status;
 
 const char* rn_last_error(void);
-/* ABI version; bumped whenever a signature changes. */
+/* ABI version; bumped whenever a signature changes.  The Python bindings (_lib.py) refuse a library
+ * whose rn_abi_version() differs from the version they were written against. */
+#define RN_ABI_VERSION 4
 int rn_abi_version(void);
 /* Number of kernel launches issued through this library by the calling process (all threads). */
 uint64_t rn_launch_count(void);
@@ -155,8 +157,10 @@ int rn_stem_s2d_plan_create(const rn_conv_desc* d, int kind, const void* u, cons
  *   (FusedBatchNorm epsilon 1.001e-5, decay 0.997, moving variance from the UNBIASED batch
  *   variance), the residual `inputs + shortcut` at :130 / :175, and FusedBatchNormGrad + ReluGrad
  *   + AddN from autodiff.  Also serves the upstream `_batch_norm` / `_relu(leakiness)` (biased
- *   moving variance, eps 1e-3, decay 0.9).  x viewed as [M = N*H*W, C]; C % 4 == 0 (f32) or
- *   C % 8 == 0 (bf16) for the vector path, any C otherwise.
+ *   moving variance, eps 1e-3, decay 0.9).  x viewed as [M = N*H*W, C]; C must be a multiple of 4 (f32)
+ *   or 8 (bf16) — every access is a 128-bit vector, other C return RN_ERR_UNSUPPORTED — and the
+ *   activation pointers (x, addend, sum_out, y, dy, dx, dx_addend) must be 16-byte aligned
+ *   (RN_ERR_INVALID otherwise).
  * ------------------------------------------------------------------------------------------ */
 size_t rn_bn_scratch_bytes(int64_t M, int32_t C);
 /* Statistics from per-CTA partial sums partials[nparts][C][2] written by a fused convolution epilogue
@@ -178,7 +182,8 @@ int rn_bn_stats_fwd(const void* x, const void* addend, void* sum_out, int64_t M,
  * live in a 512 KiB device array that is part of the library image (held by every GPU that loads the
  * library until the process exits).  The entry point performs no allocation of any kind.
  * Its first call on a device looks the array's address up (cudaGetSymbolAddress, that device
- * current): make that call during set-up, before starting any stream capture.  All calls on a
+ * current): make that call during set-up, before starting any stream capture.  On every call the
+ * device that owns `stream` must be the current device (the array used is the current device's).  All calls on a
  * device share the array; counters are re-zeroed at the start of each call, but calls that overlap
  * on the GPU race with each other — keep them ordered.  C is limited to 4096 channels (any M);
  * beyond that the call fails with RN_ERR_INVALID and rn_bn_stats_fwd must be used.
@@ -276,11 +281,15 @@ int rn_l2_sumsq(const float* w, int64_t n, const uint8_t* granule_mask, float* o
  *   bitcast((u & 0x7fffff)|0x3f800000) - 1 < 0.5.  If draws_in != NULL its int32 [B][3]
  *   (oy, ox, flip) are used instead.  draws_out (nullable) receives the (oy, ox, flip) used.
  *   train == 0: no pad/crop/flip (eval path, standardise only).
+ *   staged != 0: `records` holds only this batch — row b is the record of image b, e.g. a buffer
+ *   just copied from (pinned) host memory when the record file is not kept in HBM — while
+ *   indices[b] still names the record for the random draws, so a staged batch decodes to exactly
+ *   the same images as the resident path.
  * ------------------------------------------------------------------------------------------ */
 int rn_cifar_decode(const uint8_t* records, int64_t n_records, int32_t record_bytes, int32_t label_offset,
                     int32_t classes, const int32_t* indices, int32_t B, int32_t train, int32_t pad,
                     uint32_t seed_lo, uint32_t seed_hi, uint32_t epoch, const int32_t* draws_in,
-                    void* out_img, int32_t out_dtype, float* out_onehot, int32_t* out_labels,
+                    int32_t staged, void* out_img, int32_t out_dtype, float* out_onehot, int32_t* out_labels,
                     int32_t* draws_out, void* stream);
 
 /* ------------------------------------------------------------------------------------------
@@ -288,13 +297,19 @@ int rn_cifar_decode(const uint8_t* records, int64_t n_records, int32_t record_by
  * AddN / tf.pad at the call sites above).
  * ------------------------------------------------------------------------------------------ */
 int rn_cast(const void* src, void* dst, int64_t n, int32_t src_dtype, int32_t dst_dtype, void* stream);
-/* dst = beta*dst + src  (AddN of gradients when no fused path applies) */
+/* dst += src  (AddN of gradients when no fused path applies) */
 int rn_add_inplace(void* dst, const void* src, int64_t n, int32_t dtype, void* stream);
 /* y = a + b (forward residual add when it cannot be fused into a BN statistics pass) */
 int rn_add(const void* a, const void* b, void* y, int64_t n, int32_t dtype, void* stream);
 /* NHWC channel pad/copy: dst[..., 0:Cdst] = src[..., 0:Csrc] zero-extended (stem 3 -> 8 channels). */
 int rn_pad_channels(const void* src, void* dst, int64_t pixels, int32_t Csrc, int32_t Cdst, int32_t src_dtype,
                     int32_t dst_dtype, void* stream);
+
+/* CRC-32C of a HOST buffer, continuing from `crc` (0 to start).  Host-only helper for reading and
+ * writing the reference's TF-V2 checkpoint bundles (what tf.train.Saver / MonitoredTrainingSession
+ * produce at resnet_cifar_train.py:315-319 and saver.restore consumes at resnet_cifar_eval.py:85):
+ * both the tensor data and the index-table blocks carry masked CRC-32C checksums. */
+uint32_t rn_crc32c(const void* data, size_t n, uint32_t crc);
 
 #ifdef __cplusplus
 }

@@ -11,6 +11,7 @@ stubs).  The outputs are committed so that the GPU box (which has no
   cifar50_train_graph.json     training MetaGraphDef (model.ckpt-107738.meta): variables,
                                optimizer/loss/BN-update constants, initialisers, and the verbatim
                                tf.data function bodies (decode / pad / crop / flip / standardise)
+  ref_model.ckpt-107738.index  the reference's TF-V2 checkpoint index file as it is (binary, 14 KB)
 
 Usage:  python tests/golden/make_golden.py
 """
@@ -239,8 +240,19 @@ def train_meta():
     print("train meta:", len(variables), "variables,", len(trainable), "trainable,", len(funcs), "functions")
 
 
+def checkpoint_index():
+    """The reference's own TF-V2 checkpoint index (14 KB, 403 tensor entries: every variable, its
+    Momentum slot, global_step, ...).  The .data shards are not in the reference tree, so the index is
+    what pins the bundle reader of distributed-tensorflow-resnet_b200/tf_io.py (names, shapes, dtypes,
+    offsets, block checksums)."""
+    import shutil
+    shutil.copyfile(os.path.join(REF, "model.ckpt-107738.index"), os.path.join(OUT, "ref_model.ckpt-107738.index"))
+    print("checkpoint index copied")
+
+
 if __name__ == "__main__":
     if not os.path.isdir(REF):
         sys.exit("reference fixtures not found at " + REF)
     frozen()
     train_meta()
+    checkpoint_index()

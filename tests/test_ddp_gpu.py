@@ -12,6 +12,15 @@ import torch
 pytestmark = pytest.mark.gpu
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
+
+def _free_port():
+    """A TCP port nobody is listening on right now (a fixed pid-derived port collides when two torchrun
+    rendezvous of one pytest process follow each other closely)."""
+    import socket
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
 _WORKER = r'''
 import os, sys, numpy as np, torch, torch.distributed as dist
 sys.path.insert(0, sys.argv[1]); sys.path.insert(0, os.path.join(sys.argv[1], "tests"))
@@ -63,7 +72,7 @@ def test_two_gpu_step_matches_oracle_mean_of_replicas(tmp_path, mode):
         pytest.skip("needs 2 GPUs")
     script = tmp_path / "w.py"
     script.write_text(_WORKER)
-    port = 29600 + os.getpid() % 1000
+    port = _free_port()
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
            "--master-addr", "127.0.0.1", "--master-port", str(port), str(script), ROOT, mode]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=150)

@@ -13,6 +13,15 @@ import torch
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
+def _free_port():
+    """A TCP port nobody is listening on right now (a fixed pid-derived port collides when two torchrun
+    rendezvous of one pytest process follow each other closely)."""
+    import socket
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
 def test_cabi_library_exports_every_declared_symbol():
     from distributed_tensorflow_resnet_b200 import _lib
     hdr = open(os.path.join(ROOT, "include", "rn_b200.h")).read()
@@ -24,7 +33,7 @@ def test_cabi_library_exports_every_declared_symbol():
     for name in sorted(declared):
         assert hasattr(so, name), "symbol %s declared in include/rn_b200.h is not exported" % name
     assert declared == set(_lib.SIGNATURES), (declared ^ set(_lib.SIGNATURES))
-    assert so.rn_abi_version() == 3
+    assert so.rn_abi_version() == _lib.ABI_VERSION == 4
 
 
 def test_cabi_argument_errors_without_gpu():
@@ -35,7 +44,7 @@ def test_cabi_argument_errors_without_gpu():
     d = ConvDesc(1, 8, 8, 4, 9, 9, 4, 3, 1, 0, 0)       # output does not fit
     assert lib.rn_conv2d_fprop(ctypes.byref(d), 1, 1, 1, None) == -1
     assert lib.rn_bn_stats_fwd(None, None, None, 10, 8, 0, 1e-5, 0.9, 1, None, None, None, None, None, 0, None) == -1
-    assert lib.rn_cifar_decode(1, 10, 3000, 0, 10, None, 4, 1, 4, 0, 0, 0, None, 1, 0, None, None, None, None) == -1
+    assert lib.rn_cifar_decode(1, 10, 3000, 0, 10, None, 4, 1, 4, 0, 0, 0, None, 0, 1, 0, None, None, None, None) == -1
     assert "record" in last_error()
     assert lib.rn_sgd_momentum_fused(1, 1, 1, None, 100, None, 1, 1.0, 0.0, 0.9, 1, None, None, 0, None) == -1
 
@@ -222,9 +231,108 @@ def test_world_size_2_aggregation_over_gloo(tmp_path):
     flat fusion buffer times 1/R equals the oracle's aggregate_mean (gloo, 2 processes, CPU)."""
     script = tmp_path / "w.py"
     script.write_text(_GLOO_WORKER)
-    port = 29500 + os.getpid() % 2000
+    port = _free_port()
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
            "--master-addr", "127.0.0.1", "--master-port", str(port), str(script), ROOT]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
     assert "rank 0 ok" in r.stdout and "rank 1 ok" in r.stdout
+
+
+def test_tf_checkpoint_index_reader_on_the_reference_fixture():
+    """tf_io's LevelDB-table / BundleEntryProto reader against the reference's own checkpoint index
+    (test/resnet50-cifar-ckpt-20190218/model.ckpt-107738.index, committed unchanged under tests/golden/):
+    403 tensor entries, every block checksum valid, names / shapes == the training graph fixture, data
+    offsets contiguous in sorted-name order (how BundleWriter lays the shard out)."""
+    import json
+    from distributed_tensorflow_resnet_b200 import tf_io
+    idx = tf_io.read_checkpoint_index(os.path.join(ROOT, "tests", "golden", "ref_model.ckpt-107738"))
+    hdr = idx.pop("")
+    assert hdr["num_shards"] == 1 and len(idx) == 403
+    g = json.load(open(os.path.join(ROOT, "tests", "golden", "cifar50_train_graph.json")))
+    shapes = {v["name"]: v["shape"] for v in g["variables"]}
+    assert set(shapes) <= set(idx) | {"global_step"} or set(idx) >= set(shapes)
+    for name, e in idx.items():
+        if name in shapes:
+            assert e["shape"] == shapes[name], name
+    for name in g["trainable_variables"]:
+        assert name in idx and name + "/Momentum" in idx and idx[name + "/Momentum"]["shape"] == idx[name]["shape"]
+    assert idx["global_step"]["dtype"] == tf_io.DT_INT64 and idx["global_step"]["shape"] == []
+    off = 0
+    for name in sorted(idx):
+        assert idx[name]["offset"] == off and idx[name]["shard_id"] == 0, name
+        off += idx[name]["size"]
+    assert idx["conv2d/kernel"]["size"] == 3 * 3 * 3 * 16 * 4
+    # the frozen GraphDef of the reference, when the reference tree is present (build container only)
+    pb = "/root/reference/test/resnet50-cifar-ckpt-20190218/resnet50_cifar_frozen_model_eval.pb"
+    if os.path.exists(pb):
+        w = tf_io.read_frozen_graph(pb)
+        z = np.load(os.path.join(ROOT, "tests", "golden", "cifar50_frozen_weights.npz"))
+        assert set(w) == set(z.files) and all(np.array_equal(w[k], z[k]) for k in z.files)
+
+
+def test_tf_checkpoint_and_frozen_graph_round_trip(tmp_path):
+    from distributed_tensorflow_resnet_b200 import tf_io
+    assert tf_io.crc32c(b"123456789") == 0xE3069283 and tf_io.crc32c(bytes(32)) == 0x8A9136AA     # RFC 3720 vectors
+    assert tf_io.crc32c(b"6789", tf_io.crc32c(b"12345")) == 0xE3069283                              # incremental
+    rng = np.random.default_rng(0)
+    t = {"conv2d/kernel": rng.standard_normal((3, 3, 3, 16)).astype(np.float32),
+         "conv2d/kernel/Momentum": rng.standard_normal((3, 3, 3, 16)).astype(np.float32),
+         "dense/bias": np.arange(10, dtype=np.float32), "global_step": np.int64(107738)}
+    t.update({"batch_normalization_%d/gamma" % i: rng.standard_normal(64).astype(np.float32) for i in range(400)})
+    prefix = str(tmp_path / "model.ckpt-107738")
+    tf_io.write_checkpoint(prefix, t)
+    assert sorted(os.listdir(tmp_path)) == ["model.ckpt-107738.data-00000-of-00001", "model.ckpt-107738.index"]
+    r = tf_io.read_checkpoint(prefix)
+    assert set(r) == set(t) and all(np.array_equal(r[k], t[k]) and r[k].shape == np.shape(t[k]) for k in t)
+    raw = bytearray(open(prefix + ".data-00000-of-00001", "rb").read())
+    raw[100] ^= 1
+    open(prefix + ".data-00000-of-00001", "wb").write(raw)
+    with pytest.raises(ValueError, match="checksum"):
+        tf_io.read_checkpoint(prefix)
+    pb = str(tmp_path / "frozen.pb")
+    wts = {k: v for k, v in t.items() if k != "global_step"}
+    tf_io.write_frozen_graph(pb, wts)
+    back = tf_io.read_frozen_graph(pb)
+    assert set(back) == set(wts) and all(np.array_equal(back[k], wts[k]) for k in wts)
+
+
+def test_summary_writer_produces_tensorboard_events(tmp_path):
+    from distributed_tensorflow_resnet_b200.train_utils import SummaryWriter, read_event_scalars
+    w = SummaryWriter(str(tmp_path))
+    w.add_scalars(100, {"cross_entropy": 2.25, "cost": 2.5, "learning_rate": 0.1, "Precision": 0.125})
+    w.add_scalars(200, {"Precision": 0.25, "Best Precision": 0.25})
+    w.close()
+    assert any("tfevents" in f for f in os.listdir(tmp_path))
+    got = read_event_scalars(str(tmp_path))
+    assert (100, "cost", 2.5) in got and (200, "Best Precision", 0.25) in got and len(got) == 6
+    lines = open(tmp_path / "summaries.jsonl").read().strip().split("\n")
+    assert len(lines) == 2 and '"Precision": 0.125' in lines[0]
+
+
+def test_aggregation_disabled_with_several_ranks_is_refused(tmp_path):
+    """A process group with R > 1 ranks and both aggregation flags off would train R diverging replicas."""
+    script = tmp_path / "w.py"
+    script.write_text(r'''
+import os, sys, torch, torch.distributed as dist
+sys.path.insert(0, sys.argv[1])
+dist.init_process_group("gloo")
+from distributed_tensorflow_resnet_b200 import resnet_model, FLAGS
+FLAGS.reset(); FLAGS.update(sync_replicas=False, use_horovod=False)
+m = resnet_model.ResNet(resnet_model.HParams(10, 0.1, 2e-4, 'mom'), torch.zeros(2, 32, 32, 3), torch.zeros(2, 10), 'train')
+try:
+    m._world(); print("NO_ERROR")
+except ValueError as e:
+    print("REFUSED" if "aggregation is off" in str(e) else "WRONG " + str(e))
+FLAGS.update(sync_replicas=True, replicas_to_aggregate=1)
+try:
+    m._world(); print("NO_ERROR")
+except ValueError as e:
+    print("HINT" if "--nproc-per-node k" in str(e) else "WRONG " + str(e))
+dist.destroy_process_group()
+''')
+    port = _free_port()
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr",
+           "127.0.0.1", "--master-port", str(port), str(script), ROOT]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=240)
+    assert r.returncode == 0 and r.stdout.count("REFUSED") == 2 and r.stdout.count("HINT") == 2, r.stdout + r.stderr[-3000:]

@@ -354,7 +354,7 @@ def test_cifar_decode_bit_exact_indices(dataset, pad):
     for epoch in (0, 5):
         want, woh, wlab, (oy, ox, fl) = co.decode(rec, idx, dataset=dataset, train=True, pad=pad, epoch=epoch, seed=(7 << 32) | 9)
         check(lib.rn_cifar_decode(ptr(R), n, rec.shape[1], off, classes, ptr(I), B, 1, pad, 9, 7, epoch, None,
-                                  ptr(img), RN_F32, ptr(oh), ptr(lab), ptr(dr), stream()), "decode")
+                                  0, ptr(img), RN_F32, ptr(oh), ptr(lab), ptr(dr), stream()), "decode")
         d = dr.cpu().numpy()
         assert np.array_equal(d[:, 0], oy) and np.array_equal(d[:, 1], ox) and np.array_equal(d[:, 2], fl)  # bit-exact
         assert np.array_equal(lab.cpu().numpy(), wlab) and np.array_equal(oh.cpu().numpy(), woh)
@@ -362,21 +362,28 @@ def test_cifar_decode_bit_exact_indices(dataset, pad):
         # the uint8 -> float gather is exact: same zero pattern (padding) and same ordering of values
         assert np.array_equal(got == got.min(axis=(1, 2, 3), keepdims=True), want == want.min(axis=(1, 2, 3), keepdims=True))
         assert np.abs(got - want).max() <= 1e-6 * np.abs(want).max()
+    # staged batch (only the B records of the batch, e.g. just copied from host memory): identical images / draws
+    Rb = dev(torch.from_numpy(np.ascontiguousarray(rec[idx])))
+    img2 = torch.empty_like(img)
+    dr2 = torch.empty_like(dr)
+    check(lib.rn_cifar_decode(ptr(Rb), B, rec.shape[1], off, classes, ptr(I), B, 1, pad, 9, 7, 5, None,
+                              1, ptr(img2), RN_F32, ptr(oh), ptr(lab), ptr(dr2), stream()), "decode staged")
+    assert torch.equal(img2, img) and torch.equal(dr2, dr)
     # explicit draws, bf16 output, eval mode
     draws = np.stack([oy, ox, fl], 1).astype(np.int32)
     D = dev(torch.from_numpy(draws))
     imgb = torch.empty(B, 32, 32, 3, dtype=torch.bfloat16, device="cuda")
-    check(lib.rn_cifar_decode(ptr(R), n, rec.shape[1], off, classes, ptr(I), B, 1, pad, 0, 0, 0, ptr(D), ptr(imgb),
+    check(lib.rn_cifar_decode(ptr(R), n, rec.shape[1], off, classes, ptr(I), B, 1, pad, 0, 0, 0, ptr(D), 0, ptr(imgb),
                               RN_BF16, ptr(oh), None, None, stream()), "decode draws")
     assert torch.equal(imgb.cpu(), torch.from_numpy(want).to(torch.bfloat16).cpu()) or \
         np.abs(imgb.float().cpu().numpy() - want).max() < 2e-2
     ev, *_ = co.decode(rec, idx, dataset=dataset, train=False)
-    check(lib.rn_cifar_decode(ptr(R), n, rec.shape[1], off, classes, ptr(I), B, 0, pad, 0, 0, 0, None, ptr(img),
+    check(lib.rn_cifar_decode(ptr(R), n, rec.shape[1], off, classes, ptr(I), B, 0, pad, 0, 0, 0, None, 0, ptr(img),
                               RN_F32, ptr(oh), None, None, stream()), "decode eval")
     assert np.abs(img.cpu().numpy() - ev).max() <= 1e-6 * np.abs(ev).max()
     assert np.all(img[0].cpu().numpy() == 0)            # constant image: variance 0 -> exactly 0
     # empty batch is a no-op
-    check(lib.rn_cifar_decode(ptr(R), n, rec.shape[1], off, classes, ptr(I), 0, 1, pad, 0, 0, 0, None, ptr(img),
+    check(lib.rn_cifar_decode(ptr(R), n, rec.shape[1], off, classes, ptr(I), 0, 1, pad, 0, 0, 0, None, 0, ptr(img),
                               RN_F32, None, None, None, stream()), "decode empty")
 
 
@@ -388,7 +395,7 @@ def test_decode_full_epoch_checksum():
     R = dev(torch.from_numpy(rec))
     img = torch.empty(n, 32, 32, 3, device="cuda")
     lab = torch.empty(n, dtype=torch.int32, device="cuda")
-    check(lib.rn_cifar_decode(ptr(R), n, 3073, 0, 10, None, n, 1, 4, 0, 0, 0, None, ptr(img), RN_F32, None, ptr(lab),
+    check(lib.rn_cifar_decode(ptr(R), n, 3073, 0, 10, None, n, 1, 4, 0, 0, 0, None, 0, ptr(img), RN_F32, None, ptr(lab),
                               None, stream()), "decode")
     assert torch.equal(lab.cpu(), torch.from_numpy(rec[:, 0].astype(np.int32)))
     flat = img.view(n, -1)

@@ -42,6 +42,14 @@ def _op_name_map(model):
     return {t.name: t.name for t in model.graph.tensors.values()}
 
 
+# bf16 mode END TO END (measured on B200): relative L2 error of every stored
+# activation / every parameter gradient against the oracle that rounds to bf16 where the CUDA path stores
+# bf16.  An untrained 50-layer net amplifies a one-ulp bf16 difference (0.4 %) layer by layer, which is why
+# the per-layer max-norm 2e-2 criterion is enforced launch by launch (test_layerwise_gpu.py, worst 3.7e-3)
+# and the end-to-end bound is on the L2 norm.
+BF16_ACT_L2 = 0.25
+BF16_GRAD_L2 = 0.5
+
 CASES = [
     ("official_cifar", dict(dataset="cifar10", resnet_size=14), (8, 32, 32, 3), 10, None),
     ("official_imagenet", dict(dataset="imagenet", resnet_size=50), (8, 96, 96, 3), 16, None),
@@ -84,17 +92,33 @@ def test_training_step_parity(case, mode):
     # first 16 tensors (5e-2); the per-layer max-norm 2e-2 criterion is enforced launch by launch, on
     # every layer, in test_layerwise_gpu.py (measured worst case there: 3.7e-3).
     checked = 0
+    worst_act = ("", 0.0)
     for name, t in model.graph.tensors.items():
         if name in net.acts and t.buf is not None and name not in ("X", "Y"):
             if mode == "f32":
                 e = rel_err(t.buf.float(), net.acts[name].val)
                 assert e < tol, (name, e)
-            elif checked < 16:
+            else:
+                # EVERY stored activation, relative L2 error against the bf16-storage oracle
                 w_ = net.acts[name].val.double()
                 e = ((t.buf.double().cpu() - w_).norm() / w_.norm()).item()
-                assert e < 5e-2, (name, e)
+                if e > worst_act[1]:
+                    worst_act = (name, e)
+                assert e < BF16_ACT_L2, (name, e)
             checked += 1
     assert checked >= 10
+    if mode == "bf16":
+        # every parameter gradient, relative L2 (a ReLU-mask flip moves single elements by O(1) but the L2
+        # norm of a whole gradient tensor only by the flipped fraction)
+        worst_g = ("", 0.0)
+        for v in model.graph.trainable_variables():
+            w_ = net.param_grads[v.name].double()
+            e = ((ex.var_view(v.name, "G").double().cpu() - w_).norm() / (w_.norm() + 1e-30)).item()
+            if e > worst_g[1]:
+                worst_g = (v.name, e)
+        print("bf16 end to end [%s]: worst activation rel-L2 %.3e (%s), worst parameter-gradient rel-L2 %.3e (%s)"
+              % (kind, worst_act[1], worst_act[0], worst_g[1], worst_g[0]))
+        assert worst_g[1] < BF16_GRAD_L2, worst_g
     xent, prec, cost = ex.scalars()
     ltol = tol if mode == "f32" else 1e-1
     assert abs(xent - float(out["xent"])) < ltol * abs(float(out["xent"]))
@@ -165,49 +189,65 @@ def test_frozen_reference_weights_inference():
         assert rel_err(model.graph.tensors[name].buf, net.acts[name].val) < 1e-4
 
 
-@pytest.mark.parametrize("use_graph", [False, True])
-def test_loss_trajectory_resnet20(use_graph):
-    """C1: ResNet-20 (upstream builders, 3 units), momentum SGD lr 0.1 wd 2e-4, synthetic CIFAR
-    records through the GPU decode kernel; loss trajectory vs the CPU oracle fed the oracle's own
-    decode of the same records and draws.  Batch 32 x 40 steps keeps the CPU side short."""
-    B, steps = 32, 40
+def _c1_run(dtype, use_graph, steps, init):
+    """BASELINE config C1 exactly as north_star states it: upstream ResNet-20, batch 128, momentum SGD
+    lr 0.1, wd 2e-4 (resnet_single.py:194-202), synthetic CIFAR records through the GPU decode kernel."""
+    B = 128
     FLAGS.reset()
-    FLAGS.update(compute_dtype="f32", use_cuda_graph=use_graph, dataset="cifar10", seed=5)
+    FLAGS.update(compute_dtype=dtype, use_cuda_graph=use_graph, dataset="cifar10", seed=5)
     hps = resnet_model.HParams(batch_size=B, num_classes=10, min_lrn_rate=1e-4, lrn_rate=0.1, num_residual_units=3,
                                use_bottleneck=False, weight_decay_rate=2e-4, relu_leakiness=0.1, optimizer='mom')
-    images, labels = cifar_input.input_fn(True, "synthetic:2048", B, dataset="cifar10", seed=5)
-    pipe = images._rn_pipeline
+    images, labels = cifar_input.input_fn(True, "synthetic:8192", B, dataset="cifar10", seed=5)
     model = resnet_model.ResNet(hps, images, labels, "train")
+    model.init_values = init
     model.build_graph()
-    ex = model.executor
-    params = {k: v for k, v in ex.state_dict().items() if not k.endswith("/Momentum") and k != "global_step"}
-    # fp64 oracle = truth; fp32 oracle = the TF-CPU stand-in.  SGD at lr 0.1 amplifies rounding
-    # differences step by step, so the bound is self-calibrating: the CUDA fp32 path may drift from
-    # the truth at most 10x as far as the fp32 CPU restatement has drifted by the same step.
-    net64 = ro.UpstreamResNet(10, 3, False, 0.1, dtype=torch.float64, params=params)
-    net32 = ro.UpstreamResNet(10, 3, False, 0.1, dtype=torch.float32, params=params)
-    tr64, tr32 = ro.Trainer(net64, 2e-4, "mom", bn_decay=0.9), ro.Trainer(net32, 2e-4, "mom", bn_decay=0.9)
-    rec = co.synthetic_records(2048, "cifar10", 5)
-    # replay the pipeline's index stream on the host
-    shadow = cifar_input.RecordPipeline.__new__(cifar_input.RecordPipeline)
-    shadow.__dict__.update(shuffle=True, seed=5, n=2048, rank=0, world=1, B=B, epoch=0, _cursor=0)
-    shadow._order = shadow._epoch_order(0)
-    got, want, cpu32 = [], [], []
+    cost = []
     for s in range(steps):
-        idx = shadow.next_indices()
-        img, onehot, _, _ = co.decode(rec, idx, train=True, pad=4, epoch=shadow.epoch, seed=5)
-        xi, yi = torch.from_numpy(img), torch.from_numpy(onehot)
-        want.append(float(tr64.step([(xi.double(), yi.double())], 0.1)[0]["cost"]))
-        cpu32.append(float(tr32.step([(xi, yi)], 0.1)[0]["cost"]))
         model.lrn_rate = 0.1
         model.train_op()
-        got.append(model.cost)
-    got, want, cpu32 = np.array(got), np.array(want), np.array(cpu32)
+        cost.append(model.cost)
+    return np.array(cost)
+
+
+def test_loss_trajectory_c1_200_steps():
+    """north_star: "the same loss trajectory over the first 200 steps on a fixed seed".  The CPU oracle's
+    200-step trajectories (fp64 = truth, fp32 = the TF-CPU stand-in; 25 minutes of CPU time) are committed
+    as tests/golden/c1_trajectory.json by tests/golden/make_trajectory.py together with the initial weights.
+    SGD at lr 0.1 amplifies rounding differences step by step, so the fp32 bound is self-calibrating: the
+    CUDA fp32 path may drift from the truth at most 10x as far as the fp32 CPU restatement has drifted by the
+    same step.  bf16 mode must stay inside a stated envelope of the fp32 curve."""
+    import json
+    import os
+    gold = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+    ref = json.load(open(os.path.join(gold, "c1_trajectory.json")))
+    z = np.load(os.path.join(gold, "c1_trajectory_init.npz"))
+    init = {k: z[k] for k in z.files}
+    steps = ref["config"]["steps"]
+    assert steps == 200 and ref["config"]["batch"] == 128
+    want, cpu32 = np.array(ref["f64"]["cost"]), np.array(ref["f32"]["cost"])
+    got = _c1_run("f32", True, steps, init)
     assert np.all(np.isfinite(got))
     assert abs(got[0] - want[0]) < 1e-5 * want[0]
     env = np.maximum.accumulate(np.abs(cpu32 - want))
-    assert np.all(np.abs(got - want) <= 10 * env + 1e-5 * np.abs(want)), (np.abs(got - want)[-8:], env[-8:])
+    dev_ = np.abs(got - want)
+    print("C1 fp32 trajectory: max |cuda - fp64| %.3e, max |cpu32 - fp64| %.3e, final cost %.4f (oracle %.4f)"
+          % (dev_.max(), env[-1], got[-1], want[-1]))
+    assert np.all(dev_ <= 10 * env + 1e-5 * np.abs(want)), (dev_[-8:], env[-8:])
     assert want[-1] < want[0]            # it trains
+    # eager launches and the captured graph run the same kernels in the same order: bit-identical curve
+    got_eager = _c1_run("f32", False, 40, init)
+    assert np.array_equal(got_eager, got[:40])
+    # bf16: same curve within 2 % of the running cost for the first 20 steps (before SGD chaos separates
+    # even fp32 from fp64), and afterwards a curve of the same shape: the smoothed cost (window 20) within 10 %
+    bf = _c1_run("bf16", True, steps, init)
+    assert np.all(np.isfinite(bf))
+    rel = np.abs(bf - got) / np.abs(got)
+    k = np.ones(20) / 20
+    sm = np.abs(np.convolve(bf, k, "valid") - np.convolve(got, k, "valid")) / np.convolve(got, k, "valid")
+    print("C1 bf16 trajectory: max rel diff first 20 steps %.3e, smoothed max rel diff %.3e, final %.4f vs %.4f"
+          % (rel[:20].max(), sm.max(), bf[-1], got[-1]))
+    assert rel[:20].max() < 2e-2 and sm.max() < 0.10
+    assert bf[-1] < bf[0]
 
 
 def test_sgd_optimizer_and_eval_mode_errors():

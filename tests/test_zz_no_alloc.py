@@ -48,6 +48,14 @@ def test_noalloc_matches_caller_scratch_entry_on_two_calls(case):
             assert rel_err(b, a) < 1e-5, (what, call)
         if addend is not None:
             assert torch.equal(ref[4], got[4])          # the fused sum z = x + addend is bit-identical
+        # and directly against the fp64 oracle (FusedBatchNorm semantics, resnet_model_official.py:41-50):
+        # statistics of the STORED sum, biased variance in rstd, unbiased variance in the moving average
+        z64 = x.double() if addend is None else (x.float() + addend.float()).to(tdt).double()
+        mu = z64.mean(0)
+        var = z64.var(0, unbiased=False)
+        assert rel_err(got[0], mu) < 1e-5 and rel_err(got[1], 1.0 / torch.sqrt(var + EPS)) < 1e-5, call
+        assert rel_err(got[2], 0.25 - (0.25 - mu) * (1 - DECAY)) < 1e-5, call
+        assert rel_err(got[3], 1.5 - (1.5 - var * M / (M - 1)) * (1 - DECAY)) < 1e-5, call
 
 
 def test_noalloc_rejects_sizes_beyond_its_limit():
