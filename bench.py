@@ -547,6 +547,7 @@ def run_ours(args):
         per_launch = profile_step(ex, model.graph, iters=2)
         if args.dump_layers:
             cf = conv_flops(model.graph)
+            plans = ex.describe_plans()
             with open(args.dump_layers, "w") as f:
                 for name, ms_ in per_launch.items():
                     fam, _, key = name.partition(":")
@@ -559,7 +560,7 @@ def run_ours(args):
                         b_ = hbm_bytes(name, ex, model.graph)
                         if b_:
                             extra = " %8.1f GB/s" % (b_ / ms_ / 1e6)
-                    f.write("%-44s %9.4f ms%s\n" % (name, ms_, extra))
+                    f.write("%-44s %9.4f ms%s%s\n" % (name, ms_, extra, ("  [" + plans[name] + "]") if name in plans else ""))
         roof, table, prof_total = roofline_report(ex, model.graph, per_launch, pk, clocks)
         cpu = None
         if not args.no_cpu_baseline and world == 1:      # rank 0 at N = 1 only: at N > 1 the other ranks' GPUs would idle

@@ -89,6 +89,7 @@ SIGNATURES = {
     "rn_bn_bwd_finalize": (C.c_int, [vp, i32, i32, vp, vp, vp]),
     "rn_convtc_run": (C.c_int, [vp, f32, vp]),
     "rn_convtc_plan_destroy": (C.c_int, [vp]),
+    "rn_convtc_plan_describe": (C.c_int, [vp, C.c_char_p, sz]),
     "rn_weights_to_bf16": (C.c_int, [vp, C.c_int, C.c_int, C.c_int, vp, vp, vp]),
     "rn_relayout_job_bytes": (sz, []),
     "rn_weights_to_bf16_batched": (C.c_int, [vp, i32, vp]),
@@ -142,6 +143,12 @@ def last_error():
 def check(rc, what=""):
     if rc != 0:
         raise RnError("%s failed (status %d): %s" % (what or "librn_b200 call", rc, last_error()))
+
+
+def describe_plan(plan):
+    buf = C.create_string_buffer(256)
+    check(_so.rn_convtc_plan_describe(plan, buf, 256), "rn_convtc_plan_describe")
+    return buf.value.decode()
 
 
 def launch_count():

@@ -52,8 +52,10 @@ struct TcConvParams {
   int acc_m;                      // pixel tiles per CTA iteration (they share every B tile): 1, 2 or 4
   int tstages;                    // TMEM accumulator sets (2 = epilogue overlaps the next tile's MMAs)
   int b_mn;                       // 1: B operand is MN-major (fprop reads the HWIO weights as they are)
-  int b_boxes;                    // MN-major: TMA boxes per stage (block_n / gw), each kc rows of gw channels
+  int b_boxes;                    // MN-major: TMA boxes per stage and CTA (block_n / gw, halved for a CTA pair), each kc rows of gw channels
   uint32_t b_box_bytes;
+  int pair;                       // 1: launched as clusters of two CTAs issuing tcgen05.mma.cta_group::2 (M = 256: this CTA's 128
+                                  // pixels and its peer's; each CTA loads HALF of the B tile)
   // fused epilogue (fprop, 64-channel store groups only)
   int fuse_stats;                 // per-channel sum / sum of squares of the STORED bf16 output -> stat_partials[CTA][ncols][2]
   int fuse_add;                   // OUT = bf16(bf16(result) + residual): the residual tile arrives through r_map (warp 6)
@@ -72,10 +74,14 @@ struct TcConvParams {
 constexpr int TC_RES_SLOTS_MAX = 6;        // upper bound of TcConvParams::res_slots (tiles of 16 KB in flight)
 constexpr int TC_THREADS_RES = TC_CONV_THREADS + 32;
 
-// FUSED = false compiles the plain epilogue only (fprop / dgrad without fusion keep their registers and schedule)
-template <bool FUSED>
+// FUSED = false compiles the plain epilogue only (fprop / dgrad without fusion keep their registers and schedule).
+// PAIR = true: the grid is made of 2-CTA clusters; the pair works on two neighbouring groups of pixel tiles with ONE
+// stream of tcgen05.mma.cta_group::2 instructions issued by the leader CTA (see rn_tc_common.cuh).
+template <bool FUSED, bool PAIR>
 __global__ void __launch_bounds__(FUSED ? TC_THREADS_RES : TC_CONV_THREADS, 1)
 conv_tc_kernel(const __grid_constant__ TcConvParams p) {
+  const uint32_t cta_rank = PAIR ? cluster_ctarank() : 0u;
+  const bool leader = cta_rank == 0u;
   const bool fuse_add = FUSED && p.fuse_add;
   const bool fuse_bnbwd = FUSED && p.fuse_bnbwd;
   const bool fuse_stats = FUSED && (p.fuse_stats || p.fuse_bnbwd);      // both keep per-channel running sums
@@ -105,7 +111,8 @@ conv_tc_kernel(const __grid_constant__ TcConvParams p) {
   const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
   if (warp == 0 && lane == 0) {
     for (int i = 0; i < p.stages; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], TC_EPI_WARPS); }
+    // pair: the leader's tempty collects the epilogue warps of BOTH CTAs (the peer's arrive remotely)
+    for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], PAIR ? 2 * TC_EPI_WARPS : TC_EPI_WARPS); }
     for (int i = 0; i < TC_RES_SLOTS_MAX; ++i) { mbar_init(&rfull[i], 1); mbar_init(&rempty[i], TC_EPI_WARPS); }
     fence_barrier_init();
     tma_prefetch_desc(&p.a_map[0]);
@@ -114,13 +121,14 @@ conv_tc_kernel(const __grid_constant__ TcConvParams p) {
     if (use_ring) tma_prefetch_desc(&p.r_map);
   }
   if (warp == 1) {
-    tmem_alloc(tmem_slot, p.tmem_cols);
-    tmem_relinquish();
+    if (PAIR) { tmem_alloc_pair(tmem_slot, p.tmem_cols); tmem_relinquish_pair(); }
+    else      { tmem_alloc(tmem_slot, p.tmem_cols); tmem_relinquish(); }
   }
   if (fuse_stats && warp >= 2 && warp < 2 + TC_EPI_WARPS)
     for (int i = threadIdx.x - 64; i < 2 * p.ncols_total; i += TC_EPI_THREADS) pacc[i] = 0.f;
   tc_fence_before();
-  __syncthreads();
+  if (PAIR) cluster_sync_all();       // the peer's barriers and tensor memory exist before anything targets them
+  else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   // everything above (barriers, TMEM, descriptor prefetch) overlapped the previous kernel's tail
@@ -137,22 +145,26 @@ conv_tc_kernel(const __grid_constant__ TcConvParams p) {
   }
 
   // work item = (group of acc_m consecutive pixel tiles, column tile); the acc_m tiles share each B tile
+  // pair: a work item covers 2 * acc_m pixel tiles (acc_m per CTA); tiles past the end have out-of-range
+  // coordinates (TMA zero-fills their loads and clips their stores), so both CTAs always run the same pipeline
   const int m_tiles = p.tiles_w * p.tiles_h * p.tiles_n;
   const int m_groups = (m_tiles + p.acc_m - 1) / p.acc_m;
-  const int total = m_groups * p.n_tiles;
+  const int total = PAIR ? ((m_groups + 1) / 2) * p.n_tiles : m_groups * p.n_tiles;
+  const int wstart = PAIR ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+  const int wstep = PAIR ? (int)(gridDim.x >> 1) : (int)gridDim.x;
   const int k_iters = p.taps * p.k_chunks;
   const uint32_t a_tx = (uint32_t)(p.BW * p.BH * p.BN) * (uint32_t)(p.kc * 2);
-  const uint32_t b_tx = (uint32_t)p.block_n * (uint32_t)(p.kc * 2);
+  const uint32_t b_tx = (uint32_t)p.block_n * (uint32_t)(p.kc * 2);       // the whole B tile (both halves of a pair)
 
   if (warp == 0) {
     // ===================== TMA producer (whole warp loops, one elected lane issues) =====================
     int stage = 0;
     uint32_t phase = 0;
-    for (int t = blockIdx.x; t < total; t += gridDim.x) {
+    for (int t = wstart; t < total; t += wstep) {
       const int nt = t % p.n_tiles;
-      const int mg = t / p.n_tiles;
+      const int mg = PAIR ? (t / p.n_tiles) * 2 + (int)cta_rank : t / p.n_tiles;
       int nvalid = m_tiles - mg * p.acc_m;
-      if (nvalid > p.acc_m) nvalid = p.acc_m;
+      if (nvalid > p.acc_m || PAIR) nvalid = p.acc_m;
       int w0[4], h0[4], n0[4];
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
@@ -162,7 +174,8 @@ conv_tc_kernel(const __grid_constant__ TcConvParams p) {
         h0[j] = (mt % p.tiles_h) * p.BH;
         n0[j] = (mt / p.tiles_h) * p.BN;
       }
-      const uint32_t tx = (uint32_t)nvalid * a_tx + b_tx;
+      // pair: only the leader arms its barrier, with the bytes of BOTH CTAs (the peer's loads complete on it too)
+      const uint32_t tx = PAIR ? 2u * (uint32_t)p.acc_m * a_tx + b_tx : (uint32_t)nvalid * a_tx + b_tx;
       for (int tap = 0; tap < p.taps; ++tap) {
         const CUtensorMap* am = &p.a_map[p.tap_map[tap]];
         const int dw = p.tap_dw[tap], dh = p.tap_dh[tap];
@@ -171,17 +184,21 @@ conv_tc_kernel(const __grid_constant__ TcConvParams p) {
           mbar_wait(&empty[stage], phase ^ 1);
           if (elect_one()) {
             uint8_t* sa = smem + (size_t)stage * stage_bytes;
-            mbar_expect_tx(&full[stage], tx);
+            if (!PAIR || leader) mbar_expect_tx(&full[stage], tx);
 #pragma unroll
             for (int j = 0; j < 4; ++j)
-              if (j < nvalid)
-                tma_load_4d(sa + (size_t)j * p.a_bytes, am, &full[stage], kk * p.kc, w0[j] + dw, h0[j] + dh, n0[j]);
+              if (j < nvalid) {
+                if (PAIR) tma_load_4d_pair(sa + (size_t)j * p.a_bytes, am, &full[stage], kk * p.kc, w0[j] + dw, h0[j] + dh, n0[j]);
+                else      tma_load_4d(sa + (size_t)j * p.a_bytes, am, &full[stage], kk * p.kc, w0[j] + dw, h0[j] + dh, n0[j]);
+              }
             uint8_t* sb = sa + (size_t)p.acc_m * p.a_bytes;
             if (p.b_mn) {
               // one op: (gw couts, kc cin rows, b_boxes cout blocks) lands as b_boxes consecutive MN-major boxes
-              tma_load_4d(sb, &p.b_map, &full[stage], 0, kk * p.kc, nt * p.b_boxes, tb);
+              if (PAIR) tma_load_4d_pair(sb, &p.b_map, &full[stage], 0, kk * p.kc, (2 * nt + (int)cta_rank) * p.b_boxes, tb);
+              else      tma_load_4d(sb, &p.b_map, &full[stage], 0, kk * p.kc, nt * p.b_boxes, tb);
             } else {
-              tma_load_3d(sb, &p.b_map, &full[stage], kk * p.kc, nt * p.block_n, tb);
+              if (PAIR) tma_load_3d_pair(sb, &p.b_map, &full[stage], kk * p.kc, nt * p.block_n + (int)cta_rank * (p.block_n / 2), tb);
+              else      tma_load_3d(sb, &p.b_map, &full[stage], kk * p.kc, nt * p.block_n, tb);
             }
           }
           __syncwarp();
@@ -190,15 +207,17 @@ conv_tc_kernel(const __grid_constant__ TcConvParams p) {
       }
     }
   } else if (warp == 1) {
-    // ===================== MMA issuer (whole warp loops, one elected lane issues) =====================
-    const uint32_t idesc = make_idesc_bf16(TC_BLOCK_M, p.block_n, 0, p.b_mn);
+    // ===================== MMA issuer (whole warp loops, one elected lane issues; pair: the leader CTA only) ==========
+    if (!PAIR || leader) {
+    const uint32_t idesc = make_idesc_bf16(PAIR ? 2 * TC_BLOCK_M : TC_BLOCK_M, p.block_n, 0, p.b_mn);
     const uint32_t rowB = (uint32_t)p.gw * 2, ltB = swizzle_layout_type(p.gw * 2);
     const int row_bytes = p.kc * 2;
     const uint32_t lt = swizzle_layout_type(row_bytes);
     const uint32_t sbo = 8u * row_bytes;
     const int ksteps = p.kc / 16;
     // Descriptors differ only in their 14-bit start-address field (bytes >> 4); every address lies inside this
-    // CTA's shared-memory window (< 256 KB), so stepping is a plain add on the low word.
+    // CTA's shared-memory window (< 256 KB), so stepping is a plain add on the low word.  (Pair: the same offsets
+    // address the peer's shared memory — both CTAs use one layout.)
     const uint64_t da0 = make_smem_desc(base_u32, 16, sbo, lt);
     // K-major B: +32 bytes per K step inside the swizzled row.  MN-major B (rows = input channels):
     // +16 rows per K step, LBO = next 64-column box, SBO = 8 rows.
@@ -210,10 +229,10 @@ conv_tc_kernel(const __grid_constant__ TcConvParams p) {
     uint32_t phase = 0;
     int acc = 0;
     uint32_t acc_phase = 0;
-    for (int t = blockIdx.x; t < total; t += gridDim.x) {
+    for (int t = wstart; t < total; t += wstep) {
       const int mg = t / p.n_tiles;
       int nvalid = m_tiles - mg * p.acc_m;
-      if (nvalid > p.acc_m) nvalid = p.acc_m;
+      if (nvalid > p.acc_m || PAIR) nvalid = p.acc_m;
       mbar_wait(&tempty[acc], acc_phase ^ 1);
       tc_fence_after();
       const uint32_t d_tmem = tmem_base + (uint32_t)(acc * p.acc_m * p.block_n);
@@ -227,16 +246,22 @@ conv_tc_kernel(const __grid_constant__ TcConvParams p) {
             const uint64_t da_j = da_s + (uint64_t)((uint32_t)j * a16);
             const uint32_t d = d_tmem + (uint32_t)(j * p.block_n);
 #pragma unroll 4
-            for (int k = 0; k < ksteps; ++k)
-              umma_bf16(d, da_j + (uint64_t)(k * a_step), db_s + (uint64_t)(k * b_step), idesc, (it > 0 || k > 0) ? 1u : 0u);
+            for (int k = 0; k < ksteps; ++k) {
+              if (PAIR) umma_bf16_pair(d, da_j + (uint64_t)(k * a_step), db_s + (uint64_t)(k * b_step), idesc, (it > 0 || k > 0) ? 1u : 0u);
+              else      umma_bf16(d, da_j + (uint64_t)(k * a_step), db_s + (uint64_t)(k * b_step), idesc, (it > 0 || k > 0) ? 1u : 0u);
+            }
           }
-          umma_commit(&empty[stage]);      // frees the smem slot once these MMAs have read it
-          if (it == k_iters - 1) umma_commit(&tfull[acc]);   // accumulators complete
+          // frees the smem slot (in both CTAs of a pair) once these MMAs have read it
+          if (PAIR) umma_commit_pair(&empty[stage]); else umma_commit(&empty[stage]);
+          if (it == k_iters - 1) {                                       // accumulators complete
+            if (PAIR) umma_commit_pair(&tfull[acc]); else umma_commit(&tfull[acc]);
+          }
         }
         __syncwarp();
         if (++stage == p.stages) { stage = 0; phase ^= 1; }
       }
       if (++acc == p.tstages) { acc = 0; acc_phase ^= 1; }
+    }
     }
   } else if (warp < 2 + TC_EPI_WARPS) {
     // ===================== epilogue (warps 2..9) =====================
@@ -266,11 +291,12 @@ conv_tc_kernel(const __grid_constant__ TcConvParams p) {
       for (int q = 0; q < TC_EPI_WARPS; ++q) v += c[(q * 32 + (col >> 1)) * 4 + st * 2 + (col & 1)];
       pacc[(col0 + col) * 2 + st] += v;
     };
-    for (int t = blockIdx.x; t < total; t += gridDim.x) {
+    const uint32_t tempty_leader[2] = {PAIR ? mapa_u32(&tempty[0], 0) : 0u, PAIR ? mapa_u32(&tempty[1], 0) : 0u};
+    for (int t = wstart; t < total; t += wstep) {
       const int nt = t % p.n_tiles;
-      const int mg = t / p.n_tiles;
+      const int mg = PAIR ? (t / p.n_tiles) * 2 + (int)cta_rank : t / p.n_tiles;
       int nvalid = m_tiles - mg * p.acc_m;
-      if (nvalid > p.acc_m) nvalid = p.acc_m;
+      if (nvalid > p.acc_m || PAIR) nvalid = p.acc_m;
       mbar_wait(&tfull[acc], acc_phase);
       tc_fence_after();
       for (int j = 0; j < nvalid; ++j) {
@@ -435,7 +461,10 @@ conv_tc_kernel(const __grid_constant__ TcConvParams p) {
       // all TMEM reads of this accumulator set are complete (tcgen05.wait::ld above)
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&tempty[acc]);
+      if (lane == 0) {
+        if (PAIR) mbar_arrive_cluster(tempty_leader[acc]);     // the leader's MMA warp waits for both CTAs' epilogues
+        else mbar_arrive(&tempty[acc]);
+      }
       if (++acc == p.tstages) { acc = 0; acc_phase ^= 1; }
     }
     if (fuse_stats) {
@@ -457,11 +486,11 @@ conv_tc_kernel(const __grid_constant__ TcConvParams p) {
     const int groups = p.block_n / 64;
     int rslot = 0;
     uint32_t rphase = 0;
-    for (int t = blockIdx.x; t < total; t += gridDim.x) {
+    for (int t = wstart; t < total; t += wstep) {
       const int nt = t % p.n_tiles;
-      const int mg = t / p.n_tiles;
+      const int mg = PAIR ? (t / p.n_tiles) * 2 + (int)cta_rank : t / p.n_tiles;
       int nvalid = m_tiles - mg * p.acc_m;
-      if (nvalid > p.acc_m) nvalid = p.acc_m;
+      if (nvalid > p.acc_m || PAIR) nvalid = p.acc_m;
       for (int j = 0; j < nvalid; ++j) {
         int mt = mg * p.acc_m + j;
         const int w0 = (mt % p.tiles_w) * p.BW;
@@ -481,8 +510,12 @@ conv_tc_kernel(const __grid_constant__ TcConvParams p) {
     }
   }
   tc_fence_before();
-  __syncthreads();
-  if (warp == 1) tmem_dealloc(tmem_base, p.tmem_cols);
+  if (PAIR) cluster_sync_all();      // neither CTA may leave while the pair's MMAs / remote arrivals can still touch it
+  else __syncthreads();
+  if (warp == 1) {
+    if (PAIR) tmem_dealloc_pair(tmem_base, p.tmem_cols);
+    else tmem_dealloc(tmem_base, p.tmem_cols);
+  }
 }
 
 // ------------------------------------------------------------------------------------------
@@ -796,9 +829,47 @@ __global__ void weights_to_bf16_batched_kernel(const RelayoutJob* __restrict__ j
 // host side: tensor maps and plans
 // ------------------------------------------------------------------------------------------
 static cudaError_t set_conv_tc_smem_attr() {
-  cudaError_t e = cudaFuncSetAttribute(conv_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024));
+  cudaError_t e = cudaFuncSetAttribute(conv_tc_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024));
   if (e != cudaSuccess) return e;
-  return cudaFuncSetAttribute(conv_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024));
+  e = cudaFuncSetAttribute(conv_tc_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024));
+  if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(conv_tc_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024));
+  if (e != cudaSuccess) return e;
+  return cudaFuncSetAttribute(conv_tc_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024));
+}
+
+// Launch with the programmatic-serialization attribute and, for CTA pairs, a cluster dimension of two.
+template <typename... KArgs, typename... Args>
+static void launch_conv(void (*kernel)(KArgs...), int grid, int block, size_t smem, cudaStream_t st, bool pair, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(block);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[2];
+  int n = 0;
+  if (pdl_enabled()) {
+    attr[n].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[n].val.programmaticStreamSerializationAllowed = 1;
+    ++n;
+  }
+  if (pair) {
+    attr[n].id = cudaLaunchAttributeClusterDimension;
+    attr[n].val.clusterDim.x = 2;
+    attr[n].val.clusterDim.y = 1;
+    attr[n].val.clusterDim.z = 1;
+    ++n;
+  }
+  cfg.attrs = attr;
+  cfg.numAttrs = n;
+  cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);      // errors surface through check_launch()
+}
+
+// CTA pairs (tcgen05 .cta_group::2): RN_TC_PAIR=0 turns them off, =1 uses them wherever the tile allows (default:
+// where the weight tile is the larger share of the operand traffic, see create_sub)
+static int pair_mode() {
+  const char* e = getenv("RN_TC_PAIR");          // read on every plan creation: tests toggle it in-process
+  return e ? atoi(e) : -1;
 }
 
 typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
@@ -1108,7 +1179,19 @@ static int create_sub(const rn_conv_desc* d, int kind, const void* a, const void
   const int row_bytes = p.kc * 2;
   const uint32_t box_rows = (uint32_t)(p.BW * p.BH * p.BN);
   p.a_bytes = ((uint32_t)TC_BLOCK_M * row_bytes + 1023u) & ~1023u;
-  p.b_bytes = ((uint32_t)p.block_n * row_bytes + 1023u) & ~1023u;
+  // CTA pair: one tcgen05.mma.cta_group::2 stream over two neighbouring pixel-tile groups; each CTA stages half of
+  // the B tile.  Needs two whole 64-column halves (MN-major boxes) / 8-row groups (K-major) and full swizzle atoms.
+  {
+    const int mode = pair_mode();
+    const bool can = p.block_n % 128 == 0 && p.kc == 64 && p.gw == 64;
+    // Measured per layer on B200 (ResNet-50 / 224, profiles/r02_pair_ab.txt): pairs win 4-33 % where the GEMM is
+    // operand-traffic bound — N = 256 tiles with a long reduction (3x3 over >= 256 channels, 1x1 over >= 1024) —
+    // and lose 10-50 % on the HBM-bound large-image layers (short reductions, one or two k-chunks per tile), where
+    // running two CTAs in lock step only removes slack.  Default: N = 256 and taps * channels >= 1024.
+    p.pair = can && (mode == 1 || (mode != 0 && p.block_n >= 256 && (long)ntaps * cred >= 1024)) ? 1 : 0;
+  }
+  const int b_rows = p.pair ? p.block_n / 2 : p.block_n;           // B rows (columns of the output) staged per CTA
+  p.b_bytes = ((uint32_t)b_rows * row_bytes + 1023u) & ~1023u;
   p.tx_bytes = box_rows * row_bytes + (uint32_t)p.block_n * row_bytes;
   // pixel tiles per CTA iteration: every extra tile re-uses the B tile (less L2 -> SM traffic per FLOP,
   // which is what bounds these kernels), limited by the 512 TMEM columns, by shared memory (>= 3 stages)
@@ -1154,6 +1237,7 @@ static int create_sub(const rn_conv_desc* d, int kind, const void* a, const void
       // double-buffered (2 * cand * BLOCK_N <= 512) and every SM keeps at least one work item
       if (!forced && (2 * cand * p.block_n > 512 || cand > 2)) continue;
       if (!forced && ((m_tiles + cand - 1) / cand) * p.n_tiles < RN_NUM_SMS) continue;
+      if (p.pair && cand > 1) continue;          // pairs already double the pixels per B tile
       acc_m = cand;
       break;
     }
@@ -1177,7 +1261,7 @@ static int create_sub(const rn_conv_desc* d, int kind, const void* a, const void
   if (kind == 0) {
     // fprop: bf16 HWIO [tap][Cin][Cout] read as an MN-major B operand: dims (Cout, Cin, taps)
     p.b_mn = 1;
-    p.b_boxes = p.block_n / p.gw;
+    p.b_boxes = b_rows / p.gw;
     p.b_box_bytes = (uint32_t)p.kc * p.gw * 2;
     // dims (gw couts inside a block, cin, cout block, tap): one TMA op fetches all cout blocks of the tile
     const uint64_t dims[4] = {(uint64_t)p.gw, (uint64_t)cred, (uint64_t)(ncols / p.gw), (uint64_t)b_taps};
@@ -1189,7 +1273,7 @@ static int create_sub(const rn_conv_desc* d, int kind, const void* a, const void
     // dgrad: the same bf16 HWIO tensor is K-major for this GEMM (K = Cout contiguous): dims (cred, ncols, taps)
     const uint64_t dims[3] = {(uint64_t)cred, (uint64_t)ncols, (uint64_t)b_taps};
     const uint64_t str[2] = {(uint64_t)cred * 2, (uint64_t)ncols * cred * 2};
-    const uint32_t box[3] = {(uint32_t)p.kc, (uint32_t)p.block_n, 1u};
+    const uint32_t box[3] = {(uint32_t)p.kc, (uint32_t)b_rows, 1u};
     rc = encode_map(&p.b_map, b, 3, dims, str, box, row_bytes, "weights");
     if (rc) return rc;
   }
@@ -1203,8 +1287,14 @@ static int create_sub(const rn_conv_desc* d, int kind, const void* a, const void
       if (rc) return rc;
     }
   }
-  const long total = ((m_tiles + acc_m - 1) / acc_m) * p.n_tiles;
-  *grid = (int)(total < RN_NUM_SMS ? total : RN_NUM_SMS);
+  const long groups = (m_tiles + acc_m - 1) / acc_m;
+  if (p.pair) {
+    const long total = ((groups + 1) / 2) * p.n_tiles;                 // work items of a pair
+    *grid = 2 * (int)(total < RN_NUM_SMS / 2 ? total : RN_NUM_SMS / 2);
+  } else {
+    const long total = groups * p.n_tiles;
+    *grid = (int)(total < RN_NUM_SMS ? total : RN_NUM_SMS);
+  }
   return RN_OK;
 }
 
@@ -1419,14 +1509,30 @@ extern "C" int rn_convtc_run(rn_convtc_plan* plan, float beta, void* stream) {
   for (int i = 0; i < plan->nsub; ++i) {
     TcConvParams p = plan->p[i];
     p.accumulate = beta != 0.f ? 1 : 0;
-    if (p.fuse_add || p.fuse_stats || p.fuse_bnbwd)
-      launch_pdl(conv_tc_kernel<true>, plan->grid[i], (p.fuse_add || p.fuse_bnbwd) ? TC_THREADS_RES : TC_CONV_THREADS,
-                 plan->smem_sub[i], st, p);
-    else
-      launch_pdl(conv_tc_kernel<false>, plan->grid[i], TC_CONV_THREADS, plan->smem_sub[i], st, p);
+    const bool fused = p.fuse_add || p.fuse_stats || p.fuse_bnbwd;
+    const int threads = (p.fuse_add || p.fuse_bnbwd) ? TC_THREADS_RES : TC_CONV_THREADS;
+    if (fused && p.pair)       launch_conv(conv_tc_kernel<true, true>, plan->grid[i], threads, plan->smem_sub[i], st, true, p);
+    else if (fused)            launch_conv(conv_tc_kernel<true, false>, plan->grid[i], threads, plan->smem_sub[i], st, false, p);
+    else if (p.pair)           launch_conv(conv_tc_kernel<false, true>, plan->grid[i], threads, plan->smem_sub[i], st, true, p);
+    else                       launch_conv(conv_tc_kernel<false, false>, plan->grid[i], threads, plan->smem_sub[i], st, false, p);
     int rc = check_launch("conv_tc_kernel");
     if (rc) return rc;
   }
+  return RN_OK;
+}
+
+extern "C" int rn_convtc_plan_describe(const rn_convtc_plan* plan, char* buf, size_t n) {
+  RN_REQUIRE(plan && buf && n > 0, "convtc_plan_describe: bad arguments");
+  if (plan->kind == 2) {
+    const TcWgradParams& w = plan->w;
+    snprintf(buf, n, "wgrad block_n=%d acc=%d kp=%d stages=%d splits=%d grid=%d cluster=%d", w.block_n, w.acc, w.kp, w.stages,
+             w.splits, plan->wgrid, 1);
+    return RN_OK;
+  }
+  const TcConvParams& p = plan->p[0];
+  snprintf(buf, n, "%s subs=%d block_n=%d acc_m=%d box=%dx%dx%d kc=%d taps=%d stages=%d tstages=%d pair=%d grid=%d fused=%d%d%d halo=%d",
+           plan->kind == 0 ? "fprop" : "dgrad", plan->nsub, p.block_n, p.acc_m, p.BW, p.BH, p.BN, p.kc, p.taps, p.stages,
+           p.tstages, p.pair, plan->grid[0], p.fuse_add, p.fuse_stats, p.fuse_bnbwd, 0);
   return RN_OK;
 }
 

@@ -402,7 +402,9 @@ class Executor:
         check(lib.rn_stem_s2d_plan_create(C.byref(d), kind, ptr(u), ptr(b), ptr(out), ptr(scratch), nbytes,
                                           C.byref(plan)), "rn_stem_s2d_plan_create")
         self._plans.append(plan)
-        return lambda s, p=plan: check(lib.rn_convtc_run(p, 0.0, s), "rn_convtc_run")
+        fn = lambda s, p=plan: check(lib.rn_convtc_run(p, 0.0, s), "rn_convtc_run")   # noqa: E731
+        fn.plan = plan
+        return fn
 
     def _stem_setup(self, n):
         if hasattr(n, "_stem"):
@@ -434,7 +436,9 @@ class Executor:
         check(lib.rn_convtc_plan_create(C.byref(d), kind, ptr(a_buf), ptr(b_buf), outp, ptr(scratch), nbytes,
                                         C.byref(plan)), "rn_convtc_plan_create")
         self._plans.append(plan)
-        return lambda s, p=plan, beta=0.0: check(lib.rn_convtc_run(p, beta, s), "rn_convtc_run")
+        fn = lambda s, p=plan, beta=0.0: check(lib.rn_convtc_run(p, beta, s), "rn_convtc_run")   # noqa: E731
+        fn.plan = plan
+        return fn
 
     def _conv_fprop(self, n):
         x, y = n.inputs[0], n.outputs[0]
@@ -469,7 +473,9 @@ class Executor:
             self._plans.append(plan)
             if f["residual"] is not None:
                 y.buf = None            # conv + shortcut goes straight into the sum: the conv output is never materialised
-            return ("conv_fprop_tc:" + y.name, lambda s, p=plan: check(lib.rn_convtc_run(p, 0.0, s), "rn_convtc_run"))
+            fn = lambda s, p=plan: check(lib.rn_convtc_run(p, 0.0, s), "rn_convtc_run")   # noqa: E731
+            fn.plan = plan
+            return ("conv_fprop_tc:" + y.name, fn)
         if self._conv_impl(n, 0) == "tc":
             return ("conv_fprop_tc:" + y.name, self._tc_plan(n, d, 0, x.buf, y.buf))
         w = self._wptr(kv, "Wb" if self.bf16 else "W")
@@ -493,7 +499,9 @@ class Executor:
         check(lib.rn_convtc_plan_create(C.byref(d), kind, ptr(a_buf), b, outp, ptr(scratch), nbytes,
                                         C.byref(plan)), "rn_convtc_plan_create")
         self._plans.append(plan)
-        return lambda s, p=plan, beta=0.0: check(lib.rn_convtc_run(p, beta, s), "rn_convtc_run")
+        fn = lambda s, p=plan, beta=0.0: check(lib.rn_convtc_run(p, beta, s), "rn_convtc_run")   # noqa: E731
+        fn.plan = plan
+        return fn
 
     def _bn_fwd(self, n):
         x, y = n.inputs[0], n.outputs[0]
@@ -719,13 +727,14 @@ class Executor:
                         bn.attrs["leak"], ptr(part), C.byref(nrows), C.byref(plan)), "rn_convtc_plan_create_fused_dgrad")
                     self._plans.append(plan)
                     bn.bwd_from = dict(partials=part, nrows=nrows.value)
-                    self._emit(bwd, "conv_dgrad_tc:" + y.name,
-                               lambda s, p=plan: check(lib.rn_convtc_run(p, 0.0, s), "rn_convtc_run"),
-                               node=n, dy=dy, dx=dxb, beta=0.0)
+                    fn = lambda s, p=plan: check(lib.rn_convtc_run(p, 0.0, s), "rn_convtc_run")   # noqa: E731
+                    fn.plan = plan
+                    self._emit(bwd, "conv_dgrad_tc:" + y.name, fn, node=n, dy=dy, dx=dxb, beta=0.0)
                 elif self._conv_impl(n, 1) == "tc":
                     run = self._tc_plan(n, d, 1, dy, dxb)
-                    self._emit(bwd, "conv_dgrad_tc:" + y.name, lambda s, run=run, beta=beta: run(s, beta=beta),
-                               node=n, dy=dy, dx=dxb, beta=beta)
+                    fn = lambda s, run=run, beta=beta: run(s, beta=beta)   # noqa: E731
+                    fn.plan = run.plan
+                    self._emit(bwd, "conv_dgrad_tc:" + y.name, fn, node=n, dy=dy, dx=dxb, beta=beta)
                 else:
                     w = self._wptr(kv, "Wb" if self.bf16 else "W")
                     self._emit(bwd, "conv_dgrad:" + y.name, lambda s, d=d, pdy=ptr(dy), w=w, pdx=ptr(dxb), beta=beta:
@@ -1010,6 +1019,15 @@ class Executor:
         xs = self.loss[1].buf.tolist()
         cost = xs[0] + self.wd * 0.5 * float(self.sumsq.item()) if self.train else xs[0]
         return xs[0], xs[1], cost
+
+    def describe_plans(self):
+        """launch name -> one-line description of its tensor-core plan (tile, pipeline depth, CTA pair, fusions)."""
+        out = OrderedDict()
+        for name, fn in self.fwd + (self.bwd if self.train else []):
+            plan = getattr(fn, "plan", None)
+            if plan is not None:
+                out[name] = _lib.describe_plan(plan)
+        return out
 
     def close(self):
         for p in self._plans:

@@ -114,6 +114,8 @@ int rn_convtc_plan_create_fused_dgrad(const rn_conv_desc* d, const void* dy, con
                                       rn_convtc_plan** plan);
 int rn_convtc_run(rn_convtc_plan* plan, float beta, void* stream);
 int rn_convtc_plan_destroy(rn_convtc_plan* plan);
+/* One line of text describing how a plan will run (tile shape, pipeline depth, CTA pairs, fusions): for logs and tests. */
+int rn_convtc_plan_describe(const rn_convtc_plan* plan, char* buf, size_t n);
 /* Re-layout of the fp32 HWIO master weights into the two bf16 operand layouts above
  * ([k*k][Cout][Cin] for fprop, [k*k][Cin][Cout] for dgrad). Either output may be NULL. */
 int rn_weights_to_bf16(const float* w_hwio, int k, int Cin, int Cout, void* w_fprop, void* w_dgrad, void* stream);

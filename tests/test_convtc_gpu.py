@@ -76,6 +76,46 @@ def test_convtc_fprop_and_dgrad(case):
         assert rel_err(out.float(), want) < 2e-2, ("kind", kind)
 
 
+PAIR_CASES = [CASES[1], CASES[4], CASES[5], CASES[11], (8, 14, 14, 1024, 256, 1, 1, 0), (5, 14, 14, 256, 512, 3, 1, 1)]
+
+
+@pytest.mark.parametrize("mode", ["1", "0"])
+@pytest.mark.parametrize("case", PAIR_CASES)
+def test_convtc_cta_pairs(case, mode, monkeypatch):
+    """tcgen05.mma.cta_group::2: clusters of two CTAs, M = 256 per instruction, each CTA stages half of the weight
+    tile.  RN_TC_PAIR=1 forces pairs wherever the tile allows, =0 forbids them; both must match the oracle, including
+    an odd number of pixel-tile groups (the last pair's second CTA works on an out-of-range tile) and N = 512
+    (two column tiles per pair)."""
+    from distributed_tensorflow_resnet_b200._lib import describe_plan
+    monkeypatch.setenv("RN_TC_PAIR", mode)
+    N, H, W, Cin, Cout, k, s, pad = case
+    g = torch.Generator().manual_seed(sum(case) + 7)
+    x = torch.randn(N, H, W, Cin, generator=g).to(BF)
+    w = (torch.randn(k, k, Cin, Cout, generator=g) / (k * k * Cin) ** 0.5).to(BF)
+    dy = torch.randn(N, H, W, Cout, generator=g).to(BF)
+    net = ro.Net(dtype=torch.float64, params={"w": w.double().numpy()})
+    xv = ro.Var(x.double())
+    yv = net.conv2d(xv, "w", k, Cin, Cout, s, pad, (H, W), None, "y")
+    yv.grad = dy.double()
+    net.backward()
+    d = ConvDesc(N, H, W, Cin, H, W, Cout, k, s, pad, RN_BF16)
+    _, wd = _weights(w)
+    X, DY = dev(x), dev(dy)
+    Y = torch.full((N, H, W, Cout), float("nan"), dtype=BF, device="cuda")
+    DX = torch.full((N, H, W, Cin), float("nan"), dtype=BF, device="cuda")
+    for kind, a, out, want in ((0, X, Y, yv.val), (1, DY, DX, xv.grad)):
+        plan = C.c_void_p()
+        check(lib.rn_convtc_plan_create(C.byref(d), kind, ptr(a), ptr(wd), ptr(out), None, 0, C.byref(plan)), "plan")
+        ncols = Cout if kind == 0 else Cin
+        assert ("pair=1" in describe_plan(plan)) == (mode == "1" and ncols % 128 == 0), describe_plan(plan)
+        for _ in range(2):
+            check(lib.rn_convtc_run(plan, 0.0, stream()), "run")
+        torch.cuda.synchronize()
+        lib.rn_convtc_plan_destroy(plan)
+        assert torch.isfinite(out.float()).all()
+        assert rel_err(out.float(), want) < 2e-2, ("kind", kind)
+
+
 S2_CASES = [
     # N, H, W, Cin, Cout, k, stride, pad, (Ho, Wo)
     (4, 16, 16, 64, 128, 3, 2, 1, (8, 8)),       # official 3x3 s2: symmetric fixed_padding + VALID
