@@ -121,6 +121,7 @@ SIGNATURES = {
     "rn_sgd_momentum_fused": (C.c_int, [vp, vp, vp, vp, i64, vp, vp, f32, f32, f32, i32, vp, vp, sz, vp]),
     "rn_l2_sumsq": (C.c_int, [vp, i64, vp, vp, vp, sz, vp]),
     "rn_cifar_decode": (C.c_int, [vp, i64, i32, i32, i32, vp, i32, i32, i32, u32, u32, u32, vp, i32, vp, i32, vp, vp, vp, vp]),
+    "rn_vgg_preprocess": (C.c_int, [vp, vp, vp, i32, i32, i32, i32, i32, i32, u32, u32, u32, vp, vp, vp, i32, vp, vp, vp, i32, vp, vp]),
     "rn_cast": (C.c_int, [vp, vp, i64, i32, i32, vp]),
     "rn_add_inplace": (C.c_int, [vp, vp, i64, i32, vp]),
     "rn_add": (C.c_int, [vp, vp, vp, i64, i32, vp]),

@@ -1,7 +1,8 @@
 """ImageNet-shape trainer with the flags / loop / LR schedule of the reference's
 resnet_imagenet_train.py (flags :33-99, train() :206-281, main() :283-338).  There is no dataset
 or network here, so the TFRecord + JPEG + vgg_preprocessing input (:105-187) is replaced by
-synthetic standard-normal 224x224x3 images resident on the device.
+synthetic decoded uint8 images of random sizes run through the GPU restatement of vgg_preprocessing
+(`--train_data_path synthetic[:N]`, the default), or by one fixed standard-normal batch (`--train_data_path fixed`).
 
     torchrun --nproc-per-node 8 -m distributed_tensorflow_resnet_b200.resnet_imagenet_train \
         --batch_size 128 --train_steps 100
@@ -48,7 +49,14 @@ def train(hps, out=sys.stdout, log_every=40):
     rank, world = _cifar.init_distributed()
     dev = torch.device("cuda", torch.cuda.current_device())
     dt = torch.bfloat16 if FLAGS.compute_dtype == "bf16" else torch.float32
-    images, labels = synthetic_batch(FLAGS.batch_size, FLAGS.image_size, hps.num_classes, rank, dt, dev)
+    if str(FLAGS.train_data_path).startswith("synthetic"):
+        # the reference's input_fn (:150-187): decoded images of arbitrary sizes -> vgg_preprocessing on the GPU
+        from . import vgg_preprocessing
+        images, labels = vgg_preprocessing.input_fn(True, FLAGS.train_data_path, FLAGS.batch_size, FLAGS.num_epochs,
+                                                    image_size=FLAGS.image_size, num_classes=hps.num_classes,
+                                                    seed=FLAGS.seed, dtype=dt)
+    else:       # 'fixed': one standard-normal batch resident on the device (kernel benchmarking)
+        images, labels = synthetic_batch(FLAGS.batch_size, FLAGS.image_size, hps.num_classes, rank, dt, dev)
     model = resnet_model.ResNet(hps, images, labels, FLAGS.mode)
     model.build_graph()
     # _LearningRateSetterHook.begin sets 0.4 for the first run (reference :241); hooks as the CIFAR trainer

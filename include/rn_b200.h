@@ -295,6 +295,30 @@ int rn_cifar_decode(const uint8_t* records, int64_t n_records, int32_t record_by
                     int32_t* draws_out, void* stream);
 
 /* ------------------------------------------------------------------------------------------
+ * ImageNet input preprocessing (decoded uint8 images of arbitrary sizes -> network input)
+ *   replaces vgg_preprocessing.preprocess_image (vgg_preprocessing.py:284-353) as called from
+ *   record_parser (resnet_imagenet_train.py:137-147): image/255; aspect-preserving bilinear resize
+ *   (align_corners=False) to a smallest side drawn from [side_min, side_max] (train; the reference uses
+ *   256..512) or to side_min (eval; 256); random / central crop out_h x out_w; random left-right flip
+ *   (train); subtraction of the per-channel means 123.68/255, 116.78/255, 103.94/255.
+ *   images: the B decoded HWC uint8 images packed back to back; offsets[b] = byte offset of image b;
+ *   hw[b] = (height, width).  Random draws: Philox4x32-10, key (seed_lo, seed_hi), counter
+ *   (index[b] or b, epoch, 1, 0): word 0 -> side = side_min + u % (side_max - side_min + 1),
+ *   words 1, 2 -> crop offsets u % (resized size - crop + 1), word 3 -> flip iff the 23-bit uniform < 0.5.
+ *   draws_in (nullable) int32 [B][4] = (side, offset_y, offset_x, flip) overrides them; draws_out (nullable)
+ *   receives the values used.  error_flag (nullable device int, caller zeroes it): set to b + 1 if image b
+ *   is smaller than the crop after resizing (the reference's "Crop size greater than the image size.").
+ *   Output NHWC [B][out_h][out_w][3], RN_F32 or RN_BF16; if out_onehot != NULL also the dense one-hot
+ *   float [B][classes] of labels[b] (tf.one_hot, resnet_imagenet_train.py:144-147).  JPEG decoding is not
+ *   part of this library.
+ * ------------------------------------------------------------------------------------------ */
+int rn_vgg_preprocess(const uint8_t* images, const int64_t* offsets, const int32_t* hw, int32_t B, int32_t out_h,
+                      int32_t out_w, int32_t side_min, int32_t side_max, int32_t train, uint32_t seed_lo,
+                      uint32_t seed_hi, uint32_t epoch, const int32_t* index, const int32_t* draws_in, void* out,
+                      int32_t out_dtype, int32_t* draws_out, int32_t* error_flag, const int32_t* labels,
+                      int32_t classes, float* out_onehot, void* stream);
+
+/* ------------------------------------------------------------------------------------------
  * Small utilities used by the host graph executor (no reference counterpart beyond tf.cast /
  * AddN / tf.pad at the call sites above).
  * ------------------------------------------------------------------------------------------ */

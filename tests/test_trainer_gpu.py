@@ -105,3 +105,23 @@ def test_eval_loop_on_the_reference_trained_weights(tmp_path):
     assert abs(res["precision"] - want) < 1e-9 and res["best_precision"] == res["precision"]
     tags = {t for _, t, _ in read_event_scalars(str(eval_dir))}
     assert {"Precision", "Best Precision"} <= tags
+
+
+def test_imagenet_trainer_runs_on_the_preprocessing_pipeline(tmp_path):
+    """resnet_imagenet_train.main on the synthetic ImageNet input (uint8 images of random sizes -> rn_vgg_preprocess):
+    warm-up learning rates of the reference's hook (:236-260), loss finite, checkpoint + resume."""
+    import io
+    from distributed_tensorflow_resnet_b200 import resnet_imagenet_train as it
+    FLAGS.reset()
+    args = ["--train_data_path", "synthetic:16", "--batch_size", "4", "--resnet_size", "18", "--train_steps", "6",
+            "--train_dir", str(tmp_path), "--compute_dtype", "bf16", "--seed", "2"]
+    m = it.main(args)
+    torch.cuda.synchronize()
+    assert m.global_step == 6 and np.isfinite(m.cost)
+    assert abs(m.lrn_rate - it.imagenet_learning_rate(5)) < 1e-12           # rate for step 6 was set from step 5
+    pipe = m._images._rn_pipeline
+    assert pipe.draws.cpu().numpy()[:, 0].min() >= 256
+    w = m.executor.W.clone()
+    FLAGS.reset()
+    m2 = it.main(args)                                                     # finished directory: restore only
+    assert m2.global_step == 6 and torch.equal(m2.executor.W, w)
