@@ -69,6 +69,15 @@ struct TcConvParams {
   float* stat_partials;
   CUtensorMap r_map;
   int8_t tap_map[TC_MAX_TAPS], tap_dw[TC_MAX_TAPS], tap_dh[TC_MAX_TAPS], tap_b[TC_MAX_TAPS];
+  // Halo mode (3x3, stride 1): a pipeline stage is one HORIZONTAL tap (and k-chunk).  Its A box carries BH + 2 image
+  // rows, loaded once, and the three vertical taps read it at row offsets 0, BW, 2*BW through the matrix descriptor
+  // (start address + the descriptor's base-offset field when the offset is not a whole 1024-byte swizzle atom);
+  // the stage also holds the three weight tiles.  A traffic per output tile drops from 9 to 3 * (BH + 2) / BH boxes.
+  int halo;                       // 0 / 1
+  int8_t halo_dw[3];              // per stage group: horizontal shift of the box
+  int8_t halo_dh0;                // vertical shift of the box origin (the topmost tap)
+  int8_t halo_row[3][3];          // [group][j]: first row of the box the j-th vertical tap of the group reads, in units of BW rows
+  int8_t halo_b[3][3];            // [group][j]: weight tap index
 };
 
 constexpr int TC_RES_SLOTS_MAX = 6;        // upper bound of TcConvParams::res_slots (tiles of 16 KB in flight)
@@ -77,7 +86,9 @@ constexpr int TC_THREADS_RES = TC_CONV_THREADS + 32;
 // FUSED = false compiles the plain epilogue only (fprop / dgrad without fusion keep their registers and schedule).
 // PAIR = true: the grid is made of 2-CTA clusters; the pair works on two neighbouring groups of pixel tiles with ONE
 // stream of tcgen05.mma.cta_group::2 instructions issued by the leader CTA (see rn_tc_common.cuh).
-template <bool FUSED, bool PAIR>
+// HALO = true: 3x3 halo mode (see TcConvParams::halo); compiled separately so that the per-tap issue loops of the
+// other layers stay as tight as they were.
+template <bool FUSED, bool PAIR, bool HALO>
 __global__ void __launch_bounds__(FUSED ? TC_THREADS_RES : TC_CONV_THREADS, 1)
 conv_tc_kernel(const __grid_constant__ TcConvParams p) {
   const uint32_t cta_rank = PAIR ? cluster_ctarank() : 0u;
@@ -89,7 +100,8 @@ conv_tc_kernel(const __grid_constant__ TcConvParams p) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base_u32 = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* smem = smem_raw + (base_u32 - smem_u32(smem_raw));
-  const uint32_t stage_bytes = (uint32_t)p.acc_m * p.a_bytes + p.b_bytes;
+  constexpr int b_per_stage = HALO ? 3 : 1;                                    // weight tiles per pipeline stage
+  const uint32_t stage_bytes = (uint32_t)p.acc_m * p.a_bytes + (uint32_t)b_per_stage * p.b_bytes;
   const int row_bytes_out = p.gw * 2;
   uint8_t* epi_buf = smem + (size_t)p.stages * stage_bytes;                  // 2 x 16 KB
   uint8_t* res_buf = epi_buf + 2 * 16384;                                     // res_slots x 16 KB (fused add / fused BN backward)
@@ -152,9 +164,10 @@ conv_tc_kernel(const __grid_constant__ TcConvParams p) {
   const int total = PAIR ? ((m_groups + 1) / 2) * p.n_tiles : m_groups * p.n_tiles;
   const int wstart = PAIR ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
   const int wstep = PAIR ? (int)(gridDim.x >> 1) : (int)gridDim.x;
-  const int k_iters = p.taps * p.k_chunks;
-  const uint32_t a_tx = (uint32_t)(p.BW * p.BH * p.BN) * (uint32_t)(p.kc * 2);
-  const uint32_t b_tx = (uint32_t)p.block_n * (uint32_t)(p.kc * 2);       // the whole B tile (both halves of a pair)
+  const int stage_groups = HALO ? 3 : p.taps;                             // A boxes per k-chunk: horizontal taps / taps
+  const int k_iters = stage_groups * p.k_chunks;
+  const uint32_t a_tx = (uint32_t)(p.BW * (HALO ? p.BH + 2 : p.BH) * p.BN) * (uint32_t)(p.kc * 2);
+  const uint32_t b_tx = (uint32_t)b_per_stage * (uint32_t)p.block_n * (uint32_t)(p.kc * 2);   // whole B tiles of a stage (both halves of a pair)
 
   if (warp == 0) {
     // ===================== TMA producer (whole warp loops, one elected lane issues) =====================
@@ -176,10 +189,9 @@ conv_tc_kernel(const __grid_constant__ TcConvParams p) {
       }
       // pair: only the leader arms its barrier, with the bytes of BOTH CTAs (the peer's loads complete on it too)
       const uint32_t tx = PAIR ? 2u * (uint32_t)p.acc_m * a_tx + b_tx : (uint32_t)nvalid * a_tx + b_tx;
-      for (int tap = 0; tap < p.taps; ++tap) {
-        const CUtensorMap* am = &p.a_map[p.tap_map[tap]];
-        const int dw = p.tap_dw[tap], dh = p.tap_dh[tap];
-        const int tb = p.tap_b[tap];
+      for (int tap = 0; tap < stage_groups; ++tap) {
+        const CUtensorMap* am = &p.a_map[HALO ? 0 : p.tap_map[tap]];
+        const int dw = HALO ? p.halo_dw[tap] : p.tap_dw[tap], dh = HALO ? p.halo_dh0 : p.tap_dh[tap];
         for (int kk = 0; kk < p.k_chunks; ++kk) {
           mbar_wait(&empty[stage], phase ^ 1);
           if (elect_one()) {
@@ -191,14 +203,17 @@ conv_tc_kernel(const __grid_constant__ TcConvParams p) {
                 if (PAIR) tma_load_4d_pair(sa + (size_t)j * p.a_bytes, am, &full[stage], kk * p.kc, w0[j] + dw, h0[j] + dh, n0[j]);
                 else      tma_load_4d(sa + (size_t)j * p.a_bytes, am, &full[stage], kk * p.kc, w0[j] + dw, h0[j] + dh, n0[j]);
               }
-            uint8_t* sb = sa + (size_t)p.acc_m * p.a_bytes;
-            if (p.b_mn) {
-              // one op: (gw couts, kc cin rows, b_boxes cout blocks) lands as b_boxes consecutive MN-major boxes
-              if (PAIR) tma_load_4d_pair(sb, &p.b_map, &full[stage], 0, kk * p.kc, (2 * nt + (int)cta_rank) * p.b_boxes, tb);
-              else      tma_load_4d(sb, &p.b_map, &full[stage], 0, kk * p.kc, nt * p.b_boxes, tb);
-            } else {
-              if (PAIR) tma_load_3d_pair(sb, &p.b_map, &full[stage], kk * p.kc, nt * p.block_n + (int)cta_rank * (p.block_n / 2), tb);
-              else      tma_load_3d(sb, &p.b_map, &full[stage], kk * p.kc, nt * p.block_n, tb);
+            for (int q = 0; q < b_per_stage; ++q) {
+              uint8_t* sb = sa + (size_t)p.acc_m * p.a_bytes + (size_t)q * p.b_bytes;
+              const int tb = HALO ? p.halo_b[tap][q] : p.tap_b[tap];
+              if (p.b_mn) {
+                // one op: (gw couts, kc cin rows, b_boxes cout blocks) lands as b_boxes consecutive MN-major boxes
+                if (PAIR) tma_load_4d_pair(sb, &p.b_map, &full[stage], 0, kk * p.kc, (2 * nt + (int)cta_rank) * p.b_boxes, tb);
+                else      tma_load_4d(sb, &p.b_map, &full[stage], 0, kk * p.kc, nt * p.b_boxes, tb);
+              } else {
+                if (PAIR) tma_load_3d_pair(sb, &p.b_map, &full[stage], kk * p.kc, nt * p.block_n + (int)cta_rank * (p.block_n / 2), tb);
+                else      tma_load_3d(sb, &p.b_map, &full[stage], kk * p.kc, nt * p.block_n, tb);
+              }
             }
           }
           __syncwarp();
@@ -242,13 +257,24 @@ conv_tc_kernel(const __grid_constant__ TcConvParams p) {
         if (elect_one()) {
           const uint64_t da_s = da0 + (uint64_t)((uint32_t)stage * stage16);
           const uint64_t db_s = db0 + (uint64_t)((uint32_t)stage * stage16);
-          for (int j = 0; j < nvalid; ++j) {
-            const uint64_t da_j = da_s + (uint64_t)((uint32_t)j * a16);
-            const uint32_t d = d_tmem + (uint32_t)(j * p.block_n);
+          const int grp = HALO ? it / p.k_chunks : 0;
+          for (int q = 0; q < b_per_stage; ++q) {
+            // halo mode: vertical tap q reads the A box from row halo_row * BW on: only the start-address field moves
+            // (16-byte units).  Measured on B200: the 128-byte swizzle is a function of the absolute shared-memory
+            // address bits, so a start that is not a whole 1024-byte atom needs NO base-offset (bits 49-51 stay 0;
+            // setting them to (row & 7) produced wrong results for every BW that is not a multiple of 8).
+            const uint32_t rows = HALO ? (uint32_t)p.halo_row[grp][q] * (uint32_t)p.BW : 0u;
+            const uint64_t a_off = (uint64_t)(rows * (uint32_t)row_bytes >> 4);
+            const uint64_t db_q = db_s + (uint64_t)((uint32_t)q * (p.b_bytes >> 4));
+            for (int j = 0; j < nvalid; ++j) {
+              const uint64_t da_j = da_s + (uint64_t)((uint32_t)j * a16) + a_off;
+              const uint32_t d = d_tmem + (uint32_t)(j * p.block_n);
 #pragma unroll 4
-            for (int k = 0; k < ksteps; ++k) {
-              if (PAIR) umma_bf16_pair(d, da_j + (uint64_t)(k * a_step), db_s + (uint64_t)(k * b_step), idesc, (it > 0 || k > 0) ? 1u : 0u);
-              else      umma_bf16(d, da_j + (uint64_t)(k * a_step), db_s + (uint64_t)(k * b_step), idesc, (it > 0 || k > 0) ? 1u : 0u);
+              for (int k = 0; k < ksteps; ++k) {
+                const uint32_t accf = (it > 0 || q > 0 || k > 0) ? 1u : 0u;
+                if (PAIR) umma_bf16_pair(d, da_j + (uint64_t)(k * a_step), db_q + (uint64_t)(k * b_step), idesc, accf);
+                else      umma_bf16(d, da_j + (uint64_t)(k * a_step), db_q + (uint64_t)(k * b_step), idesc, accf);
+              }
             }
           }
           // frees the smem slot (in both CTAs of a pair) once these MMAs have read it
@@ -828,14 +854,21 @@ __global__ void weights_to_bf16_batched_kernel(const RelayoutJob* __restrict__ j
 // ------------------------------------------------------------------------------------------
 // host side: tensor maps and plans
 // ------------------------------------------------------------------------------------------
+typedef void (*conv_tc_fn)(TcConvParams);
+static conv_tc_fn conv_tc_variant(bool fused, bool pair, bool halo) {
+  if (halo) {
+    if (fused) return pair ? conv_tc_kernel<true, true, true> : conv_tc_kernel<true, false, true>;
+    return pair ? conv_tc_kernel<false, true, true> : conv_tc_kernel<false, false, true>;
+  }
+  if (fused) return pair ? conv_tc_kernel<true, true, false> : conv_tc_kernel<true, false, false>;
+  return pair ? conv_tc_kernel<false, true, false> : conv_tc_kernel<false, false, false>;
+}
 static cudaError_t set_conv_tc_smem_attr() {
-  cudaError_t e = cudaFuncSetAttribute(conv_tc_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024));
-  if (e != cudaSuccess) return e;
-  e = cudaFuncSetAttribute(conv_tc_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024));
-  if (e != cudaSuccess) return e;
-  e = cudaFuncSetAttribute(conv_tc_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024));
-  if (e != cudaSuccess) return e;
-  return cudaFuncSetAttribute(conv_tc_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024));
+  for (int v = 0; v < 8; ++v) {
+    cudaError_t e = cudaFuncSetAttribute(conv_tc_variant(v & 1, v & 2, v & 4), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024));
+    if (e != cudaSuccess) return e;
+  }
+  return cudaSuccess;
 }
 
 // Launch with the programmatic-serialization attribute and, for CTA pairs, a cluster dimension of two.
@@ -924,6 +957,38 @@ static void choose_pixel_box(int Wo, int Ho, int N, int* BW, int* BH, int* BN) {
     }
   }
   *BW = bw; *BH = bh; *BN = bn;
+}
+
+// Halo mode box: one image (BN = 1), BW x BH <= 128 pixels.  Maximise the fraction of the 128 MMA rows that are real
+// output pixels, then minimise the rows loaded per tile, (BH + 2) * BW.
+static double choose_halo_box(int Wo, int Ho, int* BW, int* BH) {
+  double best_eff = -1.0;
+  long best_rows = 0;
+  int bw = 1, bh = 1;
+  for (int w = 1; w <= Wo && w <= 128; ++w)
+    for (int h = 2; h <= Ho && w * h <= 128; ++h) {
+      const long tiles = (long)((Wo + w - 1) / w) * ((Ho + h - 1) / h);
+      const double eff = (double)Wo * Ho / ((double)tiles * 128.0);
+      const long rows = (long)(h + 2) * w * tiles;
+      if (eff > best_eff + 1e-9 || (eff > best_eff - 1e-9 && rows < best_rows)) { best_eff = eff; best_rows = rows; bw = w; bh = h; }
+    }
+  if (const char* e = getenv("RN_TC_HALO_BW")) {           // probing knobs: force the box
+    const int w = atoi(e);
+    const char* e2 = getenv("RN_TC_HALO_BH");
+    int h = e2 ? atoi(e2) : 128 / (w > 0 ? w : 1);
+    if (h > Ho) h = Ho;
+    if (w >= 1 && h >= 2 && w * h <= 128) {
+      bw = w; bh = h;
+      best_eff = (double)Wo * Ho / ((double)((Wo + w - 1) / w) * ((Ho + h - 1) / h) * 128.0);
+    }
+  }
+  *BW = bw; *BH = bh;
+  return best_eff;
+}
+
+static int halo_mode() {
+  const char* e = getenv("RN_TC_HALO");          // 1 = wherever possible; default off (measured: no gain, see create_sub)
+  return e ? atoi(e) : 0;
 }
 
 static int max_block_n() {
@@ -1169,16 +1234,54 @@ static int create_sub(const rn_conv_desc* d, int kind, const void* a, const void
   p.n_tiles = ncols / p.block_n;
   p.gw = p.block_n % 64 == 0 ? 64 : (p.block_n % 32 == 0 ? 32 : 16);
   choose_pixel_box(oW, oH, d->N, &p.BW, &p.BH, &p.BN);
-  p.tiles_w = (oW + p.BW - 1) / p.BW;
-  p.tiles_h = (oH + p.BH - 1) / p.BH;
-  p.tiles_n = (d->N + p.BN - 1) / p.BN;
   p.taps = ntaps;
   for (int t = 0; t < ntaps; ++t) {
     p.tap_map[t] = taps[t].map; p.tap_dw[t] = taps[t].dw; p.tap_dh[t] = taps[t].dh; p.tap_b[t] = taps[t].b;
   }
+  // Halo mode: a 3x3 stencil at stride 1 (all taps on map 0, shifts in {-1, 0, 1}^2), 64-channel k-chunks.
+  {
+    bool stencil = ntaps == 9 && view == nullptr && p.kc == 64;
+    for (int t = 0; t < ntaps && stencil; ++t)
+      stencil = taps[t].map == 0 && taps[t].dw >= -1 && taps[t].dw <= 1 && taps[t].dh >= -1 && taps[t].dh <= 1;
+    const int mode = halo_mode();
+    if (stencil && mode != 0) {
+      int hw_ = 1, hh_ = 2;
+      const double eff = choose_halo_box(oW, oH, &hw_, &hh_);
+      const long tiles_now = (long)((oW + p.BW - 1) / p.BW) * ((oH + p.BH - 1) / p.BH) * ((d->N + p.BN - 1) / p.BN);
+      const double eff_now = (double)oW * oH * d->N / ((double)tiles_now * 128.0);
+      // A rows fetched per output pixel: 9 per-tap boxes, 3 * (BH + 2) / BH in halo mode.  MEASURED on B200
+      // (profiles/r02_halo_sweep.txt): no layer of ResNet-50 gets faster — 56x56 64->64: 0.0573 ms per-tap vs 0.0603 ms
+      // best halo box (8x16), 28x28 128->128: 0.0389 vs 0.0451, 14x14 256->256: 0.0379 vs 0.0388 — because these
+      // kernels are not bound by L2 -> shared-memory traffic but by the rate at which tcgen05.mma fetches its operands
+      // from shared memory (~45 B/clk/SM), which the halo does not change, while a one-image box
+      // wastes an eighth of the MMA rows.  Halo mode therefore stays opt-in (RN_TC_HALO=1).
+      (void)eff; (void)eff_now;
+      if (mode == 1) {
+        p.halo = 1;
+        p.BW = hw_; p.BH = hh_; p.BN = 1;
+        // group the taps by horizontal shift (first-seen order); inside a group the vertical taps keep weight order
+        int ng = 0;
+        int8_t seen[3] = {0, 0, 0};
+        for (int t = 0; t < ntaps; ++t) {
+          int g = -1;
+          for (int q = 0; q < ng; ++q) if (p.halo_dw[q] == taps[t].dw) g = q;
+          if (g < 0) { g = ng++; p.halo_dw[g] = taps[t].dw; seen[g] = 0; }
+          p.halo_row[g][seen[g]] = (int8_t)(taps[t].dh + 1);
+          p.halo_b[g][seen[g]] = taps[t].b;
+          seen[g]++;
+        }
+        p.halo_dh0 = -1;
+      }
+    }
+  }
+  p.tiles_w = (oW + p.BW - 1) / p.BW;
+  p.tiles_h = (oH + p.BH - 1) / p.BH;
+  p.tiles_n = (d->N + p.BN - 1) / p.BN;
   const int row_bytes = p.kc * 2;
   const uint32_t box_rows = (uint32_t)(p.BW * p.BH * p.BN);
-  p.a_bytes = ((uint32_t)TC_BLOCK_M * row_bytes + 1023u) & ~1023u;
+  // halo mode: the box holds BH + 2 rows, and the MMA of the LAST vertical tap reads 128 rows from row 2 * BW on
+  const uint32_t a_rows = p.halo ? (uint32_t)(2 * p.BW) + TC_BLOCK_M : TC_BLOCK_M;
+  p.a_bytes = (a_rows * row_bytes + 1023u) & ~1023u;
   // CTA pair: one tcgen05.mma.cta_group::2 stream over two neighbouring pixel-tile groups; each CTA stages half of
   // the B tile.  Needs two whole 64-column halves (MN-major boxes) / 8-row groups (K-major) and full swizzle atoms.
   {
@@ -1232,7 +1335,7 @@ static int create_sub(const rn_conv_desc* d, int kind, const void* a, const void
     for (int cand = 4; cand >= 2; cand >>= 1) {
       if (forced && cand != forced) continue;
       if (cand * p.block_n > 512) continue;
-      if ((budget - fixed) / ((size_t)cand * p.a_bytes + p.b_bytes) < 3) continue;
+      if ((budget - fixed) / ((size_t)cand * p.a_bytes + (size_t)(p.halo ? 3 : 1) * p.b_bytes) < 3) continue;
       // measured on B200: sharing B across two pixel tiles pays (+10..18 %) only while TMEM can still be
       // double-buffered (2 * cand * BLOCK_N <= 512) and every SM keeps at least one work item
       if (!forced && (2 * cand * p.block_n > 512 || cand > 2)) continue;
@@ -1247,13 +1350,14 @@ static int create_sub(const rn_conv_desc* d, int kind, const void* a, const void
   uint32_t cols = 32;
   while (cols < (uint32_t)(p.tstages * acc_m * p.block_n)) cols <<= 1;
   p.tmem_cols = cols;
-  int stages = (int)((budget - fixed) / ((size_t)acc_m * p.a_bytes + p.b_bytes));
+  const size_t stage_sz = (size_t)acc_m * p.a_bytes + (size_t)(p.halo ? 3 : 1) * p.b_bytes;
+  int stages = (int)((budget - fixed) / stage_sz);
   if (stages > 8) stages = 8;
   if (stages < 2) return fail(RN_ERR_UNSUPPORTED, "convtc: tile does not fit shared memory");
   p.stages = stages;
-  *smem_bytes = fixed + (size_t)stages * ((size_t)acc_m * p.a_bytes + p.b_bytes);
+  *smem_bytes = fixed + (size_t)stages * stage_sz;
   int rc;
-  const uint32_t abox[4] = {(uint32_t)p.kc, (uint32_t)p.BW, (uint32_t)p.BH, (uint32_t)p.BN};
+  const uint32_t abox[4] = {(uint32_t)p.kc, (uint32_t)p.BW, (uint32_t)(p.halo ? p.BH + 2 : p.BH), (uint32_t)p.BN};
   if (b_taps == 0) b_taps = d->k * d->k;
   rc = view ? encode_view(&p.a_map[0], a, *view, abox, row_bytes)
             : encode_activation_maps(p.a_map, a, cred, aW, aH, d->N, kind == 0 ? d->stride : 1, abox, row_bytes);
@@ -1511,10 +1615,7 @@ extern "C" int rn_convtc_run(rn_convtc_plan* plan, float beta, void* stream) {
     p.accumulate = beta != 0.f ? 1 : 0;
     const bool fused = p.fuse_add || p.fuse_stats || p.fuse_bnbwd;
     const int threads = (p.fuse_add || p.fuse_bnbwd) ? TC_THREADS_RES : TC_CONV_THREADS;
-    if (fused && p.pair)       launch_conv(conv_tc_kernel<true, true>, plan->grid[i], threads, plan->smem_sub[i], st, true, p);
-    else if (fused)            launch_conv(conv_tc_kernel<true, false>, plan->grid[i], threads, plan->smem_sub[i], st, false, p);
-    else if (p.pair)           launch_conv(conv_tc_kernel<false, true>, plan->grid[i], threads, plan->smem_sub[i], st, true, p);
-    else                       launch_conv(conv_tc_kernel<false, false>, plan->grid[i], threads, plan->smem_sub[i], st, false, p);
+    launch_conv(conv_tc_variant(fused, p.pair != 0, p.halo != 0), plan->grid[i], threads, plan->smem_sub[i], st, p.pair != 0, p);
     int rc = check_launch("conv_tc_kernel");
     if (rc) return rc;
   }
@@ -1532,7 +1633,7 @@ extern "C" int rn_convtc_plan_describe(const rn_convtc_plan* plan, char* buf, si
   const TcConvParams& p = plan->p[0];
   snprintf(buf, n, "%s subs=%d block_n=%d acc_m=%d box=%dx%dx%d kc=%d taps=%d stages=%d tstages=%d pair=%d grid=%d fused=%d%d%d halo=%d",
            plan->kind == 0 ? "fprop" : "dgrad", plan->nsub, p.block_n, p.acc_m, p.BW, p.BH, p.BN, p.kc, p.taps, p.stages,
-           p.tstages, p.pair, plan->grid[0], p.fuse_add, p.fuse_stats, p.fuse_bnbwd, 0);
+           p.tstages, p.pair, plan->grid[0], p.fuse_add, p.fuse_stats, p.fuse_bnbwd, p.halo);
   return RN_OK;
 }
 

@@ -116,6 +116,47 @@ def test_convtc_cta_pairs(case, mode, monkeypatch):
         assert rel_err(out.float(), want) < 2e-2, ("kind", kind)
 
 
+HALO_CASES = [(2, 16, 16, 64, 64, 3, 1, 1), (2, 24, 24, 64, 64, 3, 1, 1), (3, 14, 14, 64, 128, 3, 1, 1),
+              (2, 28, 28, 128, 128, 3, 1, 1), (2, 56, 56, 64, 64, 3, 1, 1), (5, 9, 11, 64, 64, 3, 1, 1)]
+
+
+@pytest.mark.parametrize("pair", ["0", "1"])
+@pytest.mark.parametrize("case", HALO_CASES)
+def test_convtc_halo_mode(case, pair, monkeypatch):
+    """3x3 halo mode (opt-in, RN_TC_HALO=1): one (BH + 2)-row box per horizontal tap, the three vertical taps read it
+    at row offsets 0, BW, 2*BW through the matrix descriptor's start address — including box widths that are not a
+    multiple of the 8-row swizzle atom (5, 7, 4, 14, 9 ...).  fprop and dgrad against the oracle, with and without
+    CTA pairs."""
+    from distributed_tensorflow_resnet_b200._lib import describe_plan
+    monkeypatch.setenv("RN_TC_HALO", "1")
+    monkeypatch.setenv("RN_TC_PAIR", pair)
+    N, H, W, Cin, Cout, k, s, pad = case
+    g = torch.Generator().manual_seed(sum(case) + 3)
+    x = torch.randn(N, H, W, Cin, generator=g).to(BF)
+    w = (torch.randn(k, k, Cin, Cout, generator=g) / (k * k * Cin) ** 0.5).to(BF)
+    dy = torch.randn(N, H, W, Cout, generator=g).to(BF)
+    net = ro.Net(dtype=torch.float64, params={"w": w.double().numpy()})
+    xv = ro.Var(x.double())
+    yv = net.conv2d(xv, "w", k, Cin, Cout, s, pad, (H, W), None, "y")
+    yv.grad = dy.double()
+    net.backward()
+    d = ConvDesc(N, H, W, Cin, H, W, Cout, k, s, pad, RN_BF16)
+    _, wd = _weights(w)
+    X, DY = dev(x), dev(dy)
+    Y = torch.full((N, H, W, Cout), float("nan"), dtype=BF, device="cuda")
+    DX = torch.full((N, H, W, Cin), float("nan"), dtype=BF, device="cuda")
+    for kind, a, out, want in ((0, X, Y, yv.val), (1, DY, DX, xv.grad)):
+        plan = C.c_void_p()
+        check(lib.rn_convtc_plan_create(C.byref(d), kind, ptr(a), ptr(wd), ptr(out), None, 0, C.byref(plan)), "plan")
+        assert "halo=1" in describe_plan(plan), describe_plan(plan)
+        for _ in range(2):
+            check(lib.rn_convtc_run(plan, 0.0, stream()), "run")
+        torch.cuda.synchronize()
+        lib.rn_convtc_plan_destroy(plan)
+        assert torch.isfinite(out.float()).all()
+        assert rel_err(out.float(), want) < 2e-2, ("kind", kind)
+
+
 S2_CASES = [
     # N, H, W, Cin, Cout, k, stride, pad, (Ho, Wo)
     (4, 16, 16, 64, 128, 3, 2, 1, (8, 8)),       # official 3x3 s2: symmetric fixed_padding + VALID
