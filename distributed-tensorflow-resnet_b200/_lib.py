@@ -87,6 +87,9 @@ SIGNATURES = {
     "rn_convtc_plan_create_fused_dgrad": (C.c_int, [pdesc, vp, vp, vp, vp, vp, vp, vp, vp, f32, vp, C.POINTER(i32),
                                                     C.POINTER(vp)]),
     "rn_bn_bwd_finalize": (C.c_int, [vp, i32, i32, vp, vp, vp]),
+    "rn_convtc_bnin_supported": (C.c_int, [pdesc, C.c_int]),
+    "rn_convtc_plan_create_bnin": (C.c_int, [pdesc, C.c_int, vp, vp, vp, vp, vp, f32, vp, vp, vp, vp, C.POINTER(i32), vp, sz,
+                                             C.POINTER(vp)]),
     "rn_convtc_run": (C.c_int, [vp, f32, vp]),
     "rn_convtc_plan_destroy": (C.c_int, [vp]),
     "rn_convtc_plan_describe": (C.c_int, [vp, C.c_char_p, sz]),

@@ -313,8 +313,7 @@ bn_apply_kernel(const T* __restrict__ x, T* __restrict__ y, int64_t M, int C, Bn
   for (int i = 0; i < V; ++i) {
     const int c = cg * V + i;
     const float rs = stats_are_moving ? rsqrtf(rstd[c] + eps) : rstd[c];
-    a[i] = gamma[c] * rs;
-    b[i] = beta[c] - mean[c] * a[i];
+    bn_affine(gamma[c], beta[c], mean[c], rs, &a[i], &b[i]);
   }
   const int64_t stride = L.RY;
   const int64_t col = (int64_t)cg * V;

@@ -91,6 +91,14 @@ __device__ __forceinline__ float warp_sum(float v) {
 
 __device__ __forceinline__ float act_fn(float v, float leak) { return v < 0.f ? leak * v : v; }
 
+// y = act(a * x + b) with a = gamma * rstd, b = beta - mean * a: the ONE definition of the normalisation constants,
+// shared by bn_apply_kernel and by the convolution kernels that apply the BN to their operand on the fly, so that both
+// produce bit-identical activations.
+__device__ __forceinline__ void bn_affine(float gamma, float beta, float mean, float rstd, float* a, float* b) {
+  *a = gamma * rstd;
+  *b = beta - mean * (*a);
+}
+
 // ---- programmatic dependent launch -------------------------------------------------------------
 // The hot kernels of the step are launched with the programmatic-stream-serialization attribute: the next
 // kernel of the stream may be scheduled (and run its prologue: barrier init, TMEM allocation, descriptor

@@ -74,6 +74,13 @@ struct TcConvParams {
   // (start address + the descriptor's base-offset field when the offset is not a whole 1024-byte swizzle atom);
   // the stage also holds the three weight tiles.  A traffic per output tile drops from 9 to 3 * (BH + 2) / BH boxes.
   int halo;                       // 0 / 1
+  // Operand transform (1x1 fprop): the A operand is the INPUT of a training-mode batch_norm_relu; four extra warps
+  // turn every landed A tile into bf16(act(a*x + b)) in place (a = gamma*rstd, b = beta - mean*a, exactly the
+  // arithmetic of bn_apply_kernel) before the MMA warp may read it, so the normalised tensor is never written to HBM.
+  int xf;                         // 0 / 1
+  int xf_channels;                // channels of the BN (= reduction length of the GEMM)
+  const float *xf_gamma, *xf_beta, *xf_mean, *xf_rstd;
+  float xf_leak;
   int8_t halo_dw[3];              // per stage group: horizontal shift of the box
   int8_t halo_dh0;                // vertical shift of the box origin (the topmost tap)
   int8_t halo_row[3][3];          // [group][j]: first row of the box the j-th vertical tap of the group reads, in units of BW rows
@@ -88,9 +95,36 @@ constexpr int TC_THREADS_RES = TC_CONV_THREADS + 32;
 // stream of tcgen05.mma.cta_group::2 instructions issued by the leader CTA (see rn_tc_common.cuh).
 // HALO = true: 3x3 halo mode (see TcConvParams::halo); compiled separately so that the per-tap issue loops of the
 // other layers stay as tight as they were.
-template <bool FUSED, bool PAIR, bool HALO>
-__global__ void __launch_bounds__(FUSED ? TC_THREADS_RES : TC_CONV_THREADS, 1)
+// Operand transform of one 16-byte chunk (8 bf16 channels of one pixel row): bf16(act(a*x + b)) with the arithmetic of
+// bn_apply_kernel (fp32 fma per element, one rounding to bf16).  ab = (a0, b0, a1, b1, ...).  For a plain ReLU the
+// max is taken on the packed bf16 pair after rounding — rounding is monotonic and keeps zero, so
+// max(round(v), 0) == round(max(v, 0)) bit for bit — which halves the activation instructions.
+__device__ __forceinline__ uint4 bn_transform_chunk(const uint4 v, const float (&ab)[16], float leak) {
+  const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+  uint32_t o[4];
+#pragma unroll
+  for (int e = 0; e < 4; ++e) {
+    const float2 x = make_float2(__uint_as_float(w[e] << 16), __uint_as_float(w[e] & 0xffff0000u));
+    const float2 y = __ffma2_rn(x, make_float2(ab[4 * e], ab[4 * e + 2]), make_float2(ab[4 * e + 1], ab[4 * e + 3]));
+    if (leak == 0.f) {
+      const __nv_bfloat162 h = __hmax2(__floats2bfloat162_rn(y.x, y.y), __floats2bfloat162_rn(0.f, 0.f));
+      o[e] = *reinterpret_cast<const uint32_t*>(&h);
+    } else {
+      const __nv_bfloat162 h = __floats2bfloat162_rn(act_fn(y.x, leak), act_fn(y.y, leak));
+      o[e] = *reinterpret_cast<const uint32_t*>(&h);
+    }
+  }
+  return make_uint4(o[0], o[1], o[2], o[3]);
+}
+
+// XF = true: operand transform (see TcConvParams::xf): TC_XF_WARPS more warps, one more barrier per stage.
+constexpr int TC_XF_WARPS = 4;            // measured: 8 warps are slower (9.93 -> 10.23 ms per ResNet-50 step): the transform is bound by
+                                           // shared-memory bandwidth (it adds a read and a write of every operand byte), not by issue slots
+constexpr int TC_XF_ROWS = TC_XF_WARPS * 4;  // rows covered by one pass of the transform threads (8 threads per 128-byte row)
+template <bool FUSED, bool PAIR, bool HALO, bool XF>
+__global__ void __launch_bounds__((FUSED ? TC_THREADS_RES : TC_CONV_THREADS) + (XF ? TC_XF_WARPS * 32 : 0), 1)
 conv_tc_kernel(const __grid_constant__ TcConvParams p) {
+  static_assert(!(XF && (PAIR || HALO)), "the operand transform is built for single-CTA 1x1 layers");
   const uint32_t cta_rank = PAIR ? cluster_ctarank() : 0u;
   const bool leader = cta_rank == 0u;
   const bool fuse_add = FUSED && p.fuse_add;
@@ -111,6 +145,8 @@ conv_tc_kernel(const __grid_constant__ TcConvParams p) {
   float* ctab = pacc + 2 * p.ncols_total;                                     // [ncols_total][4] = a, b, mean, rstd (fused BN backward)
   uint8_t* after_stats = after_res + (fuse_stats ? 8192 + (size_t)p.ncols_total * 8 : 0) +
                          (fuse_bnbwd ? (size_t)p.ncols_total * 16 : 0);
+  float* xtab = reinterpret_cast<float*>(after_stats);                        // [xf_channels][2] = a, b (operand transform)
+  if (XF) after_stats += (size_t)p.xf_channels * 8;
   uint64_t* bars = reinterpret_cast<uint64_t*>(after_stats);
   uint64_t* full = bars;                  // [stages]
   uint64_t* empty = bars + p.stages;      // [stages]
@@ -118,11 +154,13 @@ conv_tc_kernel(const __grid_constant__ TcConvParams p) {
   uint64_t* tempty = tfull + 2;           // [2]
   uint64_t* rfull = tempty + 2;           // [TC_RES_SLOTS_MAX]
   uint64_t* rempty = rfull + TC_RES_SLOTS_MAX;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(rempty + TC_RES_SLOTS_MAX);
+  uint64_t* xfull = rempty + TC_RES_SLOTS_MAX;      // [stages] (operand transform: A tile rewritten, MMA may read)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(xfull + (XF ? p.stages : 0));
 
   const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
   if (warp == 0 && lane == 0) {
     for (int i = 0; i < p.stages; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+    if (XF) for (int i = 0; i < p.stages; ++i) mbar_init(&xfull[i], TC_XF_WARPS);
     // pair: the leader's tempty collects the epilogue warps of BOTH CTAs (the peer's arrive remotely)
     for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], PAIR ? 2 * TC_EPI_WARPS : TC_EPI_WARPS); }
     for (int i = 0; i < TC_RES_SLOTS_MAX; ++i) { mbar_init(&rfull[i], 1); mbar_init(&rempty[i], TC_EPI_WARPS); }
@@ -252,7 +290,7 @@ conv_tc_kernel(const __grid_constant__ TcConvParams p) {
       tc_fence_after();
       const uint32_t d_tmem = tmem_base + (uint32_t)(acc * p.acc_m * p.block_n);
       for (int it = 0; it < k_iters; ++it) {
-        mbar_wait(&full[stage], phase);
+        mbar_wait(XF ? &xfull[stage] : &full[stage], phase);
         tc_fence_after();
         if (elect_one()) {
           const uint64_t da_s = da0 + (uint64_t)((uint32_t)stage * stage16);
@@ -506,6 +544,47 @@ conv_tc_kernel(const __grid_constant__ TcConvParams p) {
       if (elect_one()) tma_store_wait<0>();
       __syncwarp();
     }
+  } else if (XF && warp >= (int)(blockDim.x / 32) - TC_XF_WARPS) {
+    // ===================== operand transform (the last four warps) =====================
+    const int tt = (warp - ((int)(blockDim.x / 32) - TC_XF_WARPS)) * 32 + lane;       // 0..127
+    for (int c = tt; c < p.xf_channels; c += TC_XF_WARPS * 32) {
+      float a, b;
+      bn_affine(p.xf_gamma[c], p.xf_beta[c], p.xf_mean[c], p.xf_rstd[c], &a, &b);
+      xtab[2 * c] = a; xtab[2 * c + 1] = b;
+    }
+    asm volatile("bar.sync 2, %0;" ::"n"(TC_XF_WARPS * 32) : "memory");
+    // a thread owns one 16-byte chunk column (8 channels: constants in registers) of rows r0, r0 + TC_XF_ROWS, ...; the
+    // 128-byte swizzle keeps logical chunk lc of row r at physical chunk lc ^ (r & 7)
+    const int lc = tt & 7, r0 = tt >> 3;
+    const float leak = p.xf_leak;
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int t = wstart; t < total; t += wstep) {
+      const int mg = t / p.n_tiles;
+      int nvalid = m_tiles - mg * p.acc_m;
+      if (nvalid > p.acc_m) nvalid = p.acc_m;
+      for (int it = 0; it < k_iters; ++it) {
+        const int kk = it % p.k_chunks;
+        float ab[16];
+        const float4* src = reinterpret_cast<const float4*>(xtab + 2 * (kk * 64 + lc * 8));
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { const float4 v = src[i]; ab[4 * i] = v.x; ab[4 * i + 1] = v.y; ab[4 * i + 2] = v.z; ab[4 * i + 3] = v.w; }
+        mbar_wait(&full[stage], phase);
+        uint8_t* sa = smem + (size_t)stage * stage_bytes;
+        for (int j = 0; j < nvalid; ++j) {
+          uint8_t* tile = sa + (size_t)j * p.a_bytes;
+#pragma unroll 4
+          for (int r = r0; r < TC_BLOCK_M; r += TC_XF_ROWS) {
+            uint4* q = reinterpret_cast<uint4*>(tile + r * 128 + ((lc ^ (r & 7)) << 4));
+            *q = bn_transform_chunk(*q, ab, leak);
+          }
+        }
+        fence_proxy_async();                 // generic-proxy writes -> visible to the tensor core's (async proxy) reads
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&xfull[stage]);
+        if (++stage == p.stages) { stage = 0; phase ^= 1; }
+      }
+    }
   } else {
     // ===================== residual-tile producer (warp 10; only launched with the fused add) =====================
     const uint32_t rtx = (uint32_t)(p.BW * p.BH * p.BN) * 128u;
@@ -571,9 +650,15 @@ struct TcWgradParams {
   int kp, stages;
   uint32_t stage_bytes, tmem_cols;
   int8_t tap_map[TC_MAX_TAPS], tap_dw[TC_MAX_TAPS], tap_dh[TC_MAX_TAPS];
+  // operand transform (see TcConvParams::xf): X is the input of a training-mode BN+ReLU, normalised in shared memory
+  int xf;
+  const float *xf_gamma, *xf_beta, *xf_mean, *xf_rstd;
+  float xf_leak;
 };
 
-__global__ void __launch_bounds__(TC_THREADS, 1) conv_wgrad_tc_kernel(const __grid_constant__ TcWgradParams p) {
+template <bool XF>
+__global__ void __launch_bounds__(TC_THREADS + (XF ? TC_XF_WARPS * 32 : 0), 1)
+conv_wgrad_tc_kernel(const __grid_constant__ TcWgradParams p) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base_u32 = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* smem = smem_raw + (base_u32 - smem_u32(smem_raw));
@@ -583,10 +668,13 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_wgrad_tc_kernel(const __gr
   uint64_t* empty = bars + p.stages;
   uint64_t* tfull = bars + 2 * p.stages;
   uint64_t* tempty = tfull + 1;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 1);
+  uint64_t* xfull = tempty + 1;                                               // [stages] (operand transform)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(xfull + (XF ? p.stages : 0));
+  float* xtab = reinterpret_cast<float*>(epi_slab + 16384 + 1024);            // [Cin][2] = a, b (operand transform)
   const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
   if (warp == 0 && lane == 0) {
     for (int i = 0; i < p.stages; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+    if (XF) for (int i = 0; i < p.stages; ++i) mbar_init(&xfull[i], TC_XF_WARPS);
     mbar_init(tfull, 1);
     mbar_init(tempty, 4);
     fence_barrier_init();
@@ -669,7 +757,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_wgrad_tc_kernel(const __gr
       tc_fence_after();
       const int kt_begin = z * p.tiles_per_split, kt_end = min((z + 1) * p.tiles_per_split, p.k_tiles);
       for (int kt = kt_begin; kt < kt_end; ++kt) {
-        mbar_wait(&full[stage], phase);
+        mbar_wait(XF ? &xfull[stage] : &full[stage], phase);
         tc_fence_after();
         if (elect_one()) {
           const uint64_t da_s = da0 + (uint64_t)((uint32_t)stage * stage16);
@@ -689,6 +777,46 @@ __global__ void __launch_bounds__(TC_THREADS, 1) conv_wgrad_tc_kernel(const __gr
         if (++stage == p.stages) { stage = 0; phase ^= 1; }
       }
       tphase ^= 1;
+    }
+  } else if (XF && warp >= 6) {
+    // ===================== operand transform (warps 6..): X tile -> bf16(act(a*x + b)) in place =====================
+    const int tt = (warp - 6) * 32 + lane;
+    for (int c = tt; c < p.Cin; c += TC_XF_WARPS * 32) {
+      float a, b;
+      bn_affine(p.xf_gamma[c], p.xf_beta[c], p.xf_mean[c], p.xf_rstd[c], &a, &b);
+      xtab[2 * c] = a; xtab[2 * c + 1] = b;
+    }
+    asm volatile("bar.sync 2, %0;" ::"n"(TC_XF_WARPS * 32) : "memory");
+    const int lc = tt & 7, r0 = tt >> 3;
+    const float leak = p.xf_leak;
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int it = blockIdx.x; it < total; it += gridDim.x) {
+      const int z = it % p.splits;
+      const int rg = it / (p.splits * p.n_tiles);
+      int valid = p.RB - rg * rb_per_cta;
+      if (valid > rb_per_cta) valid = rb_per_cta;
+      const int kt_end = min((z + 1) * p.tiles_per_split, p.k_tiles);
+      for (int kt = z * p.tiles_per_split; kt < kt_end; ++kt) {
+        mbar_wait(&full[stage], phase);
+        uint8_t* sa = smem + (size_t)stage * p.stage_bytes;
+        for (int j = 0; j < valid; ++j) {
+          const int cb = (rg * rb_per_cta + j) % p.cin_blocks;             // 64-channel block of this box
+          float ab[16];
+          const float4* src = reinterpret_cast<const float4*>(xtab + 2 * (cb * 64 + lc * 8));
+#pragma unroll
+          for (int i = 0; i < 4; ++i) { const float4 v = src[i]; ab[4 * i] = v.x; ab[4 * i + 1] = v.y; ab[4 * i + 2] = v.z; ab[4 * i + 3] = v.w; }
+          uint8_t* tile = sa + (size_t)j * p.a_box_bytes;
+          for (int r = r0; r < p.kp; r += TC_XF_ROWS) {
+            uint4* q = reinterpret_cast<uint4*>(tile + r * 128 + ((lc ^ (r & 7)) << 4));
+            *q = bn_transform_chunk(*q, ab, leak);
+          }
+        }
+        fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&xfull[stage]);
+        if (++stage == p.stages) { stage = 0; phase ^= 1; }
+      }
     }
   } else {
     const int quad = warp & 3;
@@ -855,17 +983,19 @@ __global__ void weights_to_bf16_batched_kernel(const RelayoutJob* __restrict__ j
 // host side: tensor maps and plans
 // ------------------------------------------------------------------------------------------
 typedef void (*conv_tc_fn)(TcConvParams);
-static conv_tc_fn conv_tc_variant(bool fused, bool pair, bool halo) {
+static conv_tc_fn conv_tc_variant(bool fused, bool pair, bool halo, bool xf) {
+  if (xf) return fused ? conv_tc_kernel<true, false, false, true> : conv_tc_kernel<false, false, false, true>;
   if (halo) {
-    if (fused) return pair ? conv_tc_kernel<true, true, true> : conv_tc_kernel<true, false, true>;
-    return pair ? conv_tc_kernel<false, true, true> : conv_tc_kernel<false, false, true>;
+    if (fused) return pair ? conv_tc_kernel<true, true, true, false> : conv_tc_kernel<true, false, true, false>;
+    return pair ? conv_tc_kernel<false, true, true, false> : conv_tc_kernel<false, false, true, false>;
   }
-  if (fused) return pair ? conv_tc_kernel<true, true, false> : conv_tc_kernel<true, false, false>;
-  return pair ? conv_tc_kernel<false, true, false> : conv_tc_kernel<false, false, false>;
+  if (fused) return pair ? conv_tc_kernel<true, true, false, false> : conv_tc_kernel<true, false, false, false>;
+  return pair ? conv_tc_kernel<false, true, false, false> : conv_tc_kernel<false, false, false, false>;
 }
 static cudaError_t set_conv_tc_smem_attr() {
-  for (int v = 0; v < 8; ++v) {
-    cudaError_t e = cudaFuncSetAttribute(conv_tc_variant(v & 1, v & 2, v & 4), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024));
+  for (int v = 0; v < 16; ++v) {
+    if ((v & 8) && (v & 6)) continue;                  // the operand transform has no pair / halo variants
+    cudaError_t e = cudaFuncSetAttribute(conv_tc_variant(v & 1, v & 2, v & 4, v & 8), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024));
     if (e != cudaSuccess) return e;
   }
   return cudaSuccess;
@@ -1218,13 +1348,22 @@ extern "C" size_t rn_convtc_scratch_bytes(const rn_conv_desc* d, int kind) {
 struct TapSpec { int8_t map, dw, dh, b; };
 // dgrad whose output is the dy of a BN+ReLU: the epilogue accumulates that BN's backward reductions
 struct BnBwdOpts { const void* x; const float *gamma, *beta, *mean, *rstd; float leak; };
+// fprop / wgrad whose activation operand is the INPUT of a training-mode BN+ReLU, normalised on the fly
+struct BnOperand { const float *gamma, *beta, *mean, *rstd; float leak; };
 
 static int create_sub(const rn_conv_desc* d, int kind, const void* a, const void* b, const void* out_base,
                       int oW, int oH, const uint64_t* ostr, const TapSpec* taps, int ntaps, TcConvParams* pp,
                       int* grid, size_t* smem_bytes, const ActView* view = nullptr, int b_taps = 0,
-                      const void* residual = nullptr, float* stat_partials = nullptr, const BnBwdOpts* bnbwd = nullptr) {
+                      const void* residual = nullptr, float* stat_partials = nullptr, const BnBwdOpts* bnbwd = nullptr,
+                      const BnOperand* xf = nullptr) {
   TcConvParams& p = *pp;
   memset(&p, 0, sizeof(p));
+  if (xf) {
+    if (kind != 0 || ntaps != 1 || view != nullptr || (d->Cin % 64) != 0)
+      return fail(RN_ERR_UNSUPPORTED, "convtc: the BN operand transform needs a 1x1 fprop over a multiple of 64 channels");
+    p.xf = 1; p.xf_channels = d->Cin;
+    p.xf_gamma = xf->gamma; p.xf_beta = xf->beta; p.xf_mean = xf->mean; p.xf_rstd = xf->rstd; p.xf_leak = xf->leak;
+  }
   const int cred = kind == 0 ? d->Cin : d->Cout;
   const int ncols = kind == 0 ? d->Cout : d->Cin;
   const int aW = kind == 0 ? d->W : d->Wo, aH = kind == 0 ? d->H : d->Ho;   // activation tensor that is gathered
@@ -1291,7 +1430,7 @@ static int create_sub(const rn_conv_desc* d, int kind, const void* a, const void
     // operand-traffic bound — N = 256 tiles with a long reduction (3x3 over >= 256 channels, 1x1 over >= 1024) —
     // and lose 10-50 % on the HBM-bound large-image layers (short reductions, one or two k-chunks per tile), where
     // running two CTAs in lock step only removes slack.  Default: N = 256 and taps * channels >= 1024.
-    p.pair = can && (mode == 1 || (mode != 0 && p.block_n >= 256 && (long)ntaps * cred >= 1024)) ? 1 : 0;
+    p.pair = can && !p.xf && (mode == 1 || (mode != 0 && p.block_n >= 256 && (long)ntaps * cred >= 1024)) ? 1 : 0;
   }
   const int b_rows = p.pair ? p.block_n / 2 : p.block_n;           // B rows (columns of the output) staged per CTA
   p.b_bytes = ((uint32_t)b_rows * row_bytes + 1023u) & ~1023u;
@@ -1326,7 +1465,7 @@ static int create_sub(const rn_conv_desc* d, int kind, const void* a, const void
   }
   const size_t fixed = 2 * 16384 + 1024 + 1024 + ((p.fuse_add || p.fuse_bnbwd) ? (size_t)p.res_slots * 16384 : 0) +
                        ((p.fuse_stats || p.fuse_bnbwd) ? 8192 + (size_t)ncols * 8 : 0) +
-                       (p.fuse_bnbwd ? (size_t)ncols * 16 : 0);
+                       (p.fuse_bnbwd ? (size_t)ncols * 16 : 0) + (p.xf ? (size_t)p.xf_channels * 8 : 0);
   const size_t budget = 227 * 1024;
   int acc_m = 1;
   {
@@ -1455,7 +1594,7 @@ static int create_gemm_plan(const rn_conv_desc* d, int kind, const void* a, cons
 
 static int create_wgrad_plan(const rn_conv_desc* d, const void* x, const void* dy, void* dw, void* scratch,
                              size_t scratch_bytes, rn_convtc_plan* pl, const ActView* view = nullptr,
-                             const TapSpec* taps = nullptr) {
+                             const TapSpec* taps = nullptr, const BnOperand* xf = nullptr) {
   WgradShape ws;
   if (!wgrad_shape(d, &ws)) return fail(RN_ERR_UNSUPPORTED, "convtc wgrad: shape not supported");
   if (ws.scratch > 0 && (scratch == nullptr || scratch_bytes < ws.scratch))
@@ -1468,6 +1607,16 @@ static int create_wgrad_plan(const rn_conv_desc* d, const void* x, const void* d
   w.stages = ws.stages; w.stage_bytes = ws.stage_bytes; w.tmem_cols = ws.tmem_cols;
   w.bwA = ws.bwA; w.bwB = ws.bwB; w.blocksA = ws.blocksA; w.a_box_bytes = ws.a_box_bytes; w.b_box_bytes = ws.b_box_bytes;
   w.runA = ws.runA;
+  if (xf) {
+    if (d->k != 1 || ws.bwA != 64 || view != nullptr)
+      return fail(RN_ERR_UNSUPPORTED, "convtc wgrad: the BN operand transform needs a 1x1 conv over a multiple of 64 channels");
+    w.xf = 1;
+    w.xf_gamma = xf->gamma; w.xf_beta = xf->beta; w.xf_mean = xf->mean; w.xf_rstd = xf->rstd; w.xf_leak = xf->leak;
+    // the per-channel constants live behind the barriers: give up pipeline stages if they do not fit
+    while ((size_t)w.stages * w.stage_bytes + 16384 + 2048 + (size_t)d->Cin * 8 > (size_t)227 * 1024 && w.stages > 2) --w.stages;
+    if ((size_t)w.stages * w.stage_bytes + 16384 + 2048 + (size_t)d->Cin * 8 > (size_t)227 * 1024)
+      return fail(RN_ERR_UNSUPPORTED, "convtc wgrad: the BN operand transform does not fit shared memory for this shape");
+  }
   w.partial = ws.splits > 1 ? (float*)scratch : (float*)dw;
   for (int r = 0; r < d->k; ++r)
     for (int s = 0; s < d->k; ++s)
@@ -1482,10 +1631,12 @@ static int create_wgrad_plan(const rn_conv_desc* d, const void* x, const void* d
   if (rc) return rc;
   const long total = (long)ws.row_groups * ws.n_tiles * ws.splits;
   pl->wgrid = (int)(total < RN_NUM_SMS ? total : RN_NUM_SMS);
-  pl->wsmem = ws.smem;
+  pl->wsmem = xf ? (size_t)w.stages * w.stage_bytes + 16384 + 2048 + (size_t)d->Cin * 8 : ws.smem;
   pl->dw = (float*)dw;
   pl->dw_elems = (int64_t)d->k * d->k * d->Cin * d->Cout;
-  cudaError_t e = cudaFuncSetAttribute(conv_wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024));
+  cudaError_t e = cudaFuncSetAttribute(conv_wgrad_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024));
+  if (e == cudaSuccess)
+    e = cudaFuncSetAttribute(conv_wgrad_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024));
   if (e != cudaSuccess) return fail(RN_ERR_CUDA, "convtc: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
   return RN_OK;
 }
@@ -1585,13 +1736,61 @@ extern "C" int rn_convtc_plan_create_fused_dgrad(const rn_conv_desc* d, const vo
   return RN_OK;
 }
 
+// ---- convolutions that read the INPUT of a training-mode batch_norm_relu and normalise it on the fly -------------
+extern "C" int rn_convtc_bnin_supported(const rn_conv_desc* d, int kind) {
+  if (!d || (kind != 0 && kind != 2) || d->k != 1 || d->pad != 0 || d->Cin % 64 != 0) return 0;
+  if (!rn_convtc_supported(d, kind)) return 0;
+  if (kind == 2) {
+    WgradShape w;
+    return wgrad_shape(d, &w) && w.bwA == 64 ? 1 : 0;
+  }
+  return 1;
+}
+
+extern "C" int rn_convtc_plan_create_bnin(const rn_conv_desc* d, int kind, const void* bn_x, const float* gamma,
+                                          const float* beta, const float* mean, const float* rstd, float leak,
+                                          const void* b, void* out, const void* residual, float* stat_partials,
+                                          int32_t* stat_rows, void* scratch, size_t scratch_bytes, rn_convtc_plan** plan) {
+  RN_REQUIRE(d && bn_x && gamma && beta && mean && rstd && b && out && plan, "convtc_plan_create_bnin: NULL pointer");
+  if (!rn_convtc_bnin_supported(d, kind))
+    return fail(RN_ERR_UNSUPPORTED, "convtc: the BN operand transform needs a 1x1 convolution over a multiple of 64 channels");
+  RN_REQUIRE((((uintptr_t)bn_x | (uintptr_t)b | (uintptr_t)out | (uintptr_t)residual) & 15) == 0,
+             "convtc: pointers must be 16-byte aligned");
+  RN_REQUIRE(kind == 0 || (residual == nullptr && stat_partials == nullptr), "convtc_plan_create_bnin: fused epilogues belong to fprop");
+  if ((residual || stat_partials) && !rn_convtc_fused_supported(d))
+    return fail(RN_ERR_UNSUPPORTED, "convtc: fused epilogue not supported for this shape");
+  const BnOperand xf = {gamma, beta, mean, rstd, leak};
+  rn_convtc_plan* pl = new rn_convtc_plan();
+  memset(pl, 0, sizeof(*pl));
+  pl->kind = kind;
+  int rc;
+  if (kind == 2) {
+    rc = create_wgrad_plan(d, bn_x, b, out, scratch, scratch_bytes, pl, nullptr, nullptr, &xf);
+  } else {
+    cudaError_t e = set_conv_tc_smem_attr();
+    if (e != cudaSuccess) { delete pl; return fail(RN_ERR_CUDA, "convtc: cudaFuncSetAttribute: %s", cudaGetErrorString(e)); }
+    pl->nsub = 1;
+    TapSpec tap;
+    tap.b = 0;
+    forward_tap(0, 0, 0, d->stride, &tap.map, &tap.dw, &tap.dh);
+    const uint64_t ostr[3] = {(uint64_t)d->Cout * 2, (uint64_t)d->Wo * d->Cout * 2, (uint64_t)d->Ho * d->Wo * d->Cout * 2};
+    rc = create_sub(d, 0, bn_x, b, out, d->Wo, d->Ho, ostr, &tap, 1, &pl->p[0], &pl->grid[0], &pl->smem_sub[0], nullptr, 0,
+                    residual, stat_partials, nullptr, &xf);
+    if (rc == RN_OK && stat_rows) *stat_rows = pl->grid[0];
+  }
+  if (rc) { delete pl; return rc; }
+  *plan = pl;
+  return RN_OK;
+}
+
 extern "C" int rn_convtc_run(rn_convtc_plan* plan, float beta, void* stream) {
   RN_REQUIRE(plan, "convtc_run: NULL plan");
   RN_REQUIRE(beta == 0.f || beta == 1.f, "convtc_run: beta must be 0 or 1");
   cudaStream_t st = as_stream(stream);
   if (plan->kind == 2) {
     if (beta != 0.f) return fail(RN_ERR_UNSUPPORTED, "convtc_run: wgrad overwrites its output (beta must be 0)");
-    launch_pdl(conv_wgrad_tc_kernel, plan->wgrid, TC_THREADS, plan->wsmem, st, plan->w);
+    if (plan->w.xf) launch_pdl(conv_wgrad_tc_kernel<true>, plan->wgrid, TC_THREADS + TC_XF_WARPS * 32, plan->wsmem, st, plan->w);
+    else            launch_pdl(conv_wgrad_tc_kernel<false>, plan->wgrid, TC_THREADS, plan->wsmem, st, plan->w);
     int rc = check_launch("conv_wgrad_tc_kernel");
     if (rc) return rc;
     if (plan->w.splits > 1) {
@@ -1615,7 +1814,8 @@ extern "C" int rn_convtc_run(rn_convtc_plan* plan, float beta, void* stream) {
     p.accumulate = beta != 0.f ? 1 : 0;
     const bool fused = p.fuse_add || p.fuse_stats || p.fuse_bnbwd;
     const int threads = (p.fuse_add || p.fuse_bnbwd) ? TC_THREADS_RES : TC_CONV_THREADS;
-    launch_conv(conv_tc_variant(fused, p.pair != 0, p.halo != 0), plan->grid[i], threads, plan->smem_sub[i], st, p.pair != 0, p);
+    launch_conv(conv_tc_variant(fused, p.pair != 0, p.halo != 0, p.xf != 0), plan->grid[i], threads + (p.xf ? TC_XF_WARPS * 32 : 0),
+                plan->smem_sub[i], st, p.pair != 0, p);
     int rc = check_launch("conv_tc_kernel");
     if (rc) return rc;
   }
@@ -1626,14 +1826,15 @@ extern "C" int rn_convtc_plan_describe(const rn_convtc_plan* plan, char* buf, si
   RN_REQUIRE(plan && buf && n > 0, "convtc_plan_describe: bad arguments");
   if (plan->kind == 2) {
     const TcWgradParams& w = plan->w;
-    snprintf(buf, n, "wgrad block_n=%d acc=%d kp=%d stages=%d splits=%d grid=%d cluster=%d", w.block_n, w.acc, w.kp, w.stages,
-             w.splits, plan->wgrid, 1);
+    snprintf(buf, n, "wgrad block_n=%d acc=%d kp=%d stages=%d splits=%d grid=%d bn_operand=%d", w.block_n, w.acc, w.kp, w.stages,
+             w.splits, plan->wgrid, w.xf);
     return RN_OK;
   }
   const TcConvParams& p = plan->p[0];
   snprintf(buf, n, "%s subs=%d block_n=%d acc_m=%d box=%dx%dx%d kc=%d taps=%d stages=%d tstages=%d pair=%d grid=%d fused=%d%d%d halo=%d",
            plan->kind == 0 ? "fprop" : "dgrad", plan->nsub, p.block_n, p.acc_m, p.BW, p.BH, p.BN, p.kc, p.taps, p.stages,
            p.tstages, p.pair, plan->grid[0], p.fuse_add, p.fuse_stats, p.fuse_bnbwd, p.halo);
+  if (p.xf) strncat(buf, " bn_operand=1", n - strlen(buf) - 1);
   return RN_OK;
 }
 

@@ -265,6 +265,60 @@ class Executor:
                     cv.fuse = dict(out=x, residual=None, bn=n)
                     n.stats_from = cv
 
+    def _plan_operand_fusion(self):
+        """Training-mode BN+ReLU nodes whose output is read ONLY by 1x1 tensor-core convolutions (conv1 / conv3 of a
+        bottleneck block, projection shortcuts) are not materialised: those convolutions read the BN's INPUT and
+        normalise it in shared memory (rn_convtc_plan_create_bnin), in fprop and in wgrad, so the bn_apply pass and the
+        activated tensor disappear from HBM.  OPT-IN (RN_BN_OPERAND_FUSION=1): measured on B200 (ResNet-50 / 224 /
+        batch 128, profiles/r02_bn_operand_ab.txt) the step gets SLOWER, 9.56 -> 9.93 ms — 32 bn_apply launches (0.76 ms)
+        disappear, but rewriting every operand tile in shared memory costs the 1x1 fprops +0.32 ms and the 1x1 wgrads
+        +0.80 ms: the transform adds a shared-memory read and write of every operand byte to kernels that are already
+        bound by shared-memory operand traffic (eight transform warps instead of four made it slower still, 10.23 ms)."""
+        if os.environ.get("RN_BN_OPERAND_FUSION") != "1" or not (self.use_tc and self.bf16):
+            return
+        for n in self.g.nodes:
+            if n.op != "bn_act" or not n.attrs["is_training"]:
+                continue
+            y = n.outputs[0]
+            if not y.consumers:
+                continue
+            ok = True
+            for c in y.consumers:
+                if c.op != "conv2d" or c.inputs[0] is not y or self._is_stem(c):
+                    ok = False
+                    break
+                d = self._desc(c)
+                if not (lib.rn_convtc_bnin_supported(C.byref(d), 0) and (not self.train or lib.rn_convtc_bnin_supported(C.byref(d), 2))):
+                    ok = False
+                    break
+            n.virtual = ok
+
+    def _bn_operand(self, t):
+        """(buffer to read, BN node or None): the BN input + the node when `t` is a BN output that is not materialised."""
+        p = t.producer
+        if p is not None and p.op == "bn_act" and getattr(p, "virtual", False):
+            return p.inputs[0].buf, p
+        return t.buf, None
+
+    def _bnin_args(self, bn):
+        v = bn.vars
+        return (self._wptr(v["gamma"]), self._wptr(v["beta"]), bn.saved[0].data_ptr(), bn.saved[1].data_ptr(), bn.attrs["leak"])
+
+    def materialize(self, t):
+        """The values of tensor `t`: its buffer, or — for a BN output that only exists inside the consuming
+        convolutions' shared memory — what rn_bn_apply_act_fwd stores for it (verification / debugging only)."""
+        if t.buf is not None:
+            return t.buf
+        xb, bn = self._bn_operand(t)
+        if bn is None:
+            raise ValueError("tensor %s has no buffer" % t.name)
+        out = torch.empty_like(xb)
+        C_ = xb.shape[-1]
+        a = bn.attrs
+        check(lib.rn_bn_apply_act_fwd(ptr(xb), ptr(out), xb.numel() // C_, C_, self.rn_dt, *self._bnin_args(bn)[:4], 0, a["eps"],
+                                      a["leak"], torch.cuda.current_stream().cuda_stream), "rn_bn_apply_act_fwd")
+        return out
+
     def _build_forward(self):
         fwd = []
         g = self.g
@@ -277,6 +331,7 @@ class Executor:
                     fused_adds.add(id(a))
         self._fused_adds = fused_adds
         self._plan_epilogue_fusion()
+        self._plan_operand_fusion()
         for t in g.placeholders.values():
             src = getattr(t, "cast_from", None)
             if src is not None:
@@ -445,6 +500,30 @@ class Executor:
         d = self._desc(n)
         self._keep.append(d)
         kv = n.vars["kernel"]
+        xbuf, bn_in = self._bn_operand(x)
+        if bn_in is not None:
+            f = getattr(n, "fuse", None)
+            res_p = st_p = None
+            out_buf = y.buf
+            if f is not None:
+                rows = lib.rn_convtc_stat_rows(C.byref(d))
+                f["partials"] = torch.zeros(rows, d.Cout, 2, dtype=torch.float32, device=self.dev)
+                res_p = ptr(f["residual"].buf) if f["residual"] is not None else None
+                st_p = ptr(f["partials"])
+                out_buf = f["out"].buf
+            nrows = C.c_int32(0)
+            plan = C.c_void_p()
+            check(lib.rn_convtc_plan_create_bnin(C.byref(d), 0, ptr(xbuf), *self._bnin_args(bn_in), self._wptr(kv, "Wb"),
+                                                 ptr(out_buf), res_p, st_p, C.byref(nrows), None, 0, C.byref(plan)),
+                  "rn_convtc_plan_create_bnin")
+            self._plans.append(plan)
+            if f is not None:
+                f["nrows"] = nrows.value
+                if f["residual"] is not None:
+                    y.buf = None
+            fn = lambda s, p=plan: check(lib.rn_convtc_run(p, 0.0, s), "rn_convtc_run")   # noqa: E731
+            fn.plan = plan
+            return ("conv_fprop_tc:" + y.name, fn)
         if self._stem_s2d(n):
             st = self._stem_s2d_setup(n)
             sdt = RN_BF16 if x.buf.dtype == torch.bfloat16 else RN_F32
@@ -533,9 +612,12 @@ class Executor:
                 out.append(("bn_stats:" + a["scope"],
                             lambda s, args=(px, pa, pz, M, C_, self.rn_dt, a["eps"], a["decay"], int(a["unbiased"]), mean_p, rstd_p, mm, mv):
                             check(lib.rn_bn_stats_fwd(*args, ptr(self.scratch), self.scratch_bytes, s), "rn_bn_stats_fwd")))
-            out.append(("bn_apply:" + a["scope"],
-                        lambda s, args=(ptr(x.buf), ptr(y.buf), M, C_, self.rn_dt, self._wptr(v["gamma"]), self._wptr(v["beta"]), mean_p, rstd_p, 0, a["eps"], a["leak"]):
-                        check(lib.rn_bn_apply_act_fwd(*args, s), "rn_bn_apply_act_fwd")))
+            if getattr(n, "virtual", False):
+                y.buf = None         # normalised inside the consuming 1x1 convolutions' shared memory, never stored
+            else:
+                out.append(("bn_apply:" + a["scope"],
+                            lambda s, args=(ptr(x.buf), ptr(y.buf), M, C_, self.rn_dt, self._wptr(v["gamma"]), self._wptr(v["beta"]), mean_p, rstd_p, 0, a["eps"], a["leak"]):
+                            check(lib.rn_bn_apply_act_fwd(*args, s), "rn_bn_apply_act_fwd")))
         else:
             out.append(("bn_infer:" + a["scope"],
                         lambda s, args=(ptr(x.buf), ptr(y.buf), M, C_, self.rn_dt, self._wptr(v["gamma"]), self._wptr(v["beta"]),
@@ -547,8 +629,11 @@ class Executor:
     def _slot_of(self, t):
         return getattr(t, "gradslot", None)
 
+    def _tdtype(self, t):
+        return self.adt if t.dtype == G.ACT else torch.float32
+
     def _new_slot(self, t):
-        s = _Slot(torch.zeros(t.shape, dtype=t.buf.dtype, device=self.dev))
+        s = _Slot(torch.zeros(t.shape, dtype=self._tdtype(t), device=self.dev))
         s.members.append(t)
         t.gradslot = s
         return s
@@ -566,7 +651,7 @@ class Executor:
             return s.buf, 0.0
         if not self._safe_inplace(t, s, done):
             # another reader of the shared buffer has not run yet: give t a private copy
-            ns = _Slot(torch.zeros(t.shape, dtype=t.buf.dtype, device=self.dev))
+            ns = _Slot(torch.zeros(t.shape, dtype=self._tdtype(t), device=self.dev))
             ns.members.append(t)
             ns.written = True
             dt = RN_BF16 if ns.buf.dtype == torch.bfloat16 else RN_F32
@@ -756,6 +841,19 @@ class Executor:
                 cp = (lambda s, a=ptr(tmp), b=self._wptr(kv, "G"), k=st["rows"] * d.Cout:
                       check(lib.rn_cast(a, b, k, RN_F32, RN_F32, s), "rn_cast"))
                 self._emit(bwd, "conv_wgrad_tc:" + y.name, lambda s, run=run, cp=cp: (run(s), cp(s)), node=n, dy=dy)
+            elif self._bn_operand(x)[1] is not None:
+                xbuf, bn_in = self._bn_operand(x)
+                nbytes = lib.rn_convtc_scratch_bytes(C.byref(d), 2)
+                scratch = torch.zeros(max(nbytes, 16), dtype=torch.uint8, device=self.dev)
+                self._keep.append(scratch)
+                plan = C.c_void_p()
+                check(lib.rn_convtc_plan_create_bnin(C.byref(d), 2, ptr(xbuf), *self._bnin_args(bn_in), ptr(dy),
+                                                     self._wptr(kv, "G"), None, None, None, ptr(scratch), nbytes,
+                                                     C.byref(plan)), "rn_convtc_plan_create_bnin")
+                self._plans.append(plan)
+                run = lambda s, p=plan: check(lib.rn_convtc_run(p, 0.0, s), "rn_convtc_run")   # noqa: E731
+                run.plan = plan
+                self._emit(bwd, "conv_wgrad_tc:" + y.name, run, node=n, dy=dy)
             elif self._conv_impl(n, 2) == "tc":
                 run = self._tc_plan(n, d, 2, x.buf, self._wptr(kv, "G"), b_buf=dy)
                 self._emit(bwd, "conv_wgrad_tc:" + y.name, run, node=n, dy=dy)

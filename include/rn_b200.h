@@ -112,6 +112,20 @@ int rn_convtc_plan_create_fused_dgrad(const rn_conv_desc* d, const void* dy, con
                                       const void* bn_x, const float* gamma, const float* beta, const float* mean,
                                       const float* rstd, float leak, float* sum_partials, int32_t* rows,
                                       rn_convtc_plan** plan);
+/* 1x1 convolutions (any stride, Cin a multiple of 64) whose input is the output of a training-mode
+ * batch_norm_relu (resnet_model_official.py:41-50 followed by conv2d_fixed_padding :80-91 — conv1 / conv3 of a
+ * bottleneck block and the projection shortcut): the plan reads the BN's INPUT `bn_x` and applies
+ * act(gamma * (x - mean) * rstd + beta), rounded to bf16 exactly as rn_bn_apply_act_fwd stores it, to every operand
+ * tile in shared memory before the tensor cores read it.  The normalised tensor is never written to or read from
+ * HBM: the rn_bn_apply_act_fwd pass of that BN disappears.  kind 0 (fprop; b = bf16 HWIO weights; optional fused
+ * residual / statistics epilogue as rn_convtc_plan_create_fused) or kind 2 (wgrad; b = dy, scratch as
+ * rn_convtc_plan_create).  mean / rstd are read at RUN time (they are produced by the BN's statistics kernel
+ * earlier in the same stream). */
+int rn_convtc_bnin_supported(const rn_conv_desc* d, int kind);
+int rn_convtc_plan_create_bnin(const rn_conv_desc* d, int kind, const void* bn_x, const float* gamma, const float* beta,
+                               const float* mean, const float* rstd, float leak, const void* b, void* out,
+                               const void* residual, float* stat_partials, int32_t* stat_rows, void* scratch,
+                               size_t scratch_bytes, rn_convtc_plan** plan);
 int rn_convtc_run(rn_convtc_plan* plan, float beta, void* stream);
 int rn_convtc_plan_destroy(rn_convtc_plan* plan);
 /* One line of text describing how a plan will run (tile shape, pipeline depth, CTA pairs, fusions): for logs and tests. */

@@ -480,3 +480,100 @@ def test_convtc_fused_dgrad_bn_backward_sums(case, leak):
     assert (DB.cpu().double() - sb_ref).abs().max().item() / scale_b < 1e-5
     assert (DG.cpu().double() - sg_ref).abs().max().item() / scale_g < 1e-5
     assert (DB - DB0).abs().max().item() / scale_b < 1e-5 and (DG - DG0).abs().max().item() / scale_g < 1e-5
+
+
+BNIN_CASES = [
+    # N, H, W, Cin, Cout, stride, fused residual?, fused stats?
+    (4, 16, 16, 64, 64, 1, False, False),
+    (4, 28, 28, 256, 64, 1, False, True),        # conv1 of a bottleneck block (statistics of the next BN fused)
+    (4, 28, 28, 64, 256, 1, True, True),         # conv3: shortcut add + statistics
+    (2, 56, 56, 256, 512, 2, False, False),      # projection shortcut, stride 2 (parity view)
+    (3, 9, 11, 128, 192, 1, False, False),       # ragged pixel tiles, N = 192
+    (6, 7, 7, 2048, 512, 1, False, True),        # deepest reduction: 32 k-chunks, 16 KB constants table
+    (5, 14, 14, 1024, 256, 1, False, True),
+]
+
+
+@pytest.mark.parametrize("leak", [0.0, 0.1])
+@pytest.mark.parametrize("case", BNIN_CASES)
+def test_convtc_bn_operand_transform(case, leak, monkeypatch):
+    """1x1 convolutions that read the INPUT of a training-mode BN+ReLU and normalise it in shared memory
+    (rn_convtc_plan_create_bnin): fprop (+ fused epilogues) and wgrad must be BIT-IDENTICAL to
+    rn_bn_apply_act_fwd followed by the ordinary plans — same operand values, same GEMM — and match the oracle."""
+    monkeypatch.setenv("RN_TC_PAIR", "0")        # same tiling (hence the same per-CTA statistics rows) in both pipelines
+    N, H, W, Cin, Cout, s, use_res, use_stats = case
+    Ho, Wo = (H - 1) // s + 1, (W - 1) // s + 1
+    g = torch.Generator().manual_seed(sum(case[:6]) + 5)
+    x = (torch.randn(N, H, W, Cin, generator=g) * 1.5 + 0.3).to(BF)
+    w = (torch.randn(1, 1, Cin, Cout, generator=g) / Cin ** 0.5).to(BF)
+    dy = torch.randn(N, Ho, Wo, Cout, generator=g).to(BF)
+    res = torch.randn(N, Ho, Wo, Cout, generator=g).to(BF)
+    gamma = (1.0 + 0.1 * torch.randn(Cin, generator=g)).float()
+    beta = (0.1 * torch.randn(Cin, generator=g)).float()
+    M = N * H * W
+    x2 = x.double().reshape(M, Cin)
+    mean = x2.mean(0).float()
+    rstd = (1.0 / torch.sqrt(x2.var(0, unbiased=False) + 1e-5)).float()
+    X, WB, DY, R = dev(x), dev(w), dev(dy), dev(res)
+    G_, B_, MU, RS = dev(gamma), dev(beta), dev(mean), dev(rstd)
+    d = ConvDesc(N, H, W, Cin, Ho, Wo, Cout, 1, s, 0, RN_BF16)
+    assert lib.rn_convtc_bnin_supported(C.byref(d), 0) == 1 and lib.rn_convtc_bnin_supported(C.byref(d), 2) == 1
+    # reference pipeline: bn_apply -> materialised activations -> ordinary plans
+    Yact = torch.empty(N, H, W, Cin, dtype=BF, device="cuda")
+    check(lib.rn_bn_apply_act_fwd(ptr(X), ptr(Yact), M, Cin, RN_BF16, ptr(G_), ptr(B_), ptr(MU), ptr(RS), 0, 1e-5, leak, stream()), "apply")
+    Z0 = torch.full((N, Ho, Wo, Cout), float("nan"), dtype=BF, device="cuda")
+    P0 = torch.zeros(lib.rn_convtc_stat_rows(C.byref(d)), Cout, 2, device="cuda")
+    plan = C.c_void_p()
+    nr0 = C.c_int32(0)
+    if use_res or use_stats:
+        check(lib.rn_convtc_plan_create_fused(C.byref(d), ptr(Yact), ptr(WB), ptr(Z0), ptr(R) if use_res else None,
+                                              ptr(P0) if use_stats else None, C.byref(nr0), C.byref(plan)), "plan")
+    else:
+        check(lib.rn_convtc_plan_create(C.byref(d), 0, ptr(Yact), ptr(WB), ptr(Z0), None, 0, C.byref(plan)), "plan")
+    check(lib.rn_convtc_run(plan, 0.0, stream()), "run")
+    lib.rn_convtc_plan_destroy(plan)
+    nb = lib.rn_convtc_scratch_bytes(C.byref(d), 2)
+    sc = torch.zeros(max(nb, 16), dtype=torch.uint8, device="cuda")
+    DW0 = torch.full((1, 1, Cin, Cout), float("nan"), device="cuda")
+    check(lib.rn_convtc_plan_create(C.byref(d), 2, ptr(Yact), ptr(DY), ptr(DW0), ptr(sc), nb, C.byref(plan)), "wplan")
+    check(lib.rn_convtc_run(plan, 0.0, stream()), "wrun")
+    lib.rn_convtc_plan_destroy(plan)
+    # operand-transform plans on the BN input itself
+    Z = torch.full((N, Ho, Wo, Cout), float("nan"), dtype=BF, device="cuda")
+    P1 = torch.zeros_like(P0)
+    nr1 = C.c_int32(0)
+    check(lib.rn_convtc_plan_create_bnin(C.byref(d), 0, ptr(X), ptr(G_), ptr(B_), ptr(MU), ptr(RS), leak, ptr(WB), ptr(Z),
+                                         ptr(R) if use_res else None, ptr(P1) if use_stats else None, C.byref(nr1), None, 0,
+                                         C.byref(plan)), "bnin fprop")
+    from distributed_tensorflow_resnet_b200._lib import describe_plan
+    assert "bn_operand=1" in describe_plan(plan) and "pair=0" in describe_plan(plan)
+    for _ in range(2):
+        check(lib.rn_convtc_run(plan, 0.0, stream()), "run bnin")
+    lib.rn_convtc_plan_destroy(plan)
+    DW = torch.full((1, 1, Cin, Cout), float("nan"), device="cuda")
+    sc2 = torch.zeros_like(sc)
+    check(lib.rn_convtc_plan_create_bnin(C.byref(d), 2, ptr(X), ptr(G_), ptr(B_), ptr(MU), ptr(RS), leak, ptr(DY), ptr(DW), None, None,
+                                         None, ptr(sc2), nb, C.byref(plan)), "bnin wgrad")
+    assert "bn_operand=1" in describe_plan(plan)
+    for _ in range(2):
+        check(lib.rn_convtc_run(plan, 0.0, stream()), "wrun bnin")
+    lib.rn_convtc_plan_destroy(plan)
+    torch.cuda.synchronize()
+    assert torch.equal(X.cpu(), x)                                   # the BN input in HBM is untouched
+    assert torch.isfinite(Z.float()).all() and torch.equal(Z, Z0)
+    assert torch.isfinite(DW).all() and torch.equal(DW, DW0)
+    if use_stats:
+        assert nr1.value == nr0.value and torch.equal(P1[:nr1.value], P0[:nr0.value])
+    # and against the oracle (fp64 BN + activation rounded to bf16 where the kernel rounds, conv, add)
+    pre = (x2 - mean.double()) * rstd.double() * gamma.double() + beta.double()
+    act = torch.where(pre < 0, leak * pre, pre).to(BF).double().reshape(N, H, W, Cin)
+    net = ro.Net(dtype=torch.float64, params={"w": w.double().numpy()})
+    av = ro.Var(act)
+    yv = net.conv2d(av, "w", 1, Cin, Cout, s, 0, (Ho, Wo), None, "y")
+    yv.grad = dy.double()
+    net.backward()
+    assert rel_err(Z.float(), yv.val + (res.double() if use_res else 0.0)) < 2e-2
+    assert rel_err(DW, net.param_grads["w"]) < 2e-3
+    # an unsupported request is refused, not mis-computed
+    d3 = ConvDesc(N, H, W, Cin, H, W, Cout, 3, 1, 1, RN_BF16)
+    assert lib.rn_convtc_bnin_supported(C.byref(d3), 0) == 0

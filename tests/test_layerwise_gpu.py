@@ -59,7 +59,9 @@ class Verifier:
             x, y = node.inputs[0], node.outputs[0]
             a = node.attrs
             net._given = {"w": self.weight(node).numpy()}
-            out = net.conv2d(_var(x.buf), "w", a["k"], x.shape[3], y.shape[3], a["stride"], a["pad"], y.shape[1:3], None, "y")
+            # (a BN output that exists only inside the consuming 1x1 convolutions is re-created with rn_bn_apply_act_fwd:
+            #  the check is then "conv with the on-the-fly normalisation == bn_apply followed by the oracle's conv")
+            out = net.conv2d(_var(ex.materialize(x)), "w", a["k"], x.shape[3], y.shape[3], a["stride"], a["pad"], y.shape[1:3], None, "y")
             f = getattr(node, "fuse", None)
             if f is None:
                 self.check(name, y.buf, out.val)
@@ -88,7 +90,7 @@ class Verifier:
                     rstd = 1 / torch.sqrt(_d(ex.var_view(v["moving_variance"].name)) + a["eps"])
                 pre = (x2 - mean) * rstd * g + b
                 want = torch.where(pre < 0, a["leak"] * pre, pre).reshape(x.shape)
-                self.check(name, y.buf, want)
+                self.check(name, ex.materialize(y), want)
         elif node.op == "add":
             self.check(name, node.outputs[0].buf, _d(node.inputs[0].buf) + _d(node.inputs[1].buf))
         elif node.op == "maxpool":
@@ -137,7 +139,7 @@ class Verifier:
             x, y = node.inputs[0], node.outputs[0]
             a = node.attrs
             net._given = {"w": self.weight(node).numpy()}
-            xv = _var(x.buf)
+            xv = _var(ex.materialize(x))
             out = net.conv2d(xv, "w", a["k"], x.shape[3], y.shape[3], a["stride"], a["pad"], y.shape[1:3], None, "y")
             out.grad = dy.reshape(y.shape)
             net.backward()
@@ -252,6 +254,30 @@ def test_every_launch_against_oracle(net, mode):
     assert v.count > 50
     print("\n%s %s: %d checks; worst per family: %s" % (name, mode, v.count,
           ", ".join("%s %.1e" % kv for kv in sorted(v.worst.items()))))
+
+
+def test_bn_operand_fusion_is_used_and_bit_identical(monkeypatch):
+    """ResNet-50 (bottleneck) with RN_BN_OPERAND_FUSION=1 (opt-in): the BN outputs read only by 1x1 convolutions are
+    not materialised (32 of the 49 bn_apply launches disappear), and training steps give BIT-IDENTICAL weights,
+    gradients and BN statistics to the default pipeline, which stores every BN output."""
+    res = []
+    monkeypatch.setenv("RN_TC_PAIR", "0")        # identical tilings, so the per-CTA statistics rows add up in the same order
+    for off in (False, True):
+        if off:
+            monkeypatch.delenv("RN_BN_OPERAND_FUSION")
+        else:
+            monkeypatch.setenv("RN_BN_OPERAND_FUSION", "1")
+        m = _build("c3", "bf16", (4, 96, 96, 3), 100, dict(dataset="imagenet", resnet_size=50))
+        ex = m.executor
+        napply = sum(1 for nm, _ in ex.fwd if nm.startswith("bn_apply"))
+        nvirtual = sum(1 for n in m.graph.nodes if n.op == "bn_act" and getattr(n, "virtual", False))
+        for _ in range(2):
+            m.train_op()
+        torch.cuda.synchronize()
+        res.append((napply, nvirtual, ex.W.clone(), ex.Gd.clone(), ex.S.clone(), ex.scalars()))
+    (a0, v0, W0, G0, S0, sc0), (a1, v1, W1, G1, S1, sc1) = res
+    assert v1 == 0 and a1 == 49 and v0 == 32 and a0 == 49 - 32
+    assert torch.equal(W0, W1) and torch.equal(G0, G1) and torch.equal(S0, S1) and sc0 == sc1
 
 
 def test_imagenet_resnet50_full_resolution_layers():
