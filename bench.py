@@ -110,6 +110,72 @@ def conv_flops(graph):
     return out
 
 
+def conv_layerwise_roofline(ex, graph, per_launch_ms, pk):
+    """Every convolution launch against ITS OWN bound: max(FLOPs / measured bf16 peak, algorithmic bytes / measured copy
+    bandwidth) — most 1x1 layers of ResNet-50 are HBM-bound, so a tensor-only roofline understates them.  Bytes: the
+    activation tensors the launch must read and write once (+ the shortcut of a fused add, + the BN input a fused
+    dgrad re-reads); weights and split-K partials are not counted."""
+    s = 2 if ex.bf16 else 4
+    plans = ex.describe_plans()
+    tot = {}
+    for n in graph.nodes:
+        if n.op != "conv2d":
+            continue
+        x, y = n.inputs[0], n.outputs[0]
+        fl = 2.0 * y.numel * n.attrs["k"] ** 2 * x.shape[3]
+        xin = x.numel * s if x.shape[3] >= 16 else y.numel // y.shape[3] * 16 * s      # stem: the packed 16-channel view
+        for fam in ("conv_fprop_tc", "conv_dgrad_tc", "conv_wgrad_tc", "conv_fprop", "conv_dgrad", "conv_wgrad"):
+            ms = per_launch_ms.get(fam + ":" + y.name)
+            if ms is None:
+                continue
+            by = xin + y.numel * s
+            f = getattr(n, "fuse", None)
+            if "fprop" in fam and f is not None and f["residual"] is not None:
+                by += y.numel * s
+            if "dgrad" in fam and "fused=001" in plans.get(fam + ":" + y.name, ""):
+                by += x.numel * s
+            ideal = max(fl / (pk["tf_burst"] * 1e9), by / (pk["hbm"] * 1e6))           # ms
+            base = fam.replace("_tc", "")
+            t = tot.setdefault(base, [0.0, 0.0, 0, 0])
+            t[0] += ideal
+            t[1] += ms
+            t[2] += 1
+            t[3] += 1 if fl / (pk["tf_burst"] * 1e9) > by / (pk["hbm"] * 1e6) else 0
+    out = {k: {"ideal_ms": round(v[0], 3), "measured_ms": round(v[1], 3), "frac": round(v[0] / v[1], 3), "launches": v[2],
+               "tensor_bound_launches": v[3]} for k, v in tot.items()}
+    i, m = sum(v[0] for v in tot.values()), sum(v[1] for v in tot.values())
+    out["all"] = {"ideal_ms": round(i, 3), "measured_ms": round(m, 3), "frac": round(i / m, 3) if m else None}
+    return out
+
+
+def decode_throughput(pipe, pk):
+    """The CIFAR decode kernel on the whole record file in ONE launch (50,000 images): algorithmic bytes (record read +
+    image + one-hot written) over the CUDA-event time, against the measured copy bandwidth."""
+    import torch
+    from distributed_tensorflow_resnet_b200._lib import lib, check, ptr, RN_BF16, RN_F32
+    if not pipe.resident:
+        return None
+    n = pipe.n
+    img = torch.empty(n, 32, 32, 3, dtype=pipe.images.dtype, device=pipe.images.device)
+    oh = torch.empty(n, pipe.classes, dtype=torch.float32, device=img.device)
+    odt = RN_BF16 if img.dtype == torch.bfloat16 else RN_F32
+    st = torch.cuda.current_stream()
+    best = None
+    for i in range(4):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(st)
+        check(lib.rn_cifar_decode(ptr(pipe.records), n, pipe.record_bytes, pipe.label_offset, pipe.classes, None, n, 1, pipe.pad,
+                                  pipe.seed & 0xFFFFFFFF, 0, i, None, 0, ptr(img), odt, ptr(oh), None, None, st.cuda_stream),
+              "rn_cifar_decode")
+        e1.record(st)
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1)
+        best = ms if best is None or ms < best else best
+    by = n * (pipe.record_bytes + 3072 * img.element_size() + 4 * pipe.classes)
+    return {"images": n, "ms": round(best, 4), "bytes": by, "gbs": round(by / best / 1e6, 1),
+            "frac_of_hbm_peak": round(by / best / 1e6 / pk["hbm"], 4), "images_per_s": round(n / best * 1e3)}
+
+
 def family(name):
     return name.split(":")[0]
 
@@ -594,7 +660,10 @@ def run_ours(args):
             "sustained": sustained,
             "conv": {"tflops_all_conv_kernels": round(conv_fl / conv_ms / 1e9, 2) if conv_ms else None,
                      "frac_of_sustained_peak": round(conv_fl / conv_ms / 1e9 / pk["tf_sust"], 4) if conv_ms else None,
-                     "gflop_per_step": round(conv_fl / 1e9, 2)},
+                     "frac_of_burst_peak": round(conv_fl / conv_ms / 1e9 / pk["tf_burst"], 4) if conv_ms else None,
+                     "gflop_per_step": round(conv_fl / 1e9, 2),
+                     "layerwise_roofline": conv_layerwise_roofline(ex, model.graph, per_launch, pk)},
+            "cifar_decode": decode_throughput(pipe, pk) if cifar else None,
             "kernels": table,
             "profiled_step_ms": round(prof_total, 3),
             "cpu_baseline": cpu,
