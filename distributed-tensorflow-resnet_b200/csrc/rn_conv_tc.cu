@@ -344,12 +344,13 @@ conv_tc_kernel(const __grid_constant__ TcConvParams p) {
     int csb = 0, pend_col = -1;                     // fused statistics: cs buffer in use, column base awaiting its combine
     const int groups = p.block_n / p.gw;
     // Fused statistics, second half: add the eight partial sums of the PREVIOUS store group (cs[csb ^ 1], written
-    // before this group's first barrier) into the CTA's running per-channel totals.  Thread te < 128 owns
-    // (column te & 63, statistic te >> 6); fixed order.
+    // before this group's first barrier) into the CTA's running per-channel totals.  Thread te < 2 * gw owns
+    // (column te % gw, statistic te / gw); fixed order.
+    const int gw_lg = p.gw == 64 ? 6 : (p.gw == 32 ? 5 : 4);            // store groups are 16, 32 or 64 channels wide
     auto combine = [&](int col0, int which) {
-      if (te >= 128) return;
+      if (te >= 2 * p.gw) return;
       const float* c = cs + which * 1024;
-      const int col = te & 63, st = te >> 6;
+      const int col = te & (p.gw - 1), st = te >> gw_lg;
       float v = 0.f;
 #pragma unroll
       for (int q = 0; q < TC_EPI_WARPS; ++q) v += c[(q * 32 + (col >> 1)) * 4 + st * 2 + (col & 1)];
@@ -427,21 +428,43 @@ conv_tc_kernel(const __grid_constant__ TcConvParams p) {
               if (lane == 0) mbar_arrive(&rempty[rslot]);
               if (++rslot == p.res_slots) { rslot = 0; rphase ^= 1; }
             }
-          } else if (half == 0) {
-            for (int c0 = 0; c0 < p.gw; c0 += 16) {
-              uint32_t v[16];
-              tmem_ld_32x16(taddr + c0, v);
-              tmem_ld_wait();
-              uint32_t pk[8];
+          } else {
+            // narrow store groups (16 / 32 channels): one warp per quadrant converts whole rows, 16 columns at a time
+            if (fuse_stats && pend_col >= 0) combine(pend_col, csb ^ 1);
+            const uint8_t* rb = res_buf + rslot * 16384;
+            if (half == 0) {
+              if (fuse_add) mbar_wait(&rfull[rslot], rphase);
+              for (int c0 = 0; c0 < p.gw; c0 += 16) {
+                uint32_t v[16];
+                tmem_ld_32x16(taddr + c0, v);
+                tmem_ld_wait();
+                uint32_t pk[8];
 #pragma unroll
-              for (int i = 0; i < 8; ++i) {
-                __nv_bfloat162 h = __floats2bfloat162_rn(__uint_as_float(v[2 * i]), __uint_as_float(v[2 * i + 1]));
-                pk[i] = *reinterpret_cast<uint32_t*>(&h);
+                for (int i = 0; i < 8; ++i) {
+                  __nv_bfloat162 h = __floats2bfloat162_rn(__uint_as_float(v[2 * i]), __uint_as_float(v[2 * i + 1]));
+                  pk[i] = *reinterpret_cast<uint32_t*>(&h);
+                }
+                // 16 channels = two 16-byte chunks of this row, XOR-swizzled like the TMA store expects
+                const uint32_t off0 = (uint32_t)row * row_bytes_out + (uint32_t)c0 * 2;
+                const uint32_t so0 = swizzle_offset(off0, row_bytes_out), so1 = swizzle_offset(off0 + 16, row_bytes_out);
+                if (fuse_add) {                     // z = bf16(bf16(conv) + residual), as in the 64-channel path
+                  const uint4 r0 = *reinterpret_cast<const uint4*>(rb + so0), r1 = *reinterpret_cast<const uint4*>(rb + so1);
+                  const uint32_t rw[8] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
+#pragma unroll
+                  for (int i = 0; i < 8; ++i) {
+                    const __nv_bfloat162 h = __hadd2(*reinterpret_cast<const __nv_bfloat162*>(&pk[i]),
+                                                     *reinterpret_cast<const __nv_bfloat162*>(&rw[i]));
+                    pk[i] = *reinterpret_cast<const uint32_t*>(&h);
+                  }
+                }
+                *reinterpret_cast<uint4*>(sb + so0) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+                *reinterpret_cast<uint4*>(sb + so1) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
               }
-              // 16 channels = two 16-byte chunks of this row, XOR-swizzled like the TMA store expects
-              const uint32_t off0 = (uint32_t)row * row_bytes_out + (uint32_t)c0 * 2;
-              *reinterpret_cast<uint4*>(sb + swizzle_offset(off0, row_bytes_out)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-              *reinterpret_cast<uint4*>(sb + swizzle_offset(off0 + 16, row_bytes_out)) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+            }
+            if (fuse_add) {                         // every epilogue warp releases the ring slot (the barrier counts all eight)
+              __syncwarp();
+              if (lane == 0) mbar_arrive(&rempty[rslot]);
+              if (++rslot == p.res_slots) { rslot = 0; rphase ^= 1; }
             }
           }
           fence_proxy_async();
@@ -518,6 +541,56 @@ conv_tc_kernel(const __grid_constant__ TcConvParams p) {
             *reinterpret_cast<float4*>(cs + csb * 1024 + (ew * 32 + lane) * 4) = make_float4(s0, s1, q0, q1);
             pend_col = nt * p.block_n + g * 64;
             csb ^= 1;
+          } else if (fuse_stats) {
+            // Narrow store groups (16 / 32 channels: the CIFAR widths).  A row of the staged group is 32 / 64 bytes, so a
+            // warp's 32 lanes cover gw/2 channel pairs x (64/gw) rows at a time: lane = (row lane, channel pair); each
+            // warp sums 16 rows of its quadrant, the row lanes are folded with shuffles, lanes < gw/2 publish the sums.
+            const int npairs = p.gw >> 1, rl = 32 / npairs;
+            const int cp = lane % npairs, ro = lane / npairs;
+            const uint32_t hmask = (row_mask >> (half * 16)) & 0xffffu;
+            const uint32_t rowB = (uint32_t)row_bytes_out;
+            float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
+            if (fuse_bnbwd) {
+              mbar_wait(&rfull[rslot], rphase);
+              const uint8_t* rb = res_buf + rslot * 16384;
+              const int cpair = nt * p.block_n + g * p.gw + 2 * cp;
+              const float4 k0 = *reinterpret_cast<const float4*>(ctab + 4 * cpair);
+              const float4 k1 = *reinterpret_cast<const float4*>(ctab + 4 * cpair + 4);
+              for (int rr = ro; rr < 16; rr += rl) {
+                const uint32_t so = swizzle_offset((uint32_t)(quad * 32 + half * 16 + rr) * rowB + (uint32_t)cp * 4u, row_bytes_out);
+                uint32_t wg = *reinterpret_cast<const uint32_t*>(sb + so);
+                uint32_t wx = *reinterpret_cast<const uint32_t*>(rb + so);
+                wg = ((hmask >> rr) & 1u) ? wg : 0u;
+                wx = ((hmask >> rr) & 1u) ? wx : 0u;
+                const float g0 = __uint_as_float(wg << 16), g1 = __uint_as_float(wg & 0xffff0000u);
+                const float x0 = __uint_as_float(wx << 16), x1 = __uint_as_float(wx & 0xffff0000u);
+                const float m0 = fmaf(x0, k0.x, k0.y) < 0.f ? p.bn_leak * g0 : g0;
+                const float m1 = fmaf(x1, k1.x, k1.y) < 0.f ? p.bn_leak * g1 : g1;
+                s0 += m0; s1 += m1;
+                q0 = fmaf(m0, (x0 - k0.z) * k0.w, q0);
+                q1 = fmaf(m1, (x1 - k1.z) * k1.w, q1);
+              }
+              __syncwarp();
+              if (lane == 0) mbar_arrive(&rempty[rslot]);
+              if (++rslot == p.res_slots) { rslot = 0; rphase ^= 1; }
+            } else {
+              for (int rr = ro; rr < 16; rr += rl) {
+                uint32_t w = *reinterpret_cast<const uint32_t*>(
+                    sb + swizzle_offset((uint32_t)(quad * 32 + half * 16 + rr) * rowB + (uint32_t)cp * 4u, row_bytes_out));
+                w = ((hmask >> rr) & 1u) ? w : 0u;
+                const float f0 = __uint_as_float(w << 16), f1 = __uint_as_float(w & 0xffff0000u);
+                s0 += f0; s1 += f1;
+                q0 = fmaf(f0, f0, q0); q1 = fmaf(f1, f1, q1);
+              }
+            }
+            for (int o = npairs; o < 32; o <<= 1) {               // fold the row lanes (fixed order)
+              s0 += __shfl_xor_sync(0xffffffffu, s0, o); s1 += __shfl_xor_sync(0xffffffffu, s1, o);
+              q0 += __shfl_xor_sync(0xffffffffu, q0, o); q1 += __shfl_xor_sync(0xffffffffu, q1, o);
+            }
+            if (lane < npairs)
+              *reinterpret_cast<float4*>(cs + csb * 1024 + (ew * 32 + cp) * 4) = make_float4(s0, s1, q0, q1);
+            pend_col = nt * p.block_n + g * p.gw;
+            csb ^= 1;
           }
           buf ^= 1;
         }
@@ -587,8 +660,8 @@ conv_tc_kernel(const __grid_constant__ TcConvParams p) {
     }
   } else {
     // ===================== residual-tile producer (warp 10; only launched with the fused add) =====================
-    const uint32_t rtx = (uint32_t)(p.BW * p.BH * p.BN) * 128u;
-    const int groups = p.block_n / 64;
+    const uint32_t rtx = (uint32_t)(p.BW * p.BH * p.BN) * (uint32_t)(p.gw * 2);
+    const int groups = p.block_n / p.gw;
     int rslot = 0;
     uint32_t rphase = 0;
     for (int t = wstart; t < total; t += wstep) {
@@ -606,7 +679,7 @@ conv_tc_kernel(const __grid_constant__ TcConvParams p) {
           mbar_wait(&rempty[rslot], rphase ^ 1);
           if (elect_one()) {
             mbar_expect_tx(&rfull[rslot], rtx);
-            tma_load_4d(res_buf + rslot * 16384, &p.r_map, &rfull[rslot], nt * p.block_n + g * 64, w0, h0, n0);
+            tma_load_4d(res_buf + rslot * 16384, &p.r_map, &rfull[rslot], nt * p.block_n + g * p.gw, w0, h0, n0);
           }
           __syncwarp();
           if (++rslot == p.res_slots) { rslot = 0; rphase ^= 1; }
@@ -1441,8 +1514,6 @@ static int create_sub(const rn_conv_desc* d, int kind, const void* a, const void
   const long m_tiles = (long)p.tiles_w * p.tiles_h * p.tiles_n;
   // epilogue staging, barriers, alignment slack; fused epilogue: residual tile ring, statistics scratch
   const bool want_fused = residual != nullptr || stat_partials != nullptr;
-  if (want_fused && p.gw != 64)
-    return fail(RN_ERR_UNSUPPORTED, "convtc: the fused epilogue needs output channels in multiples of 64");
   if (bnbwd ? (kind != 1 || stat_partials == nullptr || residual != nullptr) : (want_fused && kind != 0))
     return fail(RN_ERR_UNSUPPORTED, "convtc: fused add / statistics belong to fprop, fused BN backward sums to dgrad");
   p.fuse_add = residual != nullptr;
@@ -1657,9 +1728,9 @@ extern "C" int rn_convtc_plan_create(const rn_conv_desc* d, int kind, const void
 }
 
 extern "C" int rn_convtc_fused_supported(const rn_conv_desc* d) {
-  if (!rn_convtc_supported(d, 0)) return 0;
-  const int bn_ = choose_block_n(d->Cout);
-  return (bn_ % 64 == 0 && d->Cout <= 4096) ? 1 : 0;
+  // store groups of 64 channels (ImageNet widths) or 16 / 32 (CIFAR / WRN widths)
+  if (!rn_convtc_supported(d, 0) || d->Cin < 16) return 0;
+  return (choose_block_n(d->Cout) > 0 && d->Cout <= 4096) ? 1 : 0;
 }
 
 extern "C" int rn_convtc_stat_rows(const rn_conv_desc* d) {
@@ -1699,8 +1770,7 @@ extern "C" int rn_convtc_plan_create_fused(const rn_conv_desc* d, const void* x,
 
 extern "C" int rn_convtc_fused_dgrad_supported(const rn_conv_desc* d) {
   if (!rn_convtc_supported(d, 1) || d->stride != 1) return 0;
-  const int bn_ = choose_block_n(d->Cin);
-  return (bn_ % 64 == 0 && d->Cin <= 1024) ? 1 : 0;
+  return (choose_block_n(d->Cin) > 0 && d->Cin <= 1024) ? 1 : 0;
 }
 
 extern "C" int rn_convtc_plan_create_fused_dgrad(const rn_conv_desc* d, const void* dy, const void* w_bf16, void* dx,

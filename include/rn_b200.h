@@ -88,7 +88,7 @@ size_t rn_convtc_scratch_bytes(const rn_conv_desc* d, int kind);
 int rn_convtc_plan_create(const rn_conv_desc* d, int kind, const void* a, const void* b, void* out,
                           void* scratch, size_t scratch_bytes, rn_convtc_plan** plan);
 /* beta (dgrad only): 0 overwrite, 1 accumulate into `out`. */
-/* fprop with a fused epilogue (Cout a multiple of 64; beta must be 0 at run time):
+/* fprop with a fused epilogue (Cout a multiple of 16, store groups of 64 / 32 / 16 channels; beta must be 0 at run time):
  *   residual != NULL      : out = bf16(bf16(conv) + residual) — the bottleneck's `inputs + shortcut`
  *                           (resnet_model_official.py:130 / :175) without materialising the conv output;
  *                           residual has the shape and layout of out.
@@ -103,7 +103,7 @@ int rn_convtc_plan_create_fused(const rn_conv_desc* d, const void* x, const void
                                 const void* residual, float* stat_partials, int32_t* stat_rows,
                                 rn_convtc_plan** plan);
 /* dgrad whose output dx is the incoming gradient of a batch_norm_relu (resnet_model_official.py:41-50) that is
- * read by this convolution only (stride 1, Cin a multiple of 64, <= 1024; beta must be 0 at run time): the
+ * read by this convolution only (stride 1, Cin a multiple of 16, <= 1024; beta must be 0 at run time): the
  * epilogue also accumulates that BN's backward reductions — sum(g) and sum(g * xhat) with g = dx masked by the
  * ReLU, xhat from bn_x / mean / rstd — one row [Cin][2] per CTA in sum_partials (rn_convtc_stat_rows bounds the
  * rows); rn_bn_bwd_finalize turns them into dbeta / dgamma, replacing rn_bn_act_bwd_reduce's pass over dy and x. */

@@ -355,6 +355,12 @@ FUSED_CASES = [
     (2, 14, 14, 256, 256, 3, 1, 1, (14, 14), False, True),     # box 14x4x2: tile rows past the image bottom are non-zero for k = 3
     (2, 28, 28, 256, 256, 3, 2, 1, (14, 14), False, True),
     (3, 9, 11, 64, 64, 3, 1, 1, (9, 11), True, True),
+    (8, 32, 32, 16, 16, 3, 1, 1, (32, 32), False, True),       # CIFAR widths: 16-channel store groups (statistics only)
+    (8, 32, 32, 16, 16, 3, 1, 1, (32, 32), True, True),        # basic block's conv2 + shortcut + next BN's statistics
+    (8, 16, 16, 32, 32, 3, 1, 1, (16, 16), True, True),        # 32-channel store groups
+    (4, 32, 32, 160, 160, 3, 1, 1, (32, 32), True, True),      # WRN-28-10 width: N = 160 in five 32-channel groups
+    (8, 32, 32, 16, 32, 3, 2, 1, (16, 16), False, True),       # stage transition
+    (3, 9, 11, 32, 48, 3, 1, 1, (9, 11), False, True),         # N = 48: three 16-channel groups, ragged tiles
 ]
 
 
@@ -421,6 +427,9 @@ FUSED_DGRAD_CASES = [
     (4, 28, 28, 512, 128, 1, 0),       # dgrad of a bottleneck conv1: wide dx (two column tiles), short reduction
     (3, 9, 11, 64, 128, 1, 0),         # ragged
     (6, 7, 7, 1024, 256, 1, 0),        # four column tiles
+    (8, 32, 32, 16, 16, 3, 1),         # CIFAR widths: 16-channel store groups
+    (8, 16, 16, 32, 32, 3, 1),         # 32-channel store groups
+    (3, 9, 11, 48, 32, 3, 1),          # dx has 48 channels: three 16-channel groups, ragged tiles
 ]
 
 

@@ -62,7 +62,7 @@ def test_fusion_support_predicates_on_the_c3_shapes():
     assert lib.rn_convtc_fused_supported(B(desc(56, 64, 256, 1, 1))) == 1         # conv3 + shortcut + statistics
     assert lib.rn_convtc_fused_supported(B(desc(56, 64, 64, 3, 1))) == 1
     assert lib.rn_convtc_fused_supported(B(desc(28, 256, 128, 3, 2))) == 1
-    assert lib.rn_convtc_fused_supported(B(desc(32, 16, 16, 3, 1))) == 0           # CIFAR width: 16-channel store groups
+    assert lib.rn_convtc_fused_supported(B(desc(32, 16, 16, 3, 1))) == 1           # CIFAR width: 16-channel store groups
     assert lib.rn_convtc_fused_supported(B(desc(56, 64, 64, 3, 1, RN_F32))) == 0   # fp32 verification mode: no tensor cores
     assert lib.rn_convtc_fused_dgrad_supported(B(desc(56, 256, 64, 1, 1))) == 1    # dx = gradient of a 256-channel BN
     assert lib.rn_convtc_fused_dgrad_supported(B(desc(14, 1024, 256, 1, 1))) == 1
