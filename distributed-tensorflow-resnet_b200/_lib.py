@@ -22,7 +22,7 @@ class ConvDesc(C.Structure):
                 ("N", "H", "W", "Cin", "Ho", "Wo", "Cout", "k", "stride", "pad", "dtype")]
 
 
-ABI_VERSION = 4           # must equal RN_ABI_VERSION of include/rn_b200.h the .so was compiled from
+ABI_VERSION = 5           # must equal RN_ABI_VERSION of include/rn_b200.h the .so was compiled from
 
 
 def _load():
@@ -87,6 +87,10 @@ SIGNATURES = {
     "rn_convtc_plan_create_fused_dgrad": (C.c_int, [pdesc, vp, vp, vp, vp, vp, vp, vp, vp, f32, vp, C.POINTER(i32),
                                                     C.POINTER(vp)]),
     "rn_bn_bwd_finalize": (C.c_int, [vp, i32, i32, vp, vp, vp]),
+    "rn_bn_apply_act_fwd_partials": (C.c_int, [vp, vp, C.c_int64, i32, i32, vp, vp, vp, i32, f32, f32, i32, vp, vp, vp, vp, f32, vp]),
+    "rn_bn_act_bwd_apply_partials": (C.c_int, [vp, vp, vp, vp, C.c_int64, i32, i32, vp, vp, vp, vp, vp, i32, vp, vp, f32, vp]),
+    "rn_convtc_plan_fold_bn_finalize": (C.c_int, [vp, C.c_int64, f32, f32, i32, vp, vp, vp, vp, vp]),
+    "rn_convtc_plan_fold_bn_bwd_finalize": (C.c_int, [vp, vp, vp, vp]),
     "rn_convtc_bnin_supported": (C.c_int, [pdesc, C.c_int]),
     "rn_convtc_plan_create_bnin": (C.c_int, [pdesc, C.c_int, vp, vp, vp, vp, vp, f32, vp, vp, vp, vp, C.POINTER(i32), vp, sz,
                                              C.POINTER(vp)]),

@@ -295,25 +295,114 @@ bn_stats_kernel(const T* __restrict__ x, const T* __restrict__ addend, T* __rest
 }
 
 // ------------------------------------------------------------------------------------------
+// Consumer-side finalisation.  A convolution with a fused epilogue leaves a table partials[rows][C][2] of per-CTA
+// sums (rows <= 148).  Instead of one more tiny kernel between two big ones (measured: ~5 us of drain + launch + ramp
+// per BN on ResNet-50), every CTA of the apply kernel that follows sums the table for ITS <= 64 channels itself:
+// thread -> (channel pair, row slice), 16-byte loads, fp64, slices combined in slice order — the same fixed order in
+// every CTA, so all CTAs derive identical constants; the CTA with blockIdx.x == 0 of each channel chunk also writes
+// them out (mean / rstd / moving averages, or dgamma / dbeta) for the kernels that need them later.
+// ------------------------------------------------------------------------------------------
+struct BnFold {
+  const float* partials;
+  int rows;
+  double M;
+  float eps, decay;
+  int unbiased;
+  float *o0, *o1;      // forward: mean, rstd;  backward: dgamma, dbeta
+  float *mm, *mv;      // forward: moving mean / variance or NULL
+};
+constexpr int BN_FOLD_CW = 8;          // column groups per CTA of a folded apply kernel (64 bf16 channels: 32 pairs x 8 slices)
+constexpr int BN_FOLD_BATCH = 10;      // loads in flight per thread
+
+// All BN_THREADS threads call this.  Returns true for the threads that own a channel pair (slice 0): s = (S0, Q0, S1, Q1)
+// of channels c0 + 2 * pair, c0 + 2 * pair + 1.  sh: BN_THREADS * 4 doubles.
+__device__ __forceinline__ bool cta_sum_partial_rows(const float* __restrict__ partials, int rows, int C, int c0, int nch,
+                                                     double* sh, double (&s)[4], int* pair) {
+  const int np = nch >> 1;
+  const int S = BN_THREADS / np;
+  const int pr = threadIdx.x % np, slice = threadIdx.x / np;
+  s[0] = s[1] = s[2] = s[3] = 0.0;
+  if (slice < S) {
+    const float4* q = reinterpret_cast<const float4*>(partials + (size_t)2 * c0) + pr;
+    const size_t rstride = (size_t)C >> 1;                       // float4 per row
+    int z = slice;
+    for (; z + (BN_FOLD_BATCH - 1) * S < rows; z += BN_FOLD_BATCH * S) {
+      float4 v[BN_FOLD_BATCH];
+#pragma unroll
+      for (int u = 0; u < BN_FOLD_BATCH; ++u) v[u] = __ldcg(q + (size_t)(z + u * S) * rstride);
+#pragma unroll
+      for (int u = 0; u < BN_FOLD_BATCH; ++u) { s[0] += (double)v[u].x; s[1] += (double)v[u].y; s[2] += (double)v[u].z; s[3] += (double)v[u].w; }
+    }
+    float4 v[BN_FOLD_BATCH];
+#pragma unroll
+    for (int u = 0; u < BN_FOLD_BATCH; ++u) {
+      const int zz = z + u * S;
+      v[u] = zz < rows ? __ldcg(q + (size_t)zz * rstride) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+#pragma unroll
+    for (int u = 0; u < BN_FOLD_BATCH; ++u) { s[0] += (double)v[u].x; s[1] += (double)v[u].y; s[2] += (double)v[u].z; s[3] += (double)v[u].w; }
+  }
+  if (S > 1) {
+    double* mine = sh + 4 * threadIdx.x;
+    mine[0] = s[0]; mine[1] = s[1]; mine[2] = s[2]; mine[3] = s[3];
+    __syncthreads();
+    if (slice == 0)
+      for (int j = 1; j < S; ++j) {
+        const double* o = sh + 4 * (j * np + pr);
+        s[0] += o[0]; s[1] += o[1]; s[2] += o[2]; s[3] += o[3];
+      }
+  }
+  *pair = pr;
+  return slice == 0;
+}
+
+// ------------------------------------------------------------------------------------------
 // forward apply + activation
 // ------------------------------------------------------------------------------------------
-template <typename T>
+template <typename T, bool FOLD>
 __global__ void __launch_bounds__(BN_THREADS)
 bn_apply_kernel(const T* __restrict__ x, T* __restrict__ y, int64_t M, int C, BnLayout L,
                 const float* __restrict__ gamma, const float* __restrict__ beta, const float* __restrict__ mean,
-                const float* __restrict__ rstd, int stats_are_moving, float eps, float leak) {
+                const float* __restrict__ rstd, int stats_are_moving, float eps, float leak, BnFold fold) {
   constexpr int V = Vec<T>::N;
   pdl_trigger();
   pdl_wait();
   const int tx = threadIdx.x % L.CW, ty = threadIdx.x / L.CW;
   const int cg = blockIdx.y * L.CW + tx;
+  __shared__ double fold_sh[FOLD ? BN_THREADS * 4 : 1];
+  __shared__ float fold_ab[FOLD ? BN_FOLD_CW * V * 2 : 1];
+  if (FOLD) {
+    const int c0 = blockIdx.y * L.CW * V;
+    const int nch = min(L.CW * V, C - c0);
+    double s[4];
+    int pr;
+    if (cta_sum_partial_rows(fold.partials, fold.rows, C, c0, nch, fold_sh, s, &pr)) {
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const int c = c0 + 2 * pr + h;
+        const double mu = s[2 * h] / fold.M;
+        double var = s[2 * h + 1] / fold.M - mu * mu;
+        if (var < 0.0) var = 0.0;
+        const float mf = (float)mu, rf = (float)(1.0 / sqrt(var + (double)fold.eps));
+        if (blockIdx.x == 0)
+          bn_finalize_channel(s[2 * h], s[2 * h + 1], fold.M, fold.eps, fold.decay, fold.unbiased, c, fold.o0, fold.o1, fold.mm, fold.mv);
+        bn_affine(gamma[c], beta[c], mf, rf, &fold_ab[2 * (2 * pr + h)], &fold_ab[2 * (2 * pr + h) + 1]);
+      }
+    }
+    __syncthreads();
+  }
   if (!(ty < L.RY && cg < L.CV)) return;
   float a[V], b[V];
 #pragma unroll
   for (int i = 0; i < V; ++i) {
-    const int c = cg * V + i;
-    const float rs = stats_are_moving ? rsqrtf(rstd[c] + eps) : rstd[c];
-    bn_affine(gamma[c], beta[c], mean[c], rs, &a[i], &b[i]);
+    if (FOLD) {
+      a[i] = fold_ab[2 * (tx * V + i)];
+      b[i] = fold_ab[2 * (tx * V + i) + 1];
+    } else {
+      const int c = cg * V + i;
+      const float rs = stats_are_moving ? rsqrtf(rstd[c] + eps) : rstd[c];
+      bn_affine(gamma[c], beta[c], mean[c], rs, &a[i], &b[i]);
+    }
   }
   const int64_t stride = L.RY;
   const int64_t col = (int64_t)cg * V;
@@ -463,17 +552,35 @@ bn_bwd_reduce_kernel(const T* __restrict__ dy, const T* __restrict__ x, int64_t 
 // ------------------------------------------------------------------------------------------
 // backward: dx
 // ------------------------------------------------------------------------------------------
-template <typename T, bool ADD>
+template <typename T, bool ADD, bool FOLD>
 __global__ void __launch_bounds__(BN_THREADS)
 bn_bwd_apply_kernel(const T* __restrict__ dy, const T* __restrict__ x, T* dx, const T* dx_addend, int64_t M, int C,
                     BnLayout L, const float* __restrict__ gamma, const float* __restrict__ beta,
                     const float* __restrict__ mean, const float* __restrict__ rstd, const float* __restrict__ dgamma,
-                    const float* __restrict__ dbeta, float leak) {
+                    const float* __restrict__ dbeta, float leak, BnFold fold) {
   constexpr int V = Vec<T>::N;
   pdl_trigger();
   pdl_wait();
   const int tx = threadIdx.x % L.CW, ty = threadIdx.x / L.CW;
   const int cg = blockIdx.y * L.CW + tx;
+  __shared__ double fold_sh[FOLD ? BN_THREADS * 4 : 1];
+  __shared__ float fold_k[FOLD ? BN_FOLD_CW * V * 2 : 1];          // (dbeta, dgamma) per channel of the chunk
+  if (FOLD) {
+    const int c0 = blockIdx.y * L.CW * V;
+    const int nch = min(L.CW * V, C - c0);
+    double s[4];
+    int pr;
+    if (cta_sum_partial_rows(fold.partials, fold.rows, C, c0, nch, fold_sh, s, &pr)) {
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const int cl = 2 * pr + h;
+        const float db = (float)s[2 * h], dg = (float)s[2 * h + 1];   // (sum g, sum g * xhat), as bn_bwd_finalize_kernel stores them
+        fold_k[2 * cl] = db; fold_k[2 * cl + 1] = dg;
+        if (blockIdx.x == 0) { fold.o1[c0 + cl] = db; fold.o0[c0 + cl] = dg; }
+      }
+    }
+    __syncthreads();
+  }
   if (!(ty < L.RY && cg < L.CV)) return;
   float a[V], b[V], mu[V], rs[V], k1[V], k2[V];
   const float invM = 1.f / (float)M;
@@ -484,8 +591,8 @@ bn_bwd_apply_kernel(const T* __restrict__ dy, const T* __restrict__ x, T* dx, co
     mu[i] = mean[c];
     a[i] = gamma[c] * rs[i];
     b[i] = beta[c] - mu[i] * a[i];
-    k1[i] = dbeta[c] * invM;
-    k2[i] = dgamma[c] * invM;
+    k1[i] = (FOLD ? fold_k[2 * (tx * V + i)] : dbeta[c]) * invM;
+    k2[i] = (FOLD ? fold_k[2 * (tx * V + i) + 1] : dgamma[c]) * invM;
   }
   const int64_t stride = L.RY;
   const int64_t col = (int64_t)cg * V;
@@ -649,17 +756,7 @@ bn_finalize_kernel(const float* __restrict__ partials, int nparts, int64_t M, in
   if (slice == 0 && c < C) {
     double S = 0.0, Q = 0.0;
     for (int j = 0; j < FIN_SLICES; ++j) { S += sh[0][j][cl]; Q += sh[1][j][cl]; }
-    const double mean = S / (double)M;
-    double var = Q / (double)M - mean * mean;
-    if (var < 0.0) var = 0.0;
-    mean_out[c] = (float)mean;
-    rstd_out[c] = (float)(1.0 / sqrt(var + (double)eps));
-    if (moving_mean != nullptr) {
-      const double mv = unbiased ? var * ((double)M / (double)(M > 1 ? M - 1 : 1)) : var;
-      const float om = 1.f - decay;
-      moving_mean[c] -= (moving_mean[c] - (float)mean) * om;
-      moving_var[c] -= (moving_var[c] - (float)mv) * om;
-    }
+    bn_finalize_channel(S, Q, (double)M, eps, decay, unbiased, c, mean_out, rstd_out, moving_mean, moving_var);
   }
 }
 }  // namespace rn
@@ -740,14 +837,21 @@ extern "C" int rn_bn_stats_fwd(const void* x, const void* addend, void* sum_out,
 
 template <typename T>
 static int bn_apply_launch(const void* x, void* y, int64_t M, int C, const float* gamma, const float* beta,
-                           const float* mean, const float* rstd, int moving, float eps, float leak, cudaStream_t st) {
+                           const float* mean, const float* rstd, int moving, float eps, float leak, cudaStream_t st,
+                           const BnFold* fold = nullptr) {
   int rc = check_bn_args<T>(M, C);
   if (rc) return rc;
   static int awaves = -1;
   if (awaves < 0) { const char* e = getenv("RN_BN_APPLY_WAVES"); awaves = e ? atoi(e) : 4; }   // 56 registers: 4 resident CTAs per SM
+  if (fold) {
+    BnLayout L = bn_layout<T>(M, C, awaves, BN_FOLD_CW, 16384);
+    launch_pdl(bn_apply_kernel<T, true>, dim3(L.G, L.gridY), BN_THREADS, 0, st, (const T*)x, (T*)y, M, C, L, gamma, beta,
+               mean, rstd, 0, eps, leak, *fold);
+    return check_launch("bn_apply_kernel (folded finalisation)");
+  }
   BnLayout L = bn_layout<T>(M, C, awaves, bn_apply_cw(), 16384);
-  launch_pdl(bn_apply_kernel<T>, dim3(L.G, L.gridY), BN_THREADS, 0, st, (const T*)x, (T*)y, M, C, L, gamma, beta, mean,
-             rstd, moving, eps, leak);
+  launch_pdl(bn_apply_kernel<T, false>, dim3(L.G, L.gridY), BN_THREADS, 0, st, (const T*)x, (T*)y, M, C, L, gamma, beta, mean,
+             rstd, moving, eps, leak, BnFold{});
   return check_launch("bn_apply_kernel");
 }
 
@@ -817,20 +921,22 @@ extern "C" int rn_bn_act_bwd_reduce(const void* dy, const void* x, int64_t M, in
 template <typename T>
 static int bn_bwd_apply_launch(const void* dy, const void* x, void* dx, const void* addend, int64_t M, int C,
                                const float* gamma, const float* beta, const float* mean, const float* rstd,
-                               const float* dgamma, const float* dbeta, float leak, cudaStream_t st) {
+                               const float* dgamma, const float* dbeta, float leak, cudaStream_t st,
+                               const BnFold* fold = nullptr) {
   int rc = check_bn_args<T>(M, C);
   if (rc) return rc;
   static int bwaves = -1, bkb = -1;
   if (bwaves < 0) { const char* e = getenv("RN_BN_BWD_APPLY_WAVES"); bwaves = e ? atoi(e) : 3; }   // 80 registers: 3 resident CTAs per SM = one full wave
   if (bkb < 0) { const char* e = getenv("RN_BN_BWD_APPLY_KB"); bkb = e ? atoi(e) : 16; }
-  BnLayout L = bn_layout<T>(M, C, bwaves, bn_apply_cw(), (int64_t)bkb * 1024);
+  BnLayout L = bn_layout<T>(M, C, bwaves, fold ? BN_FOLD_CW : bn_apply_cw(), (int64_t)bkb * 1024);
   dim3 grid(L.G, L.gridY);
-  if (addend)
-    launch_pdl(bn_bwd_apply_kernel<T, true>, grid, BN_THREADS, 0, st, (const T*)dy, (const T*)x, (T*)dx,
-               (const T*)addend, M, C, L, gamma, beta, mean, rstd, dgamma, dbeta, leak);
-  else
-    launch_pdl(bn_bwd_apply_kernel<T, false>, grid, BN_THREADS, 0, st, (const T*)dy, (const T*)x, (T*)dx,
-               (const T*)nullptr, M, C, L, gamma, beta, mean, rstd, dgamma, dbeta, leak);
+  const BnFold f = fold ? *fold : BnFold{};
+#define RN_LAUNCH_BWD_APPLY(ADD_, FOLD_)                                                                              \
+  launch_pdl(bn_bwd_apply_kernel<T, ADD_, FOLD_>, grid, BN_THREADS, 0, st, (const T*)dy, (const T*)x, (T*)dx,        \
+             (const T*)addend, M, C, L, gamma, beta, mean, rstd, dgamma, dbeta, leak, f)
+  if (addend) { if (fold) RN_LAUNCH_BWD_APPLY(true, true); else RN_LAUNCH_BWD_APPLY(true, false); }
+  else        { if (fold) RN_LAUNCH_BWD_APPLY(false, true); else RN_LAUNCH_BWD_APPLY(false, false); }
+#undef RN_LAUNCH_BWD_APPLY
   return check_launch("bn_bwd_apply_kernel");
 }
 
@@ -848,6 +954,40 @@ extern "C" int rn_bn_act_bwd_apply(const void* dy, const void* x, void* dx, cons
     return bn_bwd_apply_launch<__nv_bfloat16>(dy, x, dx, dx_addend, M, C, gamma, beta, mean, rstd, dgamma, dbeta, leak,
                                               as_stream(stream));
   return fail(RN_ERR_INVALID, "bn_bwd_apply: bad dtype %d", dtype);
+}
+
+// The apply passes with the finalisation of a fused convolution epilogue's partial sums folded in (see BnFold).
+extern "C" int rn_bn_apply_act_fwd_partials(const void* x, void* y, int64_t M, int32_t C, int32_t dtype, const float* gamma,
+                                            const float* beta, const float* partials, int32_t nparts, float eps,
+                                            float decay, int32_t unbiased, float* mean, float* rstd, float* moving_mean,
+                                            float* moving_var, float leak, void* stream) {
+  RN_REQUIRE(x && y && gamma && beta && partials && mean && rstd && nparts > 0, "bn_apply_partials: bad arguments");
+  RN_REQUIRE((((uintptr_t)x | (uintptr_t)y | (uintptr_t)partials) & 15) == 0, "bn_apply_partials: x / y / partials must be 16-byte aligned");
+  RN_REQUIRE((moving_mean == nullptr) == (moving_var == nullptr), "bn_apply_partials: moving_mean/var must both be set or NULL");
+  const BnFold f{partials, nparts, (double)M, eps, decay, unbiased, mean, rstd, moving_mean, moving_var};
+  if (dtype == RN_F32)
+    return bn_apply_launch<float>(x, y, M, C, gamma, beta, nullptr, nullptr, 0, eps, leak, as_stream(stream), &f);
+  if (dtype == RN_BF16)
+    return bn_apply_launch<__nv_bfloat16>(x, y, M, C, gamma, beta, nullptr, nullptr, 0, eps, leak, as_stream(stream), &f);
+  return fail(RN_ERR_INVALID, "bn_apply_partials: bad dtype %d", dtype);
+}
+
+extern "C" int rn_bn_act_bwd_apply_partials(const void* dy, const void* x, void* dx, const void* dx_addend, int64_t M,
+                                            int32_t C, int32_t dtype, const float* gamma, const float* beta,
+                                            const float* mean, const float* rstd, const float* partials, int32_t nparts,
+                                            float* dgamma, float* dbeta, float leak, void* stream) {
+  RN_REQUIRE(dy && x && dx && gamma && beta && mean && rstd && partials && dgamma && dbeta && nparts > 0,
+             "bn_bwd_apply_partials: bad arguments");
+  RN_REQUIRE((((uintptr_t)dy | (uintptr_t)x | (uintptr_t)dx | (uintptr_t)dx_addend | (uintptr_t)partials) & 15) == 0,
+             "bn_bwd_apply_partials: dy / x / dx / dx_addend / partials must be 16-byte aligned");
+  const BnFold f{partials, nparts, (double)M, 0.f, 0.f, 0, dgamma, dbeta, nullptr, nullptr};
+  if (dtype == RN_F32)
+    return bn_bwd_apply_launch<float>(dy, x, dx, dx_addend, M, C, gamma, beta, mean, rstd, nullptr, nullptr, leak,
+                                      as_stream(stream), &f);
+  if (dtype == RN_BF16)
+    return bn_bwd_apply_launch<__nv_bfloat16>(dy, x, dx, dx_addend, M, C, gamma, beta, mean, rstd, nullptr, nullptr, leak,
+                                              as_stream(stream), &f);
+  return fail(RN_ERR_INVALID, "bn_bwd_apply_partials: bad dtype %d", dtype);
 }
 
 // ------------------------------------------------------------------------------------------

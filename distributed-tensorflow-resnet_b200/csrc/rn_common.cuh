@@ -99,6 +99,25 @@ __device__ __forceinline__ void bn_affine(float gamma, float beta, float mean, f
   *b = beta - mean * (*a);
 }
 
+// Batch statistics of one channel from its (sum, sum of squares) over M values, and the moving-average update of
+// tf.layers.batch_normalization: the ONE definition shared by bn_finalize_kernel and by the convolution kernels whose
+// last CTA finalises the statistics itself.
+__device__ __forceinline__ void bn_finalize_channel(double S, double Q, double M, float eps, float decay, int unbiased,
+                                                    int c, float* mean_out, float* rstd_out, float* moving_mean,
+                                                    float* moving_var) {
+  const double mean = S / M;
+  double var = Q / M - mean * mean;
+  if (var < 0.0) var = 0.0;
+  mean_out[c] = (float)mean;
+  rstd_out[c] = (float)(1.0 / sqrt(var + (double)eps));
+  if (moving_mean != nullptr) {
+    const double mv = unbiased ? var * (M / (M > 1.0 ? M - 1.0 : 1.0)) : var;
+    const float om = 1.f - decay;
+    moving_mean[c] -= (moving_mean[c] - (float)mean) * om;
+    moving_var[c] -= (moving_var[c] - (float)mv) * om;
+  }
+}
+
 // ---- programmatic dependent launch -------------------------------------------------------------
 // The hot kernels of the step are launched with the programmatic-stream-serialization attribute: the next
 // kernel of the stream may be scheduled (and run its prologue: barrier init, TMEM allocation, descriptor

@@ -67,6 +67,15 @@ struct TcConvParams {
   int ncols_total;
   int oW, oH, oN;                 // output extents (rows of a tile that fall outside are not part of the tensor)
   float* stat_partials;
+  // Folded finalisation: the CTA that finishes last (atomic ticket, reset for the next launch) sums the rows of the
+  // partial table in fp64 in a fixed order and writes what bn_finalize_kernel (1) / bn_bwd_finalize_kernel (2) would.
+  int fin_mode;                   // 0 none, 1 BN statistics (mean, rstd, moving averages), 2 BN backward (dgamma, dbeta)
+  int fin_unbiased;
+  int* fin_ticket;
+  float *fin_o0, *fin_o1;         // mode 1: mean, rstd; mode 2: dgamma, dbeta
+  float *fin_mm, *fin_mv;         // mode 1: moving mean / variance (or NULL)
+  double fin_M;
+  float fin_eps, fin_decay;
   CUtensorMap r_map;
   int8_t tap_map[TC_MAX_TAPS], tap_dw[TC_MAX_TAPS], tap_dh[TC_MAX_TAPS], tap_b[TC_MAX_TAPS];
   // Halo mode (3x3, stride 1): a pipeline stage is one HORIZONTAL tap (and k-chunk).  Its A box carries BH + 2 image
@@ -86,6 +95,55 @@ struct TcConvParams {
   int8_t halo_row[3][3];          // [group][j]: first row of the box the j-th vertical tap of the group reads, in units of BW rows
   int8_t halo_b[3][3];            // [group][j]: weight tap index
 };
+
+// Last-CTA finalisation of the partial table [rows][C][2] by the 256 epilogue threads: a thread owns a channel PAIR
+// (one 16-byte load per row) and a slice of the rows (rows slice, slice + S, ...; eight loads in flight), the slices
+// are combined in slice order through shared memory (`sh`: 256 x 4 doubles).
+__device__ __forceinline__ void fold_finalize(const TcConvParams& p, int te, int rows, double* sh) {
+  const int C2 = p.ncols_total >> 1;
+  const float4* tab = reinterpret_cast<const float4*>(p.stat_partials);
+  const int lanes = C2 < TC_EPI_THREADS ? C2 : TC_EPI_THREADS;
+  const int S = TC_EPI_THREADS / lanes;
+  const int cpl = te % lanes, slice = te / lanes;
+  for (int cp0 = 0; cp0 < C2; cp0 += lanes) {
+    const int cp = cp0 + cpl;
+    double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+    if (slice < S && cp < C2) {
+      const float4* q = tab + cp;
+      int z = slice;
+      for (; z + 7 * S < rows; z += 8 * S) {
+        float4 v[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) v[u] = __ldcg(q + (size_t)(z + u * S) * C2);
+#pragma unroll
+        for (int u = 0; u < 8; ++u) { a0 += (double)v[u].x; a1 += (double)v[u].y; a2 += (double)v[u].z; a3 += (double)v[u].w; }
+      }
+      for (; z < rows; z += S) {
+        const float4 v = __ldcg(q + (size_t)z * C2);
+        a0 += (double)v.x; a1 += (double)v.y; a2 += (double)v.z; a3 += (double)v.w;
+      }
+    }
+    if (S > 1) {                    // C <= 256: a single pass of the outer loop
+      sh[4 * te] = a0; sh[4 * te + 1] = a1; sh[4 * te + 2] = a2; sh[4 * te + 3] = a3;
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      if (slice == 0)
+        for (int j = 1; j < S; ++j) {
+          const double* o = sh + 4 * (j * lanes + cpl);
+          a0 += o[0]; a1 += o[1]; a2 += o[2]; a3 += o[3];
+        }
+    }
+    if (slice == 0 && cp < C2) {
+      const int c = 2 * cp;
+      if (p.fin_mode == 1) {
+        bn_finalize_channel(a0, a1, p.fin_M, p.fin_eps, p.fin_decay, p.fin_unbiased, c, p.fin_o0, p.fin_o1, p.fin_mm, p.fin_mv);
+        bn_finalize_channel(a2, a3, p.fin_M, p.fin_eps, p.fin_decay, p.fin_unbiased, c + 1, p.fin_o0, p.fin_o1, p.fin_mm, p.fin_mv);
+      } else {                      // (sum g, sum g * xhat) -> dbeta, dgamma
+        p.fin_o1[c] = (float)a0; p.fin_o0[c] = (float)a1;
+        p.fin_o1[c + 1] = (float)a2; p.fin_o0[c + 1] = (float)a3;
+      }
+    }
+  }
+}
 
 constexpr int TC_RES_SLOTS_MAX = 6;        // upper bound of TcConvParams::res_slots (tiles of 16 KB in flight)
 constexpr int TC_THREADS_RES = TC_CONV_THREADS + 32;
@@ -612,6 +670,23 @@ conv_tc_kernel(const __grid_constant__ TcConvParams p) {
       asm volatile("bar.sync 1, 256;" ::: "memory");
       float* dst = p.stat_partials + (size_t)blockIdx.x * 2 * p.ncols_total;
       for (int i = te; i < 2 * p.ncols_total; i += TC_EPI_THREADS) dst[i] = pacc[i];
+      if (p.fin_mode) {
+        __threadfence();                                   // this CTA's row is visible device-wide before its ticket
+        asm volatile("bar.sync 1, 256;" ::: "memory");
+        int* flag = reinterpret_cast<int*>(cs);
+        if (te == 0) {
+          const int last = atomicAdd(p.fin_ticket, 1) == (int)gridDim.x - 1;
+          if (last) atomicExch(p.fin_ticket, 0);           // every CTA has drawn its ticket: ready for the next launch
+          *flag = last;
+        }
+        asm volatile("bar.sync 1, 256;" ::: "memory");
+        const int last = *flag;
+        asm volatile("bar.sync 1, 256;" ::: "memory");     // the flag has been read before `cs` is reused
+        if (last) {
+          __threadfence();
+          fold_finalize(p, te, (int)gridDim.x, reinterpret_cast<double*>(cs));
+        }
+      }
     }
     if (warp == 2) {
       if (elect_one()) tma_store_wait<0>();
@@ -1892,6 +1967,36 @@ extern "C" int rn_convtc_run(rn_convtc_plan* plan, float beta, void* stream) {
   return RN_OK;
 }
 
+// Fold the finalisation of a fused epilogue's partial rows into the convolution kernel itself (see TcConvParams::fin_mode).
+// The table is <= 148 rows of C (sum, sum) pairs; one CTA sums it in a few microseconds while C is small, which is
+// cheaper than one more dependent launch, so the caller decides per layer (the standalone kernels spread wide tables
+// over many CTAs).  `ticket` is one zero-initialised int32 in device memory owned by the caller, private to this plan.
+extern "C" int rn_convtc_plan_fold_bn_finalize(rn_convtc_plan* plan, int64_t M, float eps, float decay, int32_t unbiased,
+                                               float* mean, float* rstd, float* moving_mean, float* moving_var,
+                                               int32_t* ticket) {
+  RN_REQUIRE(plan && mean && rstd && ticket && M > 0, "convtc_plan_fold_bn_finalize: bad arguments");
+  RN_REQUIRE((moving_mean == nullptr) == (moving_var == nullptr), "convtc_plan_fold_bn_finalize: moving_mean/var must both be set or NULL");
+  if (plan->kind != 0 || plan->nsub != 1 || !plan->p[0].fuse_stats)
+    return fail(RN_ERR_UNSUPPORTED, "convtc_plan_fold_bn_finalize: the plan has no fused statistics epilogue");
+  TcConvParams& p = plan->p[0];
+  p.fin_mode = 1;
+  p.fin_ticket = ticket;
+  p.fin_o0 = mean; p.fin_o1 = rstd; p.fin_mm = moving_mean; p.fin_mv = moving_var;
+  p.fin_M = (double)M; p.fin_eps = eps; p.fin_decay = decay; p.fin_unbiased = unbiased;
+  return RN_OK;
+}
+
+extern "C" int rn_convtc_plan_fold_bn_bwd_finalize(rn_convtc_plan* plan, float* dgamma, float* dbeta, int32_t* ticket) {
+  RN_REQUIRE(plan && dgamma && dbeta && ticket, "convtc_plan_fold_bn_bwd_finalize: bad arguments");
+  if (plan->kind != 1 || plan->nsub != 1 || !plan->p[0].fuse_bnbwd)
+    return fail(RN_ERR_UNSUPPORTED, "convtc_plan_fold_bn_bwd_finalize: the plan has no fused BN-backward epilogue");
+  TcConvParams& p = plan->p[0];
+  p.fin_mode = 2;
+  p.fin_ticket = ticket;
+  p.fin_o0 = dgamma; p.fin_o1 = dbeta;
+  return RN_OK;
+}
+
 extern "C" int rn_convtc_plan_describe(const rn_convtc_plan* plan, char* buf, size_t n) {
   RN_REQUIRE(plan && buf && n > 0, "convtc_plan_describe: bad arguments");
   if (plan->kind == 2) {
@@ -1901,9 +2006,9 @@ extern "C" int rn_convtc_plan_describe(const rn_convtc_plan* plan, char* buf, si
     return RN_OK;
   }
   const TcConvParams& p = plan->p[0];
-  snprintf(buf, n, "%s subs=%d block_n=%d acc_m=%d box=%dx%dx%d kc=%d taps=%d stages=%d tstages=%d pair=%d grid=%d fused=%d%d%d halo=%d",
+  snprintf(buf, n, "%s subs=%d block_n=%d acc_m=%d box=%dx%dx%d kc=%d taps=%d stages=%d tstages=%d pair=%d grid=%d fused=%d%d%d halo=%d fold=%d",
            plan->kind == 0 ? "fprop" : "dgrad", plan->nsub, p.block_n, p.acc_m, p.BW, p.BH, p.BN, p.kc, p.taps, p.stages,
-           p.tstages, p.pair, plan->grid[0], p.fuse_add, p.fuse_stats, p.fuse_bnbwd, p.halo);
+           p.tstages, p.pair, plan->grid[0], p.fuse_add, p.fuse_stats, p.fuse_bnbwd, p.halo, p.fin_mode);
   if (p.xf) strncat(buf, " bn_operand=1", n - strlen(buf) - 1);
   return RN_OK;
 }

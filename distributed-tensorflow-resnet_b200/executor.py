@@ -519,6 +519,7 @@ class Executor:
             self._plans.append(plan)
             if f is not None:
                 f["nrows"] = nrows.value
+                f["plan"] = plan
                 if f["residual"] is not None:
                     y.buf = None
             fn = lambda s, p=plan: check(lib.rn_convtc_run(p, 0.0, s), "rn_convtc_run")   # noqa: E731
@@ -549,6 +550,7 @@ class Executor:
                                                   ptr(f["partials"]), C.byref(nrows), C.byref(plan)),
                   "rn_convtc_plan_create_fused")
             f["nrows"] = nrows.value
+            f["plan"] = plan
             self._plans.append(plan)
             if f["residual"] is not None:
                 y.buf = None            # conv + shortcut goes straight into the sum: the conv output is never materialised
@@ -560,6 +562,29 @@ class Executor:
         w = self._wptr(kv, "Wb" if self.bf16 else "W")
         return ("conv_fprop:" + y.name, lambda s, d=d, px=ptr(x.buf), py=ptr(y.buf), w=w:
                 check(lib.rn_conv2d_fprop(C.byref(d), px, w, py, s), "rn_conv2d_fprop"))
+
+    # folded finalisation -------------------------------------------------------------------
+    def _finalize_mode(self):
+        """Where the per-CTA sums of a fused convolution epilogue become BN constants (RN_BN_FINALIZE):
+        'kernel' — a standalone rn_bn_finalize / rn_bn_bwd_finalize launch (default: the measured winner);
+        'apply'  — inside the BN apply kernel that follows (every CTA sums the rows of its channels): 87 fewer launches
+                   per ResNet-50 step, but the dependent loads at the head of every apply CTA cost what the launch did;
+        'conv'   — by the convolution's last CTA, up to RN_TC_FOLD_MAX_C channels (slower: fence + ticket + one CTA's loads).
+        profiles/r02_finalize_ab.txt has the A/B."""
+        return os.environ.get("RN_BN_FINALIZE", "kernel")
+
+    def _fold_ok(self, channels):
+        return self._finalize_mode() == "conv" and channels <= int(os.environ.get("RN_TC_FOLD_MAX_C", "256"))
+
+    def _ticket(self):
+        """One zero-initialised int32 per folded plan (the last-CTA ticket), carved from a shared device array."""
+        if getattr(self, "_tickets", None) is None or self._ticket_next == self._tickets.numel():
+            self._tickets = torch.zeros(1024, dtype=torch.int32, device=self.dev)
+            self._keep.append(self._tickets)
+            self._ticket_next = 0
+        p = self._tickets.data_ptr() + 4 * self._ticket_next
+        self._ticket_next += 1
+        return p
 
     # tensor-core plans -------------------------------------------------------------------
     def _tc_plan(self, n, d, kind, a_buf, out_ptr_or_buf, b_buf=None):
@@ -602,7 +627,16 @@ class Executor:
             if not self.train:
                 mm = mv = None       # forward-only with batch statistics: leave moving stats alone
             cv = getattr(n, "stats_from", None)
-            if cv is not None:
+            fold_apply = cv is not None and self._finalize_mode() == "apply" and not getattr(n, "virtual", False)
+            if fold_apply:
+                pass        # the apply pass below sums the convolution's per-CTA rows itself
+            elif cv is not None and self._fold_ok(C_) and not cv.fuse.get("folded"):
+                # ... and its last CTA also turns the per-CTA sums into mean / rstd / moving averages: no launch here
+                cv.fuse["folded"] = True
+                check(lib.rn_convtc_plan_fold_bn_finalize(cv.fuse["plan"], M, a["eps"], a["decay"], int(a["unbiased"]),
+                                                          mean_p, rstd_p, mm, mv, self._ticket()),
+                      "rn_convtc_plan_fold_bn_finalize")
+            elif cv is not None:
                 # the producing conv's epilogue already summed the stored tensor (and added the shortcut)
                 out.append(("bn_finalize:" + a["scope"],
                             lambda s, args=(ptr(cv.fuse["partials"]), cv.fuse["nrows"], M, C_, a["eps"], a["decay"],
@@ -614,6 +648,12 @@ class Executor:
                             check(lib.rn_bn_stats_fwd(*args, ptr(self.scratch), self.scratch_bytes, s), "rn_bn_stats_fwd")))
             if getattr(n, "virtual", False):
                 y.buf = None         # normalised inside the consuming 1x1 convolutions' shared memory, never stored
+            elif fold_apply:
+                out.append(("bn_apply:" + a["scope"],
+                            lambda s, args=(ptr(x.buf), ptr(y.buf), M, C_, self.rn_dt, self._wptr(v["gamma"]), self._wptr(v["beta"]),
+                                            ptr(cv.fuse["partials"]), cv.fuse["nrows"], a["eps"], a["decay"], int(a["unbiased"]),
+                                            mean_p, rstd_p, mm, mv, a["leak"]):
+                            check(lib.rn_bn_apply_act_fwd_partials(*args, s), "rn_bn_apply_act_fwd_partials")))
             else:
                 out.append(("bn_apply:" + a["scope"],
                             lambda s, args=(ptr(x.buf), ptr(y.buf), M, C_, self.rn_dt, self._wptr(v["gamma"]), self._wptr(v["beta"]), mean_p, rstd_p, 0, a["eps"], a["leak"]):
@@ -772,7 +812,13 @@ class Executor:
             gp, bp = self._wptr(v["gamma"]), self._wptr(v["beta"])
             dgp, dbp = self._wptr(v["gamma"], "G"), self._wptr(v["beta"], "G")
             bf = getattr(n, "bwd_from", None)
-            if bf is not None:
+            fold_apply = bf is not None and self._finalize_mode() == "apply" and x.requires_grad
+            if fold_apply:
+                pass        # bn_bwd_apply below sums the dgrad's per-CTA rows itself and writes dgamma / dbeta
+            elif bf is not None and self._fold_ok(C_):
+                check(lib.rn_convtc_plan_fold_bn_bwd_finalize(bf["plan"], dgp, dbp, self._ticket()),
+                      "rn_convtc_plan_fold_bn_bwd_finalize")
+            elif bf is not None:
                 self._emit(bwd, "bn_bwd_finalize:" + a["scope"],
                            lambda s, args=(ptr(bf["partials"]), bf["nrows"], C_, dgp, dbp):
                            check(lib.rn_bn_bwd_finalize(*args, s), "rn_bn_bwd_finalize"), node=n, dy=dy)
@@ -784,9 +830,16 @@ class Executor:
             if x.requires_grad:
                 dxb, beta = self._target(x, done, bwd)
                 addp = ptr(dxb) if beta != 0.0 else None
-                self._emit(bwd, "bn_bwd_apply:" + a["scope"],
-                           lambda s, args=(ptr(dy), ptr(x.buf), ptr(dxb), addp, M, C_, self.rn_dt, gp, bp, mean_p, rstd_p, dgp, dbp, a["leak"]):
-                           check(lib.rn_bn_act_bwd_apply(*args, s), "rn_bn_act_bwd_apply"), node=n, dy=dy, dx=dxb, beta=beta)
+                if fold_apply:
+                    self._emit(bwd, "bn_bwd_apply:" + a["scope"],
+                               lambda s, args=(ptr(dy), ptr(x.buf), ptr(dxb), addp, M, C_, self.rn_dt, gp, bp, mean_p, rstd_p,
+                                               ptr(bf["partials"]), bf["nrows"], dgp, dbp, a["leak"]):
+                               check(lib.rn_bn_act_bwd_apply_partials(*args, s), "rn_bn_act_bwd_apply_partials"),
+                               node=n, dy=dy, dx=dxb, beta=beta)
+                else:
+                    self._emit(bwd, "bn_bwd_apply:" + a["scope"],
+                               lambda s, args=(ptr(dy), ptr(x.buf), ptr(dxb), addp, M, C_, self.rn_dt, gp, bp, mean_p, rstd_p, dgp, dbp, a["leak"]):
+                               check(lib.rn_bn_act_bwd_apply(*args, s), "rn_bn_act_bwd_apply"), node=n, dy=dy, dx=dxb, beta=beta)
         elif n.op == "conv2d":
             x = n.inputs[0]
             d = self._desc(n)
@@ -811,7 +864,7 @@ class Executor:
                         self._wptr(bv["gamma"]), self._wptr(bv["beta"]), bn.saved[0].data_ptr(), bn.saved[1].data_ptr(),
                         bn.attrs["leak"], ptr(part), C.byref(nrows), C.byref(plan)), "rn_convtc_plan_create_fused_dgrad")
                     self._plans.append(plan)
-                    bn.bwd_from = dict(partials=part, nrows=nrows.value)
+                    bn.bwd_from = dict(partials=part, nrows=nrows.value, plan=plan)
                     fn = lambda s, p=plan: check(lib.rn_convtc_run(p, 0.0, s), "rn_convtc_run")   # noqa: E731
                     fn.plan = plan
                     self._emit(bwd, "conv_dgrad_tc:" + y.name, fn, node=n, dy=dy, dx=dxb, beta=0.0)

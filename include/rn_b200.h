@@ -41,7 +41,7 @@ typedef enum {
 const char* rn_last_error(void);
 /* ABI version; bumped whenever a signature changes.  The Python bindings (_lib.py) refuse a library
  * whose rn_abi_version() differs from the version they were written against. */
-#define RN_ABI_VERSION 4
+#define RN_ABI_VERSION 5
 int rn_abi_version(void);
 /* Number of kernel launches issued through this library by the calling process (all threads). */
 uint64_t rn_launch_count(void);
@@ -112,6 +112,16 @@ int rn_convtc_plan_create_fused_dgrad(const rn_conv_desc* d, const void* dy, con
                                       const void* bn_x, const float* gamma, const float* beta, const float* mean,
                                       const float* rstd, float leak, float* sum_partials, int32_t* rows,
                                       rn_convtc_plan** plan);
+/* Fold the finalisation of a fused epilogue's partial rows into the convolution launch: the CTA that finishes last
+ * (atomic ticket) sums the rows in fp64 in a fixed order and writes what rn_bn_finalize (plan from
+ * rn_convtc_plan_create_fused / _bnin with stat_partials) or rn_bn_bwd_finalize (plan from
+ * rn_convtc_plan_create_fused_dgrad) would have written, so that launch disappears from the step
+ * (FusedBatchNorm / FusedBatchNormGrad, resnet_model_official.py:41-50).  One CTA sums the table, which pays while
+ * the BN has few channels (the executor folds up to 256); `ticket` is one zero-initialised int32 in device memory
+ * owned by the caller and private to the plan.  Call after plan creation, before rn_convtc_run. */
+int rn_convtc_plan_fold_bn_finalize(rn_convtc_plan* plan, int64_t M, float eps, float decay, int32_t unbiased,
+                                    float* mean, float* rstd, float* moving_mean, float* moving_var, int32_t* ticket);
+int rn_convtc_plan_fold_bn_bwd_finalize(rn_convtc_plan* plan, float* dgamma, float* dbeta, int32_t* ticket);
 /* 1x1 convolutions (any stride, Cin a multiple of 64) whose input is the output of a training-mode
  * batch_norm_relu (resnet_model_official.py:41-50 followed by conv2d_fixed_padding :80-91 — conv1 / conv3 of a
  * bottleneck block and the projection shortcut): the plan reads the BN's INPUT `bn_x` and applies
@@ -184,6 +194,19 @@ size_t rn_bn_scratch_bytes(int64_t M, int32_t C);
 int rn_bn_finalize(const float* partials, int32_t nparts, int64_t M, int32_t C, float eps, float decay,
                    int32_t unbiased, float* mean, float* rstd, float* moving_mean, float* moving_var, void* stream);
 int rn_bn_bwd_finalize(const float* partials, int32_t nparts, int32_t C, float* dgamma, float* dbeta, void* stream);
+/* The apply passes with that finalisation folded in: every CTA sums the partial rows for its own <= 64 channels
+ * (fp64, one fixed order, so all CTAs derive identical constants) and one CTA per channel chunk writes
+ * mean / rstd / moving averages (forward) or dgamma / dbeta (backward) for later use.  Removes the
+ * rn_bn_finalize / rn_bn_bwd_finalize launch between the convolution and the apply pass; outputs equal those
+ * of rn_bn_finalize + rn_bn_apply_act_fwd, resp. rn_bn_bwd_finalize + rn_bn_act_bwd_apply. */
+int rn_bn_apply_act_fwd_partials(const void* x, void* y, int64_t M, int32_t C, int32_t dtype, const float* gamma,
+                                 const float* beta, const float* partials, int32_t nparts, float eps, float decay,
+                                 int32_t unbiased, float* mean, float* rstd, float* moving_mean, float* moving_var,
+                                 float leak, void* stream);
+int rn_bn_act_bwd_apply_partials(const void* dy, const void* x, void* dx, const void* dx_addend, int64_t M, int32_t C,
+                                 int32_t dtype, const float* gamma, const float* beta, const float* mean,
+                                 const float* rstd, const float* partials, int32_t nparts, float* dgamma, float* dbeta,
+                                 float leak, void* stream);
 /* Training statistics.  If `addend` != NULL the statistics are of z = x + addend and z is written
  * to `sum_out` (the residual add fused into the statistics pass).  Writes mean[C], rstd[C]
  * (= 1/sqrt(biased_var + eps)) and, if moving_mean != NULL, updates

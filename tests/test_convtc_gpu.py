@@ -402,9 +402,27 @@ def test_convtc_fused_epilogue(case):
         (Z.float() - want.float()).abs().max().item())
     assert rel_err(Z.float(), yv.val + (res.double() if use_res else 0.0)) < 2e-2
     assert lib.rn_convtc_run(plan, 1.0, stream()) != 0          # a fused plan cannot accumulate
+    if use_stats:
+        # folded finalisation: the last CTA of the SAME plan writes mean / rstd / moving averages (ticket resets itself)
+        M = N * Ho * Wo
+        f_mean = torch.full((Cout,), float("nan"), device="cuda"); f_rstd = torch.full((Cout,), float("nan"), device="cuda")
+        f_mm = torch.zeros(Cout, device="cuda"); f_mv = torch.ones(Cout, device="cuda")
+        ticket = torch.zeros(1, dtype=torch.int32, device="cuda")
+        check(lib.rn_convtc_plan_fold_bn_finalize(plan, M, 1e-5, 0.9, 1, ptr(f_mean), ptr(f_rstd), ptr(f_mm), ptr(f_mv),
+                                                  ptr(ticket)), "fold")
+        check(lib.rn_convtc_run(plan, 0.0, stream()), "run folded")
+        torch.cuda.synchronize()
+        assert int(ticket.item()) == 0 and torch.equal(Z, want)
+        fold1 = [t.clone() for t in (f_mean, f_rstd, f_mm, f_mv)]
+        f_mean.fill_(float("nan")); f_rstd.fill_(float("nan"))
+        check(lib.rn_convtc_run(plan, 0.0, stream()), "run folded again")
+        torch.cuda.synchronize()
+        assert int(ticket.item()) == 0 and torch.equal(f_mean, fold1[0]) and torch.equal(f_rstd, fold1[1])
+    else:
+        ticket = torch.zeros(1, dtype=torch.int32, device="cuda")
+        assert lib.rn_convtc_plan_fold_bn_finalize(plan, 1, 1e-5, 0.9, 1, ptr(ticket), ptr(ticket), None, None, ptr(ticket)) != 0
     lib.rn_convtc_plan_destroy(plan)
     if use_stats:
-        M = N * Ho * Wo
         assert 0 < nrows.value <= rows_cap and torch.isfinite(PART[:nrows.value]).all()
         mean = torch.empty(Cout, device="cuda"); rstd = torch.empty(Cout, device="cuda")
         mm = torch.zeros(Cout, device="cuda"); mv = torch.ones(Cout, device="cuda")
@@ -417,6 +435,25 @@ def test_convtc_fused_epilogue(case):
         assert rel_err(rstd.cpu().double(), 1.0 / torch.sqrt(v_ref + 1e-5)) < 1e-5
         assert rel_err(mm.cpu().double(), 0.1 * m_ref) < 1e-4
         assert rel_err(mv.cpu().double(), 0.9 + 0.1 * v_ref * M / (M - 1)) < 1e-5
+        # the folded finalisation sums the same rows in fp64 (another fixed order): equal to the standalone kernel
+        for got, ref in zip(fold1, (mean, rstd, mm, mv)):
+            assert rel_err(got.cpu().double(), ref.cpu().double()) < 1e-6
+        # consumer-side finalisation: the apply pass sums the rows itself (rn_bn_apply_act_fwd_partials) — same
+        # statistics, and its output equals the plain apply pass run with the statistics it wrote, bit for bit
+        gam = (1.0 + 0.1 * torch.randn(Cout, generator=g)).float().cuda()
+        bet = (0.1 * torch.randn(Cout, generator=g)).float().cuda()
+        a_mean = torch.full((Cout,), float("nan"), device="cuda"); a_rstd = torch.full((Cout,), float("nan"), device="cuda")
+        a_mm = torch.zeros(Cout, device="cuda"); a_mv = torch.ones(Cout, device="cuda")
+        Y1 = torch.full_like(Z, float("nan")); Y0 = torch.full_like(Z, float("nan"))
+        check(lib.rn_bn_apply_act_fwd_partials(ptr(Z), ptr(Y1), M, Cout, RN_BF16, ptr(gam), ptr(bet), ptr(PART), nrows.value,
+                                               1e-5, 0.9, 1, ptr(a_mean), ptr(a_rstd), ptr(a_mm), ptr(a_mv), 0.0, stream()),
+              "apply partials")
+        check(lib.rn_bn_apply_act_fwd(ptr(Z), ptr(Y0), M, Cout, RN_BF16, ptr(gam), ptr(bet), ptr(a_mean), ptr(a_rstd), 0,
+                                      1e-5, 0.0, stream()), "apply")
+        torch.cuda.synchronize()
+        for got, ref in zip((a_mean, a_rstd, a_mm, a_mv), (mean, rstd, mm, mv)):
+            assert rel_err(got.cpu().double(), ref.cpu().double()) < 1e-6
+        assert torch.equal(Y1, Y0)
 
 
 FUSED_DGRAD_CASES = [
@@ -476,8 +513,31 @@ def test_convtc_fused_dgrad_bn_backward_sums(case, leak):
     check(lib.rn_bn_bwd_finalize(ptr(PART), nrows.value, Cin, ptr(DG), ptr(DB), stream()), "finalize")
     torch.cuda.synchronize()
     assert lib.rn_convtc_run(plan, 1.0, stream()) != 0
+    # folded finalisation: dgamma / dbeta written by the dgrad's last CTA
+    FDG, FDB = torch.full((Cin,), float("nan"), device="cuda"), torch.full((Cin,), float("nan"), device="cuda")
+    ticket = torch.zeros(1, dtype=torch.int32, device="cuda")
+    check(lib.rn_convtc_plan_fold_bn_bwd_finalize(plan, ptr(FDG), ptr(FDB), ptr(ticket)), "fold")
+    for _ in range(2):
+        check(lib.rn_convtc_run(plan, 0.0, stream()), "run folded")
+    torch.cuda.synchronize()
+    assert int(ticket.item()) == 0
+    assert rel_err(FDG.cpu().double(), DG.cpu().double()) < 1e-6 and rel_err(FDB.cpu().double(), DB.cpu().double()) < 1e-6
     lib.rn_convtc_plan_destroy(plan)
     assert torch.equal(DX, DX0)
+    # consumer-side finalisation: rn_bn_act_bwd_apply_partials sums the rows itself, writes dgamma / dbeta, and its dx
+    # equals the plain pass run with those sums (with and without an addend)
+    for use_add in (False, True):
+        ADDEND = torch.randn(N, H, W, Cin, generator=g).to(BF).cuda() if use_add else None
+        ADG, ADB = torch.full((Cin,), float("nan"), device="cuda"), torch.full((Cin,), float("nan"), device="cuda")
+        O1 = torch.full((N, H, W, Cin), float("nan"), dtype=BF, device="cuda"); O0 = torch.full_like(O1, float("nan"))
+        check(lib.rn_bn_act_bwd_apply_partials(ptr(DX), ptr(XB), ptr(O1), ptr(ADDEND) if use_add else None, M, Cin, RN_BF16,
+                                               ptr(G_), ptr(B_), ptr(MU), ptr(RS), ptr(PART), nrows.value, ptr(ADG), ptr(ADB),
+                                               leak, stream()), "bwd apply partials")
+        check(lib.rn_bn_act_bwd_apply(ptr(DX), ptr(XB), ptr(O0), ptr(ADDEND) if use_add else None, M, Cin, RN_BF16, ptr(G_),
+                                      ptr(B_), ptr(MU), ptr(RS), ptr(ADG), ptr(ADB), leak, stream()), "bwd apply")
+        torch.cuda.synchronize()
+        assert rel_err(ADG.cpu().double(), DG.cpu().double()) < 1e-6 and rel_err(ADB.cpu().double(), DB.cpu().double()) < 1e-6
+        assert torch.equal(O1, O0)
     # against the separate reduction kernel (same inputs, different summation order)
     gd = DX0.double().reshape(M, Cin).cpu()
     pre = torch.addcmul((beta - mean * (gamma * rstd)).float(), xbn.float().reshape(M, Cin), (gamma * rstd).float()).double()

@@ -33,7 +33,7 @@ def test_cabi_library_exports_every_declared_symbol():
     for name in sorted(declared):
         assert hasattr(so, name), "symbol %s declared in include/rn_b200.h is not exported" % name
     assert declared == set(_lib.SIGNATURES), (declared ^ set(_lib.SIGNATURES))
-    assert so.rn_abi_version() == _lib.ABI_VERSION == 4
+    assert so.rn_abi_version() == _lib.ABI_VERSION == 5
 
 
 def test_cabi_argument_errors_without_gpu():
