@@ -17,17 +17,32 @@ sgemm_strided_kernel(const float* __restrict__ A, int64_t a_rs, int64_t a_cs, co
   const int tr = tid / 16, tc = tid % 16;
   const int m0 = blockIdx.y * 64, n0 = blockIdx.x * 64;
   float acc[4][4] = {};
-  for (int k0 = 0; k0 < K; k0 += 16) {
-    // consecutive threads follow whichever index is contiguous in memory (either operand may be transposed)
-    for (int e = tid; e < 64 * 16; e += 256) {
+  float ra[4], rb[4];          // register prefetch of the next k-step (see sgemm_splitk_kernel)
+  auto fetch = [&](int k0) {
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+      // consecutive threads follow whichever index is contiguous in memory (either operand may be transposed)
+      const int e = tid + t * 256;
       const int kk = a_cs == 1 ? e % 16 : e / 64, mm = a_cs == 1 ? e / 16 : e % 64;
       const int gm = m0 + mm, gk = k0 + kk;
-      As[kk][mm] = (gm < M && gk < K) ? A[gm * a_rs + gk * a_cs] : 0.f;
+      ra[t] = (gm < M && gk < K) ? A[gm * a_rs + gk * a_cs] : 0.f;
       const int nn = b_cs == 1 ? e % 64 : e / 16, k2 = b_cs == 1 ? e / 64 : e % 16;
       const int gn = n0 + nn, gk2 = k0 + k2;
-      Bs[k2][nn] = (gn < N && gk2 < K) ? Bm[gk2 * b_rs + gn * b_cs] : 0.f;
+      rb[t] = (gn < N && gk2 < K) ? Bm[gk2 * b_rs + gn * b_cs] : 0.f;
+    }
+  };
+  fetch(0);
+  for (int k0 = 0; k0 < K; k0 += 16) {
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+      const int e = tid + t * 256;
+      const int kk = a_cs == 1 ? e % 16 : e / 64, mm = a_cs == 1 ? e / 16 : e % 64;
+      As[kk][mm] = ra[t];
+      const int nn = b_cs == 1 ? e % 64 : e / 16, k2 = b_cs == 1 ? e / 64 : e % 16;
+      Bs[k2][nn] = rb[t];
     }
     __syncthreads();
+    if (k0 + 16 < K) fetch(k0 + 16);
 #pragma unroll
     for (int kk = 0; kk < 16; ++kk) {
       float a[4], b[4];
@@ -63,17 +78,34 @@ sgemm_splitk_kernel(const float* __restrict__ A, int64_t a_rs, int64_t a_cs, con
   const int kb = blockIdx.z * kslice;
   const int ke = min(K, kb + kslice);
   float acc[4][4] = {};
-  for (int k0 = kb; k0 < ke; k0 += 16) {
-    // consecutive threads follow whichever index is contiguous in memory (either operand may be transposed)
-    for (int e = tid; e < 64 * 16; e += 256) {
+  // the next k-step's operands are fetched into registers while this one is multiplied (the loop used to be
+  // load -> barrier -> multiply -> barrier with nothing in flight during the multiply); same summation order
+  float ra[4], rb[4];
+  auto fetch = [&](int k0) {
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+      // consecutive threads follow whichever index is contiguous in memory (either operand may be transposed)
+      const int e = tid + t * 256;
       const int kk = a_cs == 1 ? e % 16 : e / 64, mm = a_cs == 1 ? e / 16 : e % 64;
       const int gm = m0 + mm, gk = k0 + kk;
-      As[kk][mm] = (gm < M && gk < ke) ? A[gm * a_rs + gk * a_cs] : 0.f;
+      ra[t] = (gm < M && gk < ke) ? A[gm * a_rs + gk * a_cs] : 0.f;
       const int nn = b_cs == 1 ? e % 64 : e / 16, k2 = b_cs == 1 ? e / 64 : e % 16;
       const int gn = n0 + nn, gk2 = k0 + k2;
-      Bs[k2][nn] = (gn < N && gk2 < ke) ? Bm[gk2 * b_rs + gn * b_cs] : 0.f;
+      rb[t] = (gn < N && gk2 < ke) ? Bm[gk2 * b_rs + gn * b_cs] : 0.f;
+    }
+  };
+  fetch(kb);
+  for (int k0 = kb; k0 < ke; k0 += 16) {
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+      const int e = tid + t * 256;
+      const int kk = a_cs == 1 ? e % 16 : e / 64, mm = a_cs == 1 ? e / 16 : e % 64;
+      As[kk][mm] = ra[t];
+      const int nn = b_cs == 1 ? e % 64 : e / 16, k2 = b_cs == 1 ? e / 64 : e % 16;
+      Bs[k2][nn] = rb[t];
     }
     __syncthreads();
+    if (k0 + 16 < ke) fetch(k0 + 16);
 #pragma unroll
     for (int kk = 0; kk < 16; ++kk) {
       float a[4], b[4];
