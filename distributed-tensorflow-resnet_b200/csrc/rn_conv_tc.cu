@@ -798,15 +798,22 @@ struct TcWgradParams {
   int kp, stages;
   uint32_t stage_bytes, tmem_cols;
   int8_t tap_map[TC_MAX_TAPS], tap_dw[TC_MAX_TAPS], tap_dh[TC_MAX_TAPS];
+  int pair;                       // 1: clusters of two CTAs, M = 256 (row_groups then counts PAIRS of row groups)
   // operand transform (see TcConvParams::xf): X is the input of a training-mode BN+ReLU, normalised in shared memory
   int xf;
   const float *xf_gamma, *xf_beta, *xf_mean, *xf_rstd;
   float xf_leak;
 };
 
-template <bool XF>
+// PAIR = true: clusters of two CTAs and tcgen05.mma.cta_group::2 (M = 256): the CTAs of a pair own neighbouring row
+// groups of dW (each keeps its 128-row accumulators in its own tensor memory) and every CTA loads HALF of the dY tile,
+// so the operand bytes fetched from shared memory per MAC drop by a third (see the fprop / dgrad kernel).
+template <bool XF, bool PAIR>
 __global__ void __launch_bounds__(TC_THREADS + (XF ? TC_XF_WARPS * 32 : 0), 1)
 conv_wgrad_tc_kernel(const __grid_constant__ TcWgradParams p) {
+  static_assert(!(XF && PAIR), "the operand transform is built for single CTAs");
+  const uint32_t cta_rank = PAIR ? cluster_ctarank() : 0u;
+  const bool leader = cta_rank == 0u;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base_u32 = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* smem = smem_raw + (base_u32 - smem_u32(smem_raw));
@@ -824,37 +831,44 @@ conv_wgrad_tc_kernel(const __grid_constant__ TcWgradParams p) {
     for (int i = 0; i < p.stages; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
     if (XF) for (int i = 0; i < p.stages; ++i) mbar_init(&xfull[i], TC_XF_WARPS);
     mbar_init(tfull, 1);
-    mbar_init(tempty, 4);
+    mbar_init(tempty, PAIR ? 8 : 4);          // pair: the leader's barrier collects the epilogue warps of both CTAs
     fence_barrier_init();
     tma_prefetch_desc(&p.x_map[0]);
     tma_prefetch_desc(&p.dy_map);
   }
   if (warp == 1) {
-    tmem_alloc(tmem_slot, p.tmem_cols);
-    tmem_relinquish();
+    if (PAIR) { tmem_alloc_pair(tmem_slot, p.tmem_cols); tmem_relinquish_pair(); }
+    else      { tmem_alloc(tmem_slot, p.tmem_cols); tmem_relinquish(); }
   }
   tc_fence_before();
-  __syncthreads();
+  if (PAIR) cluster_sync_all();       // the peer's barriers and tensor memory exist before anything targets them
+  else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   pdl_trigger();
   pdl_wait();
+  // pair: p.row_groups counts PAIRS of row groups; CTA `cta_rank` of a pair works on row group 2 * rgp + cta_rank (a
+  // group past the end has no valid row blocks: nothing is loaded for it and nothing stored)
   const int total = p.row_groups * p.n_tiles * p.splits;
+  const int wstart = PAIR ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+  const int wstep = PAIR ? (int)(gridDim.x >> 1) : (int)gridDim.x;
   const int rb_per_cta = p.blocksA * p.acc;
-  const int nb = p.block_n / p.bwB;
+  const int nb = PAIR ? p.block_n / p.bwB / 2 : p.block_n / p.bwB;      // dY boxes this CTA loads per stage
 
   if (warp == 0) {
     // TMA producer: the whole warp loops, one elected lane issues
     int stage = 0;
     uint32_t phase = 0;
     const uint32_t b_tx = (uint32_t)nb * p.b_box_bytes;
-    for (int it = blockIdx.x; it < total; it += gridDim.x) {
+    for (int it = wstart; it < total; it += wstep) {
       const int z = it % p.splits;
       const int nt = (it / p.splits) % p.n_tiles;
-      const int rg = it / (p.splits * p.n_tiles);
-      int valid = p.RB - rg * rb_per_cta;
-      if (valid > rb_per_cta) valid = rb_per_cta;
-      const uint32_t tx = (uint32_t)valid * p.a_box_bytes + b_tx;
+      const int rgp = it / (p.splits * p.n_tiles);
+      const int rg = PAIR ? 2 * rgp + (int)cta_rank : rgp;
+      int valid = min(max(p.RB - rg * rb_per_cta, 0), rb_per_cta);
+      // pair: only the leader arms its barrier, with the bytes of BOTH CTAs (the peer's loads complete on it too)
+      const int valid_peer = PAIR ? min(max(p.RB - (2 * rgp + 1 - (int)cta_rank) * rb_per_cta, 0), rb_per_cta) : 0;
+      const uint32_t tx = (uint32_t)(valid + valid_peer) * p.a_box_bytes + (PAIR ? 2u * b_tx : b_tx);
       const int kt_end = min((z + 1) * p.tiles_per_split, p.k_tiles);
       for (int kt = z * p.tiles_per_split; kt < kt_end; ++kt) {
         int q = kt;
@@ -865,25 +879,29 @@ conv_wgrad_tc_kernel(const __grid_constant__ TcWgradParams p) {
         mbar_wait(&empty[stage], phase ^ 1);
         if (elect_one()) {
           uint8_t* sa = smem + (size_t)stage * p.stage_bytes;
-          mbar_expect_tx(&full[stage], tx);
+          if (!PAIR || leader) mbar_expect_tx(&full[stage], tx);
           int rb = rg * rb_per_cta;
           int tap = rb / p.cin_blocks, cb = rb - tap * p.cin_blocks;
           for (int j = 0; j < valid; j += p.runA) {      // `valid` is a multiple of runA (whole runs only)
-            tma_load_5d(sa + (size_t)j * p.a_box_bytes, &p.x_map[p.tap_map[tap]], &full[stage], 0,
-                        w0 + p.tap_dw[tap], h0 + p.tap_dh[tap], n0, cb);
+            if (PAIR) tma_load_5d_pair(sa + (size_t)j * p.a_box_bytes, &p.x_map[p.tap_map[tap]], &full[stage], 0,
+                                       w0 + p.tap_dw[tap], h0 + p.tap_dh[tap], n0, cb);
+            else      tma_load_5d(sa + (size_t)j * p.a_box_bytes, &p.x_map[p.tap_map[tap]], &full[stage], 0,
+                                  w0 + p.tap_dw[tap], h0 + p.tap_dh[tap], n0, cb);
             cb += p.runA;
             if (cb >= p.cin_blocks) { cb -= p.cin_blocks; ++tap; }   // runA divides cin_blocks
           }
           uint8_t* sbm = sa + (size_t)rb_per_cta * p.a_box_bytes;
-          tma_load_5d(sbm, &p.dy_map, &full[stage], 0, w0, h0, n0, nt * nb);
+          if (PAIR) tma_load_5d_pair(sbm, &p.dy_map, &full[stage], 0, w0, h0, n0, (2 * nt + (int)cta_rank) * nb);
+          else      tma_load_5d(sbm, &p.dy_map, &full[stage], 0, w0, h0, n0, nt * nb);
         }
         __syncwarp();
         if (++stage == p.stages) { stage = 0; phase ^= 1; }
       }
     }
   } else if (warp == 1) {
-    // MMA issuer: the whole warp loops, one elected lane issues
-    const uint32_t idesc = make_idesc_bf16(TC_BLOCK_M, p.block_n, 1, 1);
+    // MMA issuer: the whole warp loops, one elected lane issues (pair: the leader CTA only)
+    if (!PAIR || leader) {
+    const uint32_t idesc = make_idesc_bf16(PAIR ? 2 * TC_BLOCK_M : TC_BLOCK_M, p.block_n, 1, 1);
     const int ksteps = p.kp / 16;
     const uint32_t rowA = (uint32_t)p.bwA * 2, rowB = (uint32_t)p.bwB * 2;
     const uint32_t ltA = swizzle_layout_type(rowA), ltB = swizzle_layout_type(rowB);
@@ -895,9 +913,10 @@ conv_wgrad_tc_kernel(const __grid_constant__ TcWgradParams p) {
     const uint32_t stage16 = p.stage_bytes >> 4, acc16 = ((uint32_t)p.blocksA * p.a_box_bytes) >> 4;
     int stage = 0;
     uint32_t phase = 0, tphase = 0;
-    for (int it = blockIdx.x; it < total; it += gridDim.x) {
+    for (int it = wstart; it < total; it += wstep) {
       const int z = it % p.splits;
-      const int rg = it / (p.splits * p.n_tiles);
+      const int rgp = it / (p.splits * p.n_tiles);
+      const int rg = PAIR ? 2 * rgp : rgp;              // the leader's row group is the fuller one of a pair
       int valid = p.RB - rg * rb_per_cta;
       if (valid > rb_per_cta) valid = rb_per_cta;
       const int nacc = (valid + p.blocksA - 1) / p.blocksA;
@@ -914,17 +933,21 @@ conv_wgrad_tc_kernel(const __grid_constant__ TcWgradParams p) {
             const uint64_t da_a = da_s + (uint64_t)((uint32_t)a * acc16);
             const uint32_t d = tmem_base + (uint32_t)(a * p.block_n);
 #pragma unroll 4
-            for (int ks = 0; ks < ksteps; ++ks)
-              umma_bf16(d, da_a + (uint64_t)(ks * a_step), db_s + (uint64_t)(ks * b_step), idesc,
-                        (kt > kt_begin || ks > 0) ? 1u : 0u);
+            for (int ks = 0; ks < ksteps; ++ks) {
+              const uint32_t accf = (kt > kt_begin || ks > 0) ? 1u : 0u;
+              if (PAIR) umma_bf16_pair(d, da_a + (uint64_t)(ks * a_step), db_s + (uint64_t)(ks * b_step), idesc, accf);
+              else      umma_bf16(d, da_a + (uint64_t)(ks * a_step), db_s + (uint64_t)(ks * b_step), idesc, accf);
+            }
           }
-          umma_commit(&empty[stage]);
-          if (kt == kt_end - 1) umma_commit(tfull);
+          // frees the stage (in both CTAs of a pair) once these MMAs have read it
+          if (PAIR) umma_commit_pair(&empty[stage]); else umma_commit(&empty[stage]);
+          if (kt == kt_end - 1) { if (PAIR) umma_commit_pair(tfull); else umma_commit(tfull); }
         }
         __syncwarp();
         if (++stage == p.stages) { stage = 0; phase ^= 1; }
       }
       tphase ^= 1;
+    }
     }
   } else if (XF && warp >= 6) {
     // ===================== operand transform (warps 6..): X tile -> bf16(act(a*x + b)) in place =====================
@@ -939,7 +962,7 @@ conv_wgrad_tc_kernel(const __grid_constant__ TcWgradParams p) {
     const float leak = p.xf_leak;
     int stage = 0;
     uint32_t phase = 0;
-    for (int it = blockIdx.x; it < total; it += gridDim.x) {
+    for (int it = wstart; it < total; it += wstep) {
       const int z = it % p.splits;
       const int rg = it / (p.splits * p.n_tiles);
       int valid = p.RB - rg * rb_per_cta;
@@ -971,10 +994,12 @@ conv_wgrad_tc_kernel(const __grid_constant__ TcWgradParams p) {
     const int row = quad * 32 + lane;
     uint32_t tphase = 0;
     const int64_t rows_total = (int64_t)p.taps * p.Cin;
-    for (int it = blockIdx.x; it < total; it += gridDim.x) {
+    const uint32_t tempty_leader = PAIR ? mapa_u32(tempty, 0) : 0u;
+    for (int it = wstart; it < total; it += wstep) {
       const int z = it % p.splits;
       const int nt = (it / p.splits) % p.n_tiles;
-      const int rg = it / (p.splits * p.n_tiles);
+      const int rgp = it / (p.splits * p.n_tiles);
+      const int rg = PAIR ? 2 * rgp + (int)cta_rank : rgp;
       mbar_wait(tfull, tphase);
       tc_fence_after();
       for (int a = 0; a < p.acc; ++a) {
@@ -1026,13 +1051,20 @@ conv_wgrad_tc_kernel(const __grid_constant__ TcWgradParams p) {
       }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(tempty);
+      if (lane == 0) {
+        if (PAIR) mbar_arrive_cluster(tempty_leader);     // the leader's MMA warp waits for both CTAs' epilogues
+        else mbar_arrive(tempty);
+      }
       tphase ^= 1;
     }
   }
   tc_fence_before();
-  __syncthreads();
-  if (warp == 1) tmem_dealloc(tmem_base, p.tmem_cols);
+  if (PAIR) cluster_sync_all();      // neither CTA may leave while the pair's MMAs / remote arrivals can still touch it
+  else __syncthreads();
+  if (warp == 1) {
+    if (PAIR) tmem_dealloc_pair(tmem_base, p.tmem_cols);
+    else tmem_dealloc(tmem_base, p.tmem_cols);
+  }
 }
 
 // Sum of the split-K partials in a fixed order.  A CTA covers 256/S consecutive float4 outputs with S thread
@@ -1369,6 +1401,7 @@ static void forward_tap(int r, int s, int pad, int stride, int8_t* map, int8_t* 
 }
 
 struct WgradShape {
+  int pair;
   int block_n, n_tiles, acc, cin_blocks, RB, row_groups, kp, stages, PW, PH, PN, tiles_w, tiles_h, tiles_n, k_tiles;
   int splits, tiles_per_split, bwA, bwB, blocksA, runA;
   uint32_t a_box_bytes, b_box_bytes, stage_bytes, tmem_cols;
@@ -1377,7 +1410,14 @@ struct WgradShape {
 
 static int box_width(int c) { return c % 64 == 0 ? 64 : (c % 32 == 0 ? 32 : (c % 16 == 0 ? 16 : 0)); }
 
-static bool wgrad_shape(const rn_conv_desc* d, WgradShape* w) {
+// CTA pairs for wgrad: RN_WG_PAIR=0 off, =1 wherever the dY tile splits in two, default see wgrad_shape.
+static int wgrad_pair_mode() {
+  const char* e = getenv("RN_WG_PAIR");            // read on every plan creation: tests toggle it in-process
+  return e ? atoi(e) : -1;
+}
+
+static bool wgrad_shape(const rn_conv_desc* d, WgradShape* w, bool allow_pair = true) {
+  w->pair = 0;
   w->bwA = box_width(d->Cin);
   w->block_n = choose_block_n(d->Cout);
   if (w->block_n == 0) return false;
@@ -1427,6 +1467,34 @@ static bool wgrad_shape(const rn_conv_desc* d, WgradShape* w) {
   }
   if (!found) return false;
   w->row_groups = (w->RB + w->blocksA * w->acc - 1) / (w->blocksA * w->acc);
+  int sms = RN_NUM_SMS;
+  {
+    const int pm = wgrad_pair_mode();
+    // default: wherever the tile allows it, unless an odd number of row groups would leave a tenth or more of the
+    // pairs' tensor-core time on an empty row group.  Measured on ResNet-50 (profiles/r02_wgrad_pair_ab.txt): the
+    // gain comes as much from the halved split-K factor (half the partial tiles written and re-read) as from the
+    // cheaper operand fetch: 1x1 256 -> 1024 at 14x14 -11 %, 1x1/2 256 -> 512 -14 %, 3x3 256 -> 256 (9 row groups) +5 %.
+    const int rg = (w->row_groups < 2 && w->acc >= 2) ? 2 : w->row_groups;
+    const bool want = pm == 1 || (pm < 0 && (rg % 2 == 0 || rg >= 11));
+    // a pair needs two row groups: when one CTA's accumulators cover all rows, each CTA of the pair takes half of them
+    if (allow_pair && want && pm != 0 && nb % 2 == 0 && w->row_groups < 2 && w->acc >= 2 &&
+        w->RB > w->blocksA * (w->acc / 2)) {
+      w->acc /= 2;
+      const int rbpc = w->blocksA * w->acc;
+      if (w->cin_blocks >= rbpc) w->runA = (w->cin_blocks % rbpc == 0) ? rbpc : 1;
+      else w->runA = (rbpc % w->cin_blocks == 0) ? w->cin_blocks : 1;
+      w->row_groups = (w->RB + rbpc - 1) / rbpc;
+    }
+    if (allow_pair && want && pm != 0 && nb % 2 == 0 && w->row_groups >= 2) {
+      w->pair = 1;
+      w->row_groups = (w->row_groups + 1) / 2;         // pairs of row groups
+      sms = RN_NUM_SMS / 2;                            // work items are executed by pairs of CTAs
+      const size_t stage = (size_t)w->blocksA * w->acc * w->a_box_bytes + (size_t)(nb / 2) * w->b_box_bytes;
+      const int stages = (int)((204 * 1024) / stage);
+      w->stage_bytes = (uint32_t)stage;
+      w->stages = stages > 8 ? 8 : stages;
+    }
+  }
   w->smem = (size_t)w->stages * w->stage_bytes + 16384 + 2048;
   uint32_t cols = 32;
   while (cols < (uint32_t)(w->acc * w->block_n)) cols <<= 1;
@@ -1439,7 +1507,7 @@ static bool wgrad_shape(const rn_conv_desc* d, WgradShape* w) {
   // split-K factor: as many work items as fit in ONE wave of the persistent grid (rounding up would leave a
   // second, almost empty wave that doubles the kernel time)
   const int base = w->row_groups * w->n_tiles;
-  int splits = RN_NUM_SMS / base;
+  int splits = sms / base;
   const int max_splits = w->k_tiles / 8 > 0 ? w->k_tiles / 8 : 1;
   if (splits > max_splits) splits = max_splits;
   if (splits < 1) splits = 1;
@@ -1486,8 +1554,9 @@ extern "C" int rn_convtc_supported(const rn_conv_desc* d, int kind) {
 
 extern "C" size_t rn_convtc_scratch_bytes(const rn_conv_desc* d, int kind) {
   if (!d || kind != 2) return 0;
-  WgradShape w;
+  WgradShape w, w1;
   if (!wgrad_shape(d, &w)) return 0;
+  if (w.pair && wgrad_shape(d, &w1, false) && w1.scratch > w.scratch) return w1.scratch;   // a plan with the operand transform never pairs
   return w.scratch;
 }
 
@@ -1742,7 +1811,7 @@ static int create_wgrad_plan(const rn_conv_desc* d, const void* x, const void* d
                              size_t scratch_bytes, rn_convtc_plan* pl, const ActView* view = nullptr,
                              const TapSpec* taps = nullptr, const BnOperand* xf = nullptr) {
   WgradShape ws;
-  if (!wgrad_shape(d, &ws)) return fail(RN_ERR_UNSUPPORTED, "convtc wgrad: shape not supported");
+  if (!wgrad_shape(d, &ws, xf == nullptr)) return fail(RN_ERR_UNSUPPORTED, "convtc wgrad: shape not supported");
   if (ws.scratch > 0 && (scratch == nullptr || scratch_bytes < ws.scratch))
     return fail(RN_ERR_SCRATCH, "convtc wgrad: scratch %zu < %zu bytes", scratch_bytes, ws.scratch);
   TcWgradParams& w = pl->w;
@@ -1753,6 +1822,7 @@ static int create_wgrad_plan(const rn_conv_desc* d, const void* x, const void* d
   w.stages = ws.stages; w.stage_bytes = ws.stage_bytes; w.tmem_cols = ws.tmem_cols;
   w.bwA = ws.bwA; w.bwB = ws.bwB; w.blocksA = ws.blocksA; w.a_box_bytes = ws.a_box_bytes; w.b_box_bytes = ws.b_box_bytes;
   w.runA = ws.runA;
+  w.pair = ws.pair;
   if (xf) {
     if (d->k != 1 || ws.bwA != 64 || view != nullptr)
       return fail(RN_ERR_UNSUPPORTED, "convtc wgrad: the BN operand transform needs a 1x1 conv over a multiple of 64 channels");
@@ -1773,16 +1843,19 @@ static int create_wgrad_plan(const rn_conv_desc* d, const void* x, const void* d
                 : encode_activation_maps_5d(w.x_map, x, d->Cin, d->W, d->H, d->N, d->stride, ws.bwA, ws.PW, ws.PH, ws.PN, ws.runA);
   if (rc) return rc;
   rc = encode_activation_maps_5d(&w.dy_map, dy, d->Cout, d->Wo, d->Ho, d->N, 1, ws.bwB, ws.PW, ws.PH, ws.PN,
-                                 ws.block_n / ws.bwB);
+                                 ws.pair ? ws.block_n / ws.bwB / 2 : ws.block_n / ws.bwB);   // pair: each CTA loads half of the tile's columns
   if (rc) return rc;
   const long total = (long)ws.row_groups * ws.n_tiles * ws.splits;
-  pl->wgrid = (int)(total < RN_NUM_SMS ? total : RN_NUM_SMS);
+  if (ws.pair) pl->wgrid = 2 * (int)(total < RN_NUM_SMS / 2 ? total : RN_NUM_SMS / 2);
+  else pl->wgrid = (int)(total < RN_NUM_SMS ? total : RN_NUM_SMS);
   pl->wsmem = xf ? (size_t)w.stages * w.stage_bytes + 16384 + 2048 + (size_t)d->Cin * 8 : ws.smem;
   pl->dw = (float*)dw;
   pl->dw_elems = (int64_t)d->k * d->k * d->Cin * d->Cout;
-  cudaError_t e = cudaFuncSetAttribute(conv_wgrad_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024));
+  cudaError_t e = cudaFuncSetAttribute(conv_wgrad_tc_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024));
   if (e == cudaSuccess)
-    e = cudaFuncSetAttribute(conv_wgrad_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024));
+    e = cudaFuncSetAttribute(conv_wgrad_tc_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024));
+  if (e == cudaSuccess)
+    e = cudaFuncSetAttribute(conv_wgrad_tc_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024));
   if (e != cudaSuccess) return fail(RN_ERR_CUDA, "convtc: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
   return RN_OK;
 }
@@ -1934,8 +2007,9 @@ extern "C" int rn_convtc_run(rn_convtc_plan* plan, float beta, void* stream) {
   cudaStream_t st = as_stream(stream);
   if (plan->kind == 2) {
     if (beta != 0.f) return fail(RN_ERR_UNSUPPORTED, "convtc_run: wgrad overwrites its output (beta must be 0)");
-    if (plan->w.xf) launch_pdl(conv_wgrad_tc_kernel<true>, plan->wgrid, TC_THREADS + TC_XF_WARPS * 32, plan->wsmem, st, plan->w);
-    else            launch_pdl(conv_wgrad_tc_kernel<false>, plan->wgrid, TC_THREADS, plan->wsmem, st, plan->w);
+    if (plan->w.xf)        launch_pdl(conv_wgrad_tc_kernel<true, false>, plan->wgrid, TC_THREADS + TC_XF_WARPS * 32, plan->wsmem, st, plan->w);
+    else if (plan->w.pair) launch_conv(conv_wgrad_tc_kernel<false, true>, plan->wgrid, TC_THREADS, plan->wsmem, st, true, plan->w);
+    else                   launch_pdl(conv_wgrad_tc_kernel<false, false>, plan->wgrid, TC_THREADS, plan->wsmem, st, plan->w);
     int rc = check_launch("conv_wgrad_tc_kernel");
     if (rc) return rc;
     if (plan->w.splits > 1) {
@@ -2001,8 +2075,8 @@ extern "C" int rn_convtc_plan_describe(const rn_convtc_plan* plan, char* buf, si
   RN_REQUIRE(plan && buf && n > 0, "convtc_plan_describe: bad arguments");
   if (plan->kind == 2) {
     const TcWgradParams& w = plan->w;
-    snprintf(buf, n, "wgrad block_n=%d acc=%d kp=%d stages=%d splits=%d grid=%d bn_operand=%d", w.block_n, w.acc, w.kp, w.stages,
-             w.splits, plan->wgrid, w.xf);
+    snprintf(buf, n, "wgrad block_n=%d acc=%d kp=%d stages=%d splits=%d grid=%d pair=%d bn_operand=%d", w.block_n, w.acc, w.kp, w.stages,
+             w.splits, plan->wgrid, w.pair, w.xf);
     return RN_OK;
   }
   const TcConvParams& p = plan->p[0];

@@ -192,6 +192,60 @@ def test_convtc_wgrad(case):
     _run_fprop_wgrad(case, fprop=False)
 
 
+WGRAD_PAIR_CASES = [
+    # N, H, W, Cin, Cout, k, stride, pad, (Ho, Wo)
+    (8, 14, 14, 256, 256, 3, 1, 1, (14, 14)),     # 36 row blocks: 9 row groups -> 5 pairs, the last one half empty
+    (8, 14, 14, 256, 1024, 1, 1, 0, (14, 14)),    # one row group: the pair splits the CTA's two accumulators
+    (8, 14, 14, 1024, 256, 1, 1, 0, (14, 14)),
+    (4, 28, 28, 128, 128, 3, 1, 1, (28, 28)),     # BLOCK_N = 128: each CTA loads one 64-channel dY box
+    (4, 28, 28, 256, 256, 3, 2, 1, (14, 14)),     # stride 2
+    (2, 7, 7, 512, 2048, 1, 1, 0, (7, 7)),        # eight column tiles
+    (3, 9, 11, 192, 128, 3, 1, 1, (9, 11)),       # ragged pixel tiles, 27 row blocks
+    (4, 16, 16, 160, 320, 3, 1, 1, (16, 16)),     # BLOCK_N = 160 is five 32-channel boxes: cannot pair, must fall back
+]
+
+
+@pytest.mark.parametrize("case", WGRAD_PAIR_CASES)
+def test_convtc_wgrad_cta_pairs(case, monkeypatch):
+    """wgrad as clusters of two CTAs (tcgen05.mma.cta_group::2, M = 256; RN_WG_PAIR=1 forces it wherever the dY tile
+    splits in two) against the oracle, and against the single-CTA kernel (same products, fp32 sums in another order)."""
+    from distributed_tensorflow_resnet_b200._lib import describe_plan
+    N, H, W, Cin, Cout, k, s, pad, (Ho, Wo) = case
+    g = torch.Generator().manual_seed(sum(case[:8]) + 5)
+    x = torch.randn(N, H, W, Cin, generator=g).to(BF)
+    w = (torch.randn(k, k, Cin, Cout, generator=g) / (k * k * Cin) ** 0.5).to(BF)
+    dy = torch.randn(N, Ho, Wo, Cout, generator=g).to(BF)
+    net = ro.Net(dtype=torch.float64, params={"w": w.double().numpy()})
+    xv = ro.Var(x.double())
+    yv = net.conv2d(xv, "w", k, Cin, Cout, s, pad, (Ho, Wo), None, "y")
+    yv.grad = dy.double()
+    net.backward()
+    want = torch.as_tensor(net.param_grads["w"])
+    d = ConvDesc(N, H, W, Cin, Ho, Wo, Cout, k, s, pad, RN_BF16)
+    X, DY = dev(x), dev(dy)
+    got = {}
+    for mode in ("1", "0"):
+        monkeypatch.setenv("RN_WG_PAIR", mode)
+        nb = lib.rn_convtc_scratch_bytes(C.byref(d), 2)
+        scratch = torch.full((max(nb, 16),), 0xFF, dtype=torch.uint8, device="cuda")
+        DW = torch.full((k, k, Cin, Cout), float("nan"), dtype=torch.float32, device="cuda")
+        plan = C.c_void_p()
+        check(lib.rn_convtc_plan_create(C.byref(d), 2, ptr(X), ptr(DY), ptr(DW), ptr(scratch), nb, C.byref(plan)), "plan wgrad")
+        desc = describe_plan(plan)
+        if mode == "1" and Cout != 320:
+            assert "pair=1" in desc, desc
+        else:
+            assert "pair=0" in desc, desc
+        for _ in range(2):
+            check(lib.rn_convtc_run(plan, 0.0, stream()), "run wgrad")
+        torch.cuda.synchronize()
+        lib.rn_convtc_plan_destroy(plan)
+        assert torch.isfinite(DW).all(), desc
+        assert rel_err(DW.double().cpu(), want) < 2e-3, desc
+        got[mode] = DW.clone()
+    assert rel_err(got["1"].double().cpu(), got["0"].double().cpu()) < 1e-5
+
+
 @pytest.mark.parametrize("beta", [0.0, 1.0])
 @pytest.mark.parametrize("case", S2_CASES + [c + ((c[1], c[2]),) for c in (CASES[3], CASES[5], CASES[7])])
 def test_convtc_dgrad_stride2_and_accumulate(case, beta):
