@@ -230,7 +230,7 @@ def profile_step(ex, graph, iters=3):
     return {k: sum(v) / len(v) for k, v in acc.items()}
 
 
-def roofline_report(ex, graph, per_launch_ms, pk, clocks=None):
+def roofline_report(ex, graph, per_launch_ms, pk, clocks=None, workload=None, batch=None):
     cf = conv_flops(graph)
     fams = {}
     for name, ms in per_launch_ms.items():
@@ -264,7 +264,10 @@ def roofline_report(ex, graph, per_launch_ms, pk, clocks=None):
     tp = os.path.join(ROOT, "profiles", "traffic.json")     # per-launch DRAM bytes / tensor-pipe % from the ncu captures
     if top and os.path.exists(tp):
         tj = json.load(open(tp))
-        if tj.get("sources_sha256") == sources_digest():
+        if (tj.get("workload"), tj.get("batch")) != (workload, batch):
+            stale = "profiles/traffic.json was captured on %s at batch %s: traffic not reported for this workload" % (
+                tj.get("workload"), tj.get("batch"))
+        elif tj.get("sources_sha256") == sources_digest():
             traffic = tj.get("dram_bytes_per_launch", {}).get(top["kernel"])
             tensor_pipe = tj.get("tensor_pipe_pct")
         else:
@@ -622,7 +625,7 @@ def run_ours(args):
                         if b_:
                             extra = " %8.1f GB/s" % (b_ / ms_ / 1e6)
                     f.write("%-44s %9.4f ms%s%s\n" % (name, ms_, extra, ("  [" + plans[name] + "]") if name in plans else ""))
-        roof, table, prof_total = roofline_report(ex, model.graph, per_launch, pk, clocks)
+        roof, table, prof_total = roofline_report(ex, model.graph, per_launch, pk, clocks, args.workload, B)
         cpu = None
         if not args.no_cpu_baseline and world == 1:      # rank 0 at N = 1 only: at N > 1 the other ranks' GPUs would idle
             cb = 8 if args.workload == "imagenet50" else 64

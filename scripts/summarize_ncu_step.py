@@ -110,5 +110,6 @@ for k, (c, t, rd, wr, tp) in agg.items():
         if tp > 0:
             pipe[fam_of[k]] = round(tp / t, 1)
 json.dump({"sources_sha256": bench.sources_digest(), "captured_by": "scripts/ncu_step.sh + scripts/summarize_ncu_step.py " + tag,
+           "workload": "imagenet50", "batch": 128,
            "dram_bytes_per_launch": traffic, "tensor_pipe_pct": pipe}, open(os.path.join(ROOT, "profiles", "traffic.json"), "w"), indent=1)
 print(json.dumps(json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))), indent=1))
