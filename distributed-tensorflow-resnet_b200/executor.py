@@ -1122,15 +1122,26 @@ class Executor:
         lists = [(lst, ready) for lst, ready in self._segments()] if self.train else [(self.fwd, [])]
         if self.train:
             lists.append((self.update, None))
-        for lst, ready in lists:
-            gexec = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(gexec, pool=pool):
-                if ready is None:
-                    self._run_list(lst, torch.cuda.current_stream().cuda_stream)
-                else:
-                    self._run_overlapped(lst, torch.cuda.current_stream())
-            pool = gexec.pool()
-            graphs.append((gexec, ready))
+        # No garbage collection while a stream is capturing: if the cyclic collector happens to free an OLDER model's
+        # CUDAGraph objects in the middle of this capture, their cudaGraphExecDestroy is "not permitted when stream is
+        # capturing" and invalidates it (torch.cuda.graph no longer collects before capturing by itself).
+        import gc
+        gc.collect()
+        gc_was_on = gc.isenabled()
+        gc.disable()
+        try:
+            for lst, ready in lists:
+                gexec = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(gexec, pool=pool):
+                    if ready is None:
+                        self._run_list(lst, torch.cuda.current_stream().cuda_stream)
+                    else:
+                        self._run_overlapped(lst, torch.cuda.current_stream())
+                pool = gexec.pool()
+                graphs.append((gexec, ready))
+        finally:
+            if gc_was_on:
+                gc.enable()
         self._graph_exec = graphs
 
     def _replay(self):

@@ -227,8 +227,15 @@ def test_convtc_wgrad_cta_pairs(case, monkeypatch):
     for mode in ("1", "0"):
         monkeypatch.setenv("RN_WG_PAIR", mode)
         nb = lib.rn_convtc_scratch_bytes(C.byref(d), 2)
-        scratch = torch.full((max(nb, 16),), 0xFF, dtype=torch.uint8, device="cuda")
-        DW = torch.full((k, k, Cin, Cout), float("nan"), dtype=torch.float32, device="cuda")
+        # scratch and dW sit between 4 KB guard zones that must come back untouched (the epilogue stores through
+        # computed addresses, not through a bounds-checked tensor map)
+        G = 4096
+        sbuf = torch.full((max(nb, 16) + 2 * G,), 0xA5, dtype=torch.uint8, device="cuda")
+        scratch = sbuf[G:G + max(nb, 16)]
+        n_dw = k * k * Cin * Cout
+        dbuf = torch.full((n_dw + 2 * G // 4,), float("nan"), dtype=torch.float32, device="cuda")
+        dbuf[:G // 4] = 12345.0; dbuf[G // 4 + n_dw:] = 12345.0
+        DW = dbuf[G // 4:G // 4 + n_dw].view(k, k, Cin, Cout)
         plan = C.c_void_p()
         check(lib.rn_convtc_plan_create(C.byref(d), 2, ptr(X), ptr(DY), ptr(DW), ptr(scratch), nb, C.byref(plan)), "plan wgrad")
         desc = describe_plan(plan)
@@ -241,6 +248,8 @@ def test_convtc_wgrad_cta_pairs(case, monkeypatch):
         torch.cuda.synchronize()
         lib.rn_convtc_plan_destroy(plan)
         assert torch.isfinite(DW).all(), desc
+        assert bool((sbuf[:G] == 0xA5).all()) and bool((sbuf[G + max(nb, 16):] == 0xA5).all()), "scratch guard overwritten: " + desc
+        assert bool((dbuf[:G // 4] == 12345.0).all()) and bool((dbuf[G // 4 + n_dw:] == 12345.0).all()), "dW guard overwritten: " + desc
         assert rel_err(DW.double().cpu(), want) < 2e-3, desc
         got[mode] = DW.clone()
     assert rel_err(got["1"].double().cpu(), got["0"].double().cpu()) < 1e-5
