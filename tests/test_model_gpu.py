@@ -194,6 +194,45 @@ def test_frozen_reference_weights_inference():
         assert rel_err(model.graph.tensors[name].buf, net.acts[name].val) < 1e-4
 
 
+def test_capture_survives_garbage_from_an_older_model(monkeypatch):
+    """A second model built in the same process captures its CUDA graphs while an older model (reference cycles, still
+    holding its CUDAGraph objects) is uncollected garbage.  If the cyclic collector fires in the middle of the new
+    capture, the old graphs are destroyed there, which CUDA refuses ("operation not permitted when stream is
+    capturing") and which invalidates the capture; Executor.capture collects BEFORE it starts capturing and keeps
+    the collector off until it is done.  The test makes the collector fire inside the capture."""
+    import gc
+    from distributed_tensorflow_resnet_b200 import executor
+
+    def build():
+        FLAGS.reset()
+        FLAGS.update(compute_dtype="bf16", use_cuda_graph=True, dataset="cifar10", resnet_size=8, seed=3)
+        images, labels = cifar_input.input_fn(True, "synthetic:256", 16, dataset="cifar10", seed=3)
+        hps = resnet_model.HParams(num_classes=10, lrn_rate=0.1, weight_decay_rate=2e-4, optimizer='mom')
+        m = resnet_model.ResNet(hps, images, labels, "train")
+        m.build_graph()
+        m.train_op()
+        torch.cuda.synchronize()
+        return m.cost
+
+    orig = executor.Executor._run_overlapped
+    fired = []
+
+    def collect_inside_capture(self, lst, cur):
+        if torch.cuda.is_current_stream_capturing() and not fired:
+            fired.append(gc.collect())
+        return orig(self, lst, cur)
+
+    gc.collect()
+    gc.disable()
+    try:
+        c0 = build()                  # garbage from here on, and nothing collects it ...
+        monkeypatch.setattr(executor.Executor, "_run_overlapped", collect_inside_capture)
+        c1 = build()                  # ... until the collector runs in the middle of this model's capture
+    finally:
+        gc.enable()
+    assert fired and np.isfinite(c0) and c0 == c1
+
+
 def _c1_run(dtype, use_graph, steps, init):
     """BASELINE config C1 exactly as north_star states it: upstream ResNet-20, batch 128, momentum SGD
     lr 0.1, wd 2e-4 (resnet_single.py:194-202), synthetic CIFAR records through the GPU decode kernel."""
