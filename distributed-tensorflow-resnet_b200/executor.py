@@ -304,9 +304,21 @@ class Executor:
         v = bn.vars
         return (self._wptr(v["gamma"]), self._wptr(v["beta"]), bn.saved[0].data_ptr(), bn.saved[1].data_ptr(), bn.attrs["leak"])
 
+    def _elide_cast(self, t, src):
+        """An fp32 image batch bound to a bf16 placeholder needs no cast launch when its one consumer is a stem
+        convolution (space-to-depth pack or unfold: both read either dtype).  RN_NO_CAST_ELISION=1 keeps the cast."""
+        if os.environ.get("RN_NO_CAST_ELISION", "0") not in ("", "0") or src.dtype != torch.float32 or t.buf.dtype != torch.bfloat16:
+            return False
+        if not (src.is_contiguous() and src.device == self.dev and len(t.consumers) == 1):
+            return False
+        n = t.consumers[0]
+        return n.op == "conv2d" and n.inputs[0] is t and self._is_stem(n)
+
     def materialize(self, t):
         """The values of tensor `t`: its buffer, or — for a BN output that only exists inside the consuming
         convolutions' shared memory — what rn_bn_apply_act_fwd stores for it (verification / debugging only)."""
+        if getattr(t, "cast_elided", False):
+            return t.cast_from.to(t.buf.dtype)
         if t.buf is not None:
             return t.buf
         xb, bn = self._bn_operand(t)
@@ -334,6 +346,12 @@ class Executor:
         self._plan_operand_fusion()
         for t in g.placeholders.values():
             src = getattr(t, "cast_from", None)
+            if src is not None and self._elide_cast(t, src):
+                # the only reader is the stem convolution's pack / unfold kernel, which converts on the fly (same
+                # round-to-nearest): the bf16 copy of the image batch is never written
+                t.cast_elided = True
+                self._keep.append(src)
+                continue
             if src is not None:
                 sdt = RN_BF16 if src.dtype == torch.bfloat16 else RN_F32
                 ddt = RN_BF16 if t.buf.dtype == torch.bfloat16 else RN_F32
@@ -527,15 +545,17 @@ class Executor:
             return ("conv_fprop_tc:" + y.name, fn)
         if self._stem_s2d(n):
             st = self._stem_s2d_setup(n)
-            sdt = RN_BF16 if x.buf.dtype == torch.bfloat16 else RN_F32
-            pack = (lambda s, d=d, px=ptr(x.buf), pu=ptr(st["u"]), sdt=sdt:
+            xsrc = x.cast_from if getattr(x, "cast_elided", False) else x.buf
+            sdt = RN_BF16 if xsrc.dtype == torch.bfloat16 else RN_F32
+            pack = (lambda s, d=d, px=ptr(xsrc), pu=ptr(st["u"]), sdt=sdt:
                     check(lib.rn_stem_s2d_pack(C.byref(d), px, sdt, pu, s), "rn_stem_s2d_pack"))
             run = self._s2d_plan(d, 0, st["u"], st["wp"], y.buf)
             return ("conv_fprop_tc:" + y.name, lambda s, pack=pack, run=run: (pack(s), run(s)))
         if self._is_stem(n):
             st = self._stem_setup(n)
-            sdt = RN_BF16 if x.buf.dtype == torch.bfloat16 else RN_F32
-            im2col = (lambda s, a=(ptr(x.buf), ptr(st["cols"]), d.N, d.H, d.W, d.Cin, d.Ho, d.Wo, d.k, d.stride, d.pad, st["kpad"], sdt):
+            xsrc = x.cast_from if getattr(x, "cast_elided", False) else x.buf
+            sdt = RN_BF16 if xsrc.dtype == torch.bfloat16 else RN_F32
+            im2col = (lambda s, a=(ptr(xsrc), ptr(st["cols"]), d.N, d.H, d.W, d.Cin, d.Ho, d.Wo, d.k, d.stride, d.pad, st["kpad"], sdt):
                       check(lib.rn_im2col(*a, s), "rn_im2col"))
             run = self._plan_raw(st["d1"], 0, st["cols"], st["wf"], y.buf)
             return ("conv_fprop_tc:" + y.name, lambda s, im2col=im2col, run=run: (im2col(s), run(s)))
