@@ -21,10 +21,14 @@ from .flags import FLAGS
 from .train_utils import latest_checkpoint, load_checkpoint_file, SummaryWriter
 
 
-def evaluate(hps, out=sys.stdout, poll_secs=60, max_rounds=None):
-    batch_size = 100                                              # reference :62
-    images, labels = cifar_input.build_input(FLAGS.dataset, FLAGS.eval_data_path or "synthetic:10000", batch_size,
-                                             FLAGS.mode, seed=FLAGS.seed)
+def evaluate(hps, out=sys.stdout, poll_secs=60, max_rounds=None, inputs=None):
+    """`inputs` = (images, labels) device tensors refilled by `images._rn_pipeline` (seek / next_batch); default: the
+    CIFAR eval pipeline at batch 100 (reference :62).  resnet_imagenet_eval passes the vgg_preprocessing eval input."""
+    if inputs is None:
+        batch_size = 100                                          # reference :62
+        inputs = cifar_input.build_input(FLAGS.dataset, FLAGS.eval_data_path or "synthetic:10000", batch_size,
+                                         FLAGS.mode, seed=FLAGS.seed)
+    images, labels = inputs
     pipe = images._rn_pipeline
     model = resnet_model.ResNet(hps, images, labels, FLAGS.mode)
     model.build_graph(False)

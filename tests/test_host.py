@@ -336,3 +336,20 @@ dist.destroy_process_group()
            "127.0.0.1", "--master-port", str(port), str(script), ROOT]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=240)
     assert r.returncode == 0 and r.stdout.count("REFUSED") == 2 and r.stdout.count("HINT") == 2, r.stdout + r.stderr[-3000:]
+
+
+def test_reference_entry_point_names_exist():
+    """Every trainer / eval script name of the reference (resnet_cifar_main.py, resnet_cifar_train_horovod.py,
+    resnet_imagenet_main.py, resnet_imagenet_horovod_train.py, resnet_imagenet_eval.py, ...) is a module of the
+    package with a main(argv); the Horovod-named ones preset the all-reduce flags, --job_name=ps exits at once."""
+    import importlib
+    from distributed_tensorflow_resnet_b200 import FLAGS
+    for name in ("resnet_cifar_train", "resnet_cifar_main", "resnet_cifar_train_horovod", "resnet_cifar_eval",
+                 "resnet_imagenet_train", "resnet_imagenet_main", "resnet_imagenet_horovod_train", "resnet_imagenet_eval"):
+        mod = importlib.import_module("distributed_tensorflow_resnet_b200." + name)
+        assert callable(getattr(mod, "main", None)) or callable(getattr(mod, "evaluate", None)), name
+    FLAGS.reset()
+    hv = importlib.import_module("distributed_tensorflow_resnet_b200.resnet_cifar_train_horovod")
+    assert hv.main(["--job_name", "ps"]) is None                  # parsed the preset flags, then left (no parameter servers)
+    assert FLAGS.use_horovod and FLAGS.variable_update == "horovod"
+    FLAGS.reset()

@@ -125,3 +125,33 @@ def test_imagenet_trainer_runs_on_the_preprocessing_pipeline(tmp_path):
     FLAGS.reset()
     m2 = it.main(args)                                                     # finished directory: restore only
     assert m2.global_step == 6 and torch.equal(m2.executor.W, w)
+    # the ImageNet eval loop (resnet_imagenet_eval.py:169-230) on that checkpoint: vgg eval preprocessing (central crop),
+    # BN on the moving statistics, Precision / Best Precision; through the combined entry point resnet_imagenet_main
+    from distributed_tensorflow_resnet_b200 import resnet_imagenet_main, resnet_imagenet_horovod_train
+    from distributed_tensorflow_resnet_b200.train_utils import read_event_scalars
+    FLAGS.reset()
+    eval_dir = tmp_path / "eval"
+    res = resnet_imagenet_main.main(["--mode", "eval", "--eval_data_path", "synthetic:16", "--batch_size", "4",
+                                     "--resnet_size", "18", "--train_dir", str(tmp_path), "--eval_dir", str(eval_dir),
+                                     "--eval_batch_count", "3", "--eval_once", "true", "--seed", "2"])
+    assert res["global_step"] == 6 and res["total"] == 12 and 0.0 <= res["precision"] <= 1.0 and np.isfinite(res["loss"])
+    assert {"Precision", "Best Precision"} <= {t for _, t, _ in read_event_scalars(str(eval_dir))}
+    # the Horovod-named trainer is the same loop with the all-reduce flags preset; a finished directory only restores
+    FLAGS.reset()
+    m3 = resnet_imagenet_horovod_train.main(args)
+    assert FLAGS.use_horovod and FLAGS.variable_update == "horovod" and m3.global_step == 6
+
+
+def test_resnet_single_entry_point_trains_the_north_star_builders(tmp_path):
+    """resnet_single.main: the upstream builders behind the nine-field HParams of resnet_single.py:194-202 (5 residual
+    units per stage = ResNet-32, leaky ReLU 0.1, weight decay on the DW variables), checkpoints under log_root/train."""
+    from distributed_tensorflow_resnet_b200 import resnet_single
+    FLAGS.reset()
+    m = resnet_single.main(["--train_data_path", "synthetic:512", "--train_steps", "4", "--log_root", str(tmp_path),
+                            "--batch_size", "16", "--seed", "1"])
+    torch.cuda.synchronize()
+    assert m.global_step == 4 and np.isfinite(m.cost)
+    assert m.hps.num_residual_units == 5 and m.hps.relu_leakiness == 0.1
+    names = list(m.graph.variables)
+    assert any(n.endswith("/DW") for n in names) and any("unit_3_4" in n for n in names)      # upstream naming, 5 units per stage
+    assert (tmp_path / "train").is_dir() and any(f.startswith("model.ckpt-4") for f in os.listdir(tmp_path / "train"))
