@@ -345,7 +345,8 @@ def test_reference_entry_point_names_exist():
     import importlib
     from distributed_tensorflow_resnet_b200 import FLAGS
     for name in ("resnet_cifar_train", "resnet_cifar_main", "resnet_cifar_train_horovod", "resnet_cifar_eval",
-                 "resnet_imagenet_train", "resnet_imagenet_main", "resnet_imagenet_horovod_train", "resnet_imagenet_eval"):
+                 "resnet_imagenet_train", "resnet_imagenet_main", "resnet_imagenet_horovod_train", "resnet_imagenet_eval",
+                 "resnet_single", "resnet_cifar_frozen_model", "resnet_cifar_predict_from_pd"):
         mod = importlib.import_module("distributed_tensorflow_resnet_b200." + name)
         assert callable(getattr(mod, "main", None)) or callable(getattr(mod, "evaluate", None)), name
     FLAGS.reset()

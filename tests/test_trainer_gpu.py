@@ -155,3 +155,25 @@ def test_resnet_single_entry_point_trains_the_north_star_builders(tmp_path):
     names = list(m.graph.variables)
     assert any(n.endswith("/DW") for n in names) and any("unit_3_4" in n for n in names)      # upstream naming, 5 units per stage
     assert (tmp_path / "train").is_dir() and any(f.startswith("model.ckpt-4") for f in os.listdir(tmp_path / "train"))
+
+
+def test_freeze_then_predict_from_pb(tmp_path):
+    """resnet_cifar_frozen_model.main freezes the newest checkpoint into a GraphDef of Const nodes (and predicts one
+    batch); resnet_cifar_predict_from_pd.main loads that .pb into a fresh eval graph and must print the very same
+    predictions — the round trip the reference's two scripts make through tf.import_graph_def."""
+    import io
+    from distributed_tensorflow_resnet_b200 import resnet_cifar_frozen_model as fz, resnet_cifar_predict_from_pd as pp
+    FLAGS.reset()
+    ct.main(["--train_data_path", "synthetic:1024", "--batch_size", "32", "--resnet_size", "8", "--train_steps", "5",
+             "--train_dir", str(tmp_path), "--seed", "4"])
+    FLAGS.reset()
+    buf = io.StringIO()
+    a = fz.main(["--train_dir", str(tmp_path), "--resnet_size", "8", "--batch_size", "50", "--seed", "4"], out=buf)
+    assert os.path.exists(a["path"]) and "The precision:" in buf.getvalue()
+    got = tf_io.read_frozen_graph(a["path"])
+    assert len(got) == a["tensors"] and any(k.endswith("moving_variance") for k in got)
+    FLAGS.reset()
+    b = pp.main(["--frozen_model", a["path"], "--resnet_size", "8", "--EVAL_NUM", "50", "--seed", "4"], out=io.StringIO())
+    assert b["loaded"] == a["tensors"]
+    assert np.array_equal(a["prediction"], b["prediction"]) and np.array_equal(a["label"], b["label"])
+    assert a["precision"] == b["precision"]
